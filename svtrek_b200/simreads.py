@@ -1,0 +1,375 @@
+"""Seeded synthetic long-read sets with planted DEL/INS, in the SoA layout the B200 path consumes.
+
+This is the input generator for BASELINE.json's five configs: reads are produced
+directly as packed BAM-native CIGAR words (len<<4 | op) sorted by (tid, pos) -- the same order a
+coordinate-sorted BAM yields -- so the full-size configs never have to pass through BGZF.  Small sets can
+also be written as SAM (+ random SEQ/QUAL so the BAM compresses realistically) for the reference CLI.
+
+VCF lines are written in the exact shape the reference's utils/simvcf.py produces
+(``...;CIPOS=a,b;CIEND=c,d;END=e;SVELDT=SIMULATED;SVTYPE=DEL`` -- simvcf.py:173-186), plus the
+"END-first" twin that makes the reference's strstr("END=") find the real END (audit.c:145).
+Nothing here is on the product path; bench.py and the tests use it to make inputs.
+"""
+from __future__ import annotations
+
+import dataclasses
+import numpy as np
+
+OP_M, OP_I, OP_D, OP_N, OP_S, OP_H, OP_P, OP_EQ, OP_X = range(9)
+OPCHARS = "MIDNSHP=X"
+JITTER = np.array([0, 0, 0, 0, 0, 1, -1, 2, -2, 3], dtype=np.int64)
+
+
+@dataclasses.dataclass
+class ReadSet:
+    """SoA long-read set: reads sorted by (tid, pos). cigar words are BAM-native: len<<4 | op."""
+    tid_off: np.ndarray      # int64[n_tid+1]  read index range per contig
+    pos: np.ndarray          # uint32[n_reads] 0-based leftmost position (bam1_core_t.pos)
+    end: np.ndarray          # uint32[n_reads] bam_endpos(): pos + max(1, ref-consumed length)
+    n_cigar: np.ndarray      # uint32[n_reads]
+    cigar_off: np.ndarray    # uint64[n_reads+1] word offset of each read's CIGAR
+    cigar: np.ndarray        # uint32[n_words]
+    contig_len: list
+
+    @property
+    def n_reads(self) -> int:
+        return int(self.pos.shape[0])
+
+    @property
+    def n_tid(self) -> int:
+        return int(self.tid_off.shape[0] - 1)
+
+
+@dataclasses.dataclass
+class SVTruth:
+    tid: np.ndarray    # int32
+    pos0: np.ndarray   # int64 0-based breakpoint (first deleted base / insertion point)
+    length: np.ndarray  # int64
+    is_del: np.ndarray  # bool
+
+
+def ref_consumed(words: np.ndarray) -> np.ndarray:
+    op = words & 15
+    ln = (words >> 4).astype(np.int64)
+    # M, D, N, =, X consume the reference (bam_cigar_type & 2)
+    consumes = (op == OP_M) | (op == OP_D) | (op == OP_N) | (op == OP_EQ) | (op == OP_X)
+    return np.where(consumes, ln, 0)
+
+
+def endpos_from_cigar(pos, cigar_off, cigar) -> np.ndarray:
+    """bam_endpos (htslib sam.c:638-643) for every read, vectorised."""
+    n = pos.shape[0]
+    rc = ref_consumed(cigar)
+    csum = np.zeros(cigar.shape[0] + 1, dtype=np.int64)
+    np.cumsum(rc, out=csum[1:])
+    rlen = csum[cigar_off[1:].astype(np.int64)] - csum[cigar_off[:-1].astype(np.int64)]
+    rlen = np.where(rlen == 0, 1, rlen)
+    return (pos.astype(np.int64) + rlen).astype(np.uint32)[:n]
+
+
+def plant_svs(rng, contig_len, n_sv, *, min_len=60, max_len=2000, min_gap=1500, margin=25000,
+              kind="alt", log_uniform=False) -> tuple:
+    """SV breakpoints on one contig: sorted, >= min_gap apart (and clear of the previous DEL's span)."""
+    span = contig_len - 2 * margin
+    if n_sv <= 0 or span <= 0:
+        z = np.zeros(0, dtype=np.int64)
+        return z, z, np.zeros(0, dtype=bool)
+    if log_uniform:
+        length = np.exp(rng.uniform(np.log(min_len), np.log(max_len), n_sv)).astype(np.int64)
+    else:
+        length = rng.integers(min_len, max_len + 1, n_sv)
+    if kind == "alt":
+        is_del = (np.arange(n_sv) % 2) == 0
+    elif kind == "ins":
+        is_del = np.zeros(n_sv, dtype=bool)
+    else:
+        is_del = np.ones(n_sv, dtype=bool)
+    need = np.maximum(np.where(is_del, length + 200, 0), min_gap)   # room each SV takes before the next may start
+    slack = span - int(need.sum())
+    if slack < 0:
+        raise ValueError("contig too small for the requested SV density")
+    cuts = np.sort(rng.integers(0, slack + 1, n_sv))
+    pos0 = margin + cuts + np.concatenate(([0], np.cumsum(need)[:-1]))
+    return pos0.astype(np.int64), length.astype(np.int64), is_del
+
+
+def _expand_ranges(lo, hi):
+    """flat (owner, index) pairs for integer ranges [lo_i, hi_i)."""
+    cnt = np.maximum(hi - lo, 0)
+    owner = np.repeat(np.arange(lo.shape[0]), cnt)
+    start = np.repeat(lo, cnt)
+    base = np.repeat(np.cumsum(cnt) - cnt, cnt)
+    idx = start + (np.arange(int(cnt.sum())) - base)
+    return owner, idx
+
+
+def gen_contig(rng, contig_len, n_reads, read_len, small_rate, sv_pos0, sv_len, sv_is_del, *,
+               carrier_frac=0.8, split_frac=0.05, clip_len=(200, 3000), chunk=1 << 17):
+    """One contig's reads -> (pos, n_cigar, cigar words). Vectorised, chunked over reads."""
+    starts_all = np.sort(rng.integers(0, max(1, contig_len - read_len), n_reads)).astype(np.int64)
+    out_pos, out_n, out_words = [], [], []
+    for c0 in range(0, n_reads, chunk):
+        s = starts_all[c0:c0 + chunk].copy()
+        nr = s.shape[0]
+        e = s + read_len
+        lead = np.zeros(nr, dtype=np.int64)   # leading soft clip length (0 = none)
+        trail = np.zeros(nr, dtype=np.int64)
+
+        # --- planted SVs overlapped by each read (breakpoint well inside the read)
+        lo = np.searchsorted(sv_pos0, s + 50, side="left")
+        hi = np.searchsorted(sv_pos0, e - 50, side="left")
+        rid_sv, k = _expand_ranges(lo, hi)
+        carried = rng.random(rid_sv.shape[0]) < carrier_frac
+        rid_sv, k = rid_sv[carried], k[carried]
+        bp = sv_pos0[k] + JITTER[rng.integers(0, JITTER.shape[0], k.shape[0])]
+        ln = sv_len[k]
+        isd = sv_is_del[k]
+        # split reads: first chosen SV per read cuts the read and becomes a soft clip
+        is_split = rng.random(rid_sv.shape[0]) < split_frac
+        if is_split.any():
+            cand = np.flatnonzero(is_split)
+            first = np.unique(rid_sv[cand], return_index=True)[1]
+            cand = cand[first]
+            left_part = rng.random(cand.shape[0]) < 0.5
+            cl = rng.integers(clip_len[0], clip_len[1] + 1, cand.shape[0])
+            r = rid_sv[cand]
+            # A: keep [s, bp) + trailing clip ; B: leading clip + [bp(+len), e)
+            e[r[left_part]] = bp[cand[left_part]]
+            trail[r[left_part]] = cl[left_part]
+            nb = np.where(isd[cand[~left_part]], bp[cand[~left_part]] + ln[cand[~left_part]], bp[cand[~left_part]])
+            s[r[~left_part]] = nb
+            lead[r[~left_part]] = cl[~left_part]
+        ev_rid = [rid_sv]
+        ev_pos = [bp]
+        ev_op = [np.where(isd, OP_D, OP_I)]
+        ev_len = [ln]
+
+        # --- small indels (sequencing noise)
+        if small_rate > 0:
+            cnt = rng.poisson(small_rate * read_len, nr)
+            rid_sm = np.repeat(np.arange(nr), cnt)
+            p = starts_all[c0:c0 + chunk][rid_sm] + rng.integers(1, read_len - 1, rid_sm.shape[0])
+            near = np.searchsorted(sv_pos0, p + 60, side="right") - 1       # last SV starting <= p+60
+            near = np.clip(near, 0, max(0, sv_pos0.shape[0] - 1))
+            if sv_pos0.shape[0]:
+                blocked = (p >= sv_pos0[near] - 60) & (p <= sv_pos0[near] + np.where(sv_is_del[near], sv_len[near], 0) + 60)
+            else:
+                blocked = np.zeros(p.shape[0], dtype=bool)
+            keep = ~blocked
+            rid_sm, p = rid_sm[keep], p[keep]
+            sm_del = rng.random(p.shape[0]) < 0.5
+            sm_len = 1 + (rng.random(p.shape[0]) < 0.15) + (rng.random(p.shape[0]) < 0.03)
+            ev_rid.append(rid_sm); ev_pos.append(p); ev_op.append(np.where(sm_del, OP_D, OP_I)); ev_len.append(sm_len.astype(np.int64))
+
+        rid = np.concatenate(ev_rid); p = np.concatenate(ev_pos)
+        op = np.concatenate(ev_op).astype(np.int64); ln = np.concatenate(ev_len)
+        rl = np.where(op == OP_D, ln, 0)
+        ok = (p >= s[rid] + 1) & (p + rl <= e[rid] - 1)
+        rid, p, op, ln, rl = rid[ok], p[ok], op[ok], ln[ok], rl[ok]
+        order = np.argsort(rid.astype(np.uint64) << np.uint64(34) | p.astype(np.uint64), kind="stable")
+        rid, p, op, ln, rl = rid[order], p[order], op[order], ln[order], rl[order]
+        # drop events that start before the previous event (same read) has ended + 1
+        while True:
+            same = np.concatenate(([False], rid[1:] == rid[:-1]))
+            prev_end = np.concatenate(([0], (p + rl)[:-1]))
+            bad = same & (p < prev_end + 1)
+            if not bad.any():
+                break
+            keep = ~bad
+            rid, p, op, ln, rl = rid[keep], p[keep], op[keep], ln[keep], rl[keep]
+        same = np.concatenate(([False], rid[1:] == rid[:-1]))
+        prev_end = np.where(same, np.concatenate(([0], (p + rl)[:-1])), s[rid])
+        gap = p - prev_end                                   # M run before each event, >= 1
+        nev = np.bincount(rid, minlength=nr)
+        ev_off = np.cumsum(nev) - nev
+        last_end = s.copy()
+        has = nev > 0
+        last_idx = (ev_off + nev - 1)[has]
+        last_end[has] = (p + rl)[last_idx]
+        tail_m = e - last_end                                # final M run, >= 1
+        nw = 2 * nev + 1 + (lead > 0) + (trail > 0)
+        woff = np.cumsum(nw) - nw
+        words = np.zeros(int(nw.sum()), dtype=np.uint32)
+        li = lead > 0
+        words[woff[li]] = (lead[li] << 4 | OP_S).astype(np.uint32)
+        base = woff + li                                     # first non-clip word of each read
+        j = np.arange(rid.shape[0]) - ev_off[rid]            # event ordinal within its read
+        words[base[rid] + 2 * j] = (gap << 4 | OP_M).astype(np.uint32)
+        words[base[rid] + 2 * j + 1] = (ln << 4 | op).astype(np.uint32)
+        words[base + 2 * nev] = (tail_m << 4 | OP_M).astype(np.uint32)
+        ti = trail > 0
+        words[(base + 2 * nev + 1)[ti]] = (trail[ti] << 4 | OP_S).astype(np.uint32)
+        # split reads of kind B moved their start: re-sort the chunk by pos later (global sort below)
+        out_pos.append(s); out_n.append(nw); out_words.append(words)
+    pos = np.concatenate(out_pos) if out_pos else np.zeros(0, dtype=np.int64)
+    ncig = np.concatenate(out_n) if out_n else np.zeros(0, dtype=np.int64)
+    words = np.concatenate(out_words) if out_words else np.zeros(0, dtype=np.uint32)
+    # coordinate sort (only B-type split reads are out of place); permute CIGAR blocks accordingly
+    order = np.argsort(pos, kind="stable")
+    if not np.array_equal(order, np.arange(pos.shape[0])):
+        off = np.cumsum(ncig) - ncig
+        _, widx = _expand_ranges(off[order], (off + ncig)[order])
+        words = words[widx]
+        pos, ncig = pos[order], ncig[order]
+    return pos, ncig, words
+
+
+def simulate(seed, contig_lens, coverage, read_len, small_rate, n_sv, *, sv_kind="alt", min_len=60, max_len=2000,
+             min_gap=1500, log_uniform=False, carrier_frac=0.8, split_frac=0.05, margin=25000):
+    """Whole read set + planted truth. SVs are spread over contigs proportionally to length."""
+    rng = np.random.default_rng(seed)
+    total = float(sum(contig_lens))
+    pos_l, n_l, w_l, tid_off = [], [], [], [0]
+    t_tid, t_pos, t_len, t_del = [], [], [], []
+    left = n_sv
+    for tid, L in enumerate(contig_lens):
+        k = int(round(n_sv * L / total)) if tid < len(contig_lens) - 1 else left
+        k = max(0, min(k, left)); left -= k
+        sp, sl, sd = plant_svs(rng, L, k, min_len=min_len, max_len=max_len, min_gap=min_gap, margin=margin,
+                               kind=sv_kind, log_uniform=log_uniform)
+        nreads = int(L * coverage / read_len)
+        pos, ncig, words = gen_contig(rng, L, nreads, read_len, small_rate, sp, sl, sd,
+                                      carrier_frac=carrier_frac, split_frac=split_frac)
+        pos_l.append(pos); n_l.append(ncig); w_l.append(words); tid_off.append(tid_off[-1] + pos.shape[0])
+        t_tid.append(np.full(k, tid, dtype=np.int32)); t_pos.append(sp); t_len.append(sl); t_del.append(sd)
+    pos = np.concatenate(pos_l).astype(np.uint32)
+    ncig = np.concatenate(n_l).astype(np.uint32)
+    words = np.concatenate(w_l)
+    cigar_off = np.zeros(pos.shape[0] + 1, dtype=np.uint64)
+    np.cumsum(ncig.astype(np.uint64), out=cigar_off[1:])
+    rs = ReadSet(np.array(tid_off, dtype=np.int64), pos, None, ncig, cigar_off, words, list(contig_lens))
+    rs.end = endpos_from_cigar(pos, cigar_off, words)
+    truth = SVTruth(np.concatenate(t_tid), np.concatenate(t_pos), np.concatenate(t_len), np.concatenate(t_del))
+    return rs, truth
+
+
+# ----------------------------------------------------------------------------------------------------------
+# BASELINE.json configs.  `scale` shrinks contig length / SV count for bounded samples.
+CONFIGS = {
+    # name: (contig_lens, coverage, read_len, small_rate, n_sv, kwargs)
+    "c1": dict(contig_lens=[1_000_000], coverage=30, read_len=15000, small_rate=0.005, n_sv=500,
+               min_gap=1500),
+    "c2": dict(contig_lens=[64_000_000], coverage=30, read_len=15000, small_rate=0.005, n_sv=10_000,
+               min_gap=1500),
+    "c3": dict(contig_lens=[248_000_000, 242_000_000, 198_000_000, 190_000_000, 181_000_000, 171_000_000,
+                            159_000_000, 145_000_000, 138_000_000, 134_000_000, 135_000_000, 133_000_000,
+                            114_000_000, 107_000_000, 102_000_000, 90_000_000, 83_000_000, 80_000_000,
+                            59_000_000, 64_000_000, 47_000_000, 51_000_000, 156_000_000, 73_000_000],
+               coverage=30, read_len=15000, small_rate=0.005, n_sv=25_000, min_gap=1500),
+    "c4": dict(contig_lens=[64_000_000], coverage=60, read_len=15000, small_rate=0.08, n_sv=20_000,
+               sv_kind="ins", min_len=50, max_len=10_000, log_uniform=True, min_gap=1500),
+    "c5": dict(contig_lens=[8_000_000], coverage=200, read_len=15000, small_rate=0.005, n_sv=2000,
+               min_gap=50, min_len=60, max_len=300, margin=25000),
+}
+
+
+def make_config(name, seed=None, scale=1.0):
+    cfg = dict(CONFIGS[name])
+    if scale != 1.0:
+        cfg["contig_lens"] = [max(200_000, int(L * scale)) for L in cfg["contig_lens"]]
+        cfg["n_sv"] = max(1, int(cfg["n_sv"] * scale))
+    if seed is None:
+        seed = 20261104 + sorted(CONFIGS).index(name)
+    if name == "c5":
+        return _make_c5(seed, cfg)
+    return simulate(seed, **cfg)
+
+
+def _make_c5(seed, cfg):
+    """Stress: tandem clusters -- 50 loci x 40 SVs spaced 50-300 bp => heavily overlapping windows."""
+    rng = np.random.default_rng(seed)
+    L = cfg["contig_lens"][0]
+    n_loci = max(1, cfg["n_sv"] // 40)
+    loci = np.sort(rng.integers(100_000, L - 100_000, n_loci))
+    pos0, length, is_del = [], [], []
+    for c in loci:
+        p = c
+        for j in range(40):
+            ln = int(rng.integers(cfg["min_len"], cfg["max_len"] + 1))
+            d = (j % 2 == 0)
+            pos0.append(p); length.append(ln); is_del.append(d)
+            p += (ln if d else 0) + int(rng.integers(50, 301))
+    pos0 = np.array(pos0, dtype=np.int64); length = np.array(length, dtype=np.int64); is_del = np.array(is_del)
+    order = np.argsort(pos0, kind="stable")
+    pos0, length, is_del = pos0[order], length[order], is_del[order]
+    nreads = int(L * cfg["coverage"] / cfg["read_len"])
+    pos, ncig, words = gen_contig(rng, L, nreads, cfg["read_len"], cfg["small_rate"], pos0, length, is_del,
+                                  carrier_frac=0.3, split_frac=0.05)
+    cigar_off = np.zeros(pos.shape[0] + 1, dtype=np.uint64)
+    np.cumsum(ncig.astype(np.uint64), out=cigar_off[1:])
+    rs = ReadSet(np.array([0, pos.shape[0]], dtype=np.int64), pos.astype(np.uint32), None, ncig.astype(np.uint32),
+                 cigar_off, words, [L])
+    rs.end = endpos_from_cigar(rs.pos, cigar_off, words)
+    return rs, SVTruth(np.zeros(pos0.shape[0], dtype=np.int32), pos0, length, is_del)
+
+
+# ----------------------------------------------------------------------------------------------------------
+def vcf_lines(truth: SVTruth, seed=1, *, end_first=False, pos_noise=40, chr_prefix="chr"):
+    """VCF data lines shaped like utils/simvcf.py output (CIPOS;CIEND;END;SVELDT;SVTYPE appended to INFO).
+
+    POS is the 1-based anchor of the planted breakpoint plus uniform noise in [-pos_noise, pos_noise]
+    (an "imprecise" call).  end_first=True writes END= at the head of INFO so that the reference's
+    strstr("END=") does not hit CIEND= first."""
+    rng = np.random.default_rng(seed)
+    lines = []
+    noise = rng.integers(-pos_noise, pos_noise + 1, truth.pos0.shape[0])
+    noise_e = rng.integers(-pos_noise, pos_noise + 1, truth.pos0.shape[0])
+    ci = rng.integers(25, 150, (truth.pos0.shape[0], 4))
+    for i in range(truth.pos0.shape[0]):
+        pos = int(truth.pos0[i] + noise[i])
+        ln = int(truth.length[i])
+        if truth.is_del[i]:
+            end = int(truth.pos0[i] + ln + noise_e[i])
+            tail = f"CIPOS=-{ci[i,0]},{ci[i,1]};CIEND=-{ci[i,2]},{ci[i,3]};END={end};SVELDT=SIMULATED;SVTYPE=DEL"
+            info = f"SVLEN=-{ln};{tail}"
+            if end_first:
+                info = f"END={end};SVLEN=-{ln};CIPOS=-{ci[i,0]},{ci[i,1]};CIEND=-{ci[i,2]},{ci[i,3]};SVELDT=SIMULATED;SVTYPE=DEL"
+        else:
+            end = pos + 1
+            info = f"SVLEN={ln};CIPOS=-{ci[i,0]},{ci[i,1]};END={end};SVELDT=SIMULATED;SVTYPE=INS"
+            if end_first:
+                info = f"END={end};SVLEN={ln};CIPOS=-{ci[i,0]},{ci[i,1]};SVELDT=SIMULATED;SVTYPE=INS"
+        lines.append(f"{chr_prefix}{int(truth.tid[i]) + 1}\t{pos}\tGoldStandard{i + 1}\tN\tN\t.\tPASS\t{info}\tGT\t0/1")
+    return lines
+
+
+VCF_HEADER = ("##fileformat=VCFv4.2\n"
+              '##INFO=<ID=SVTYPE,Number=1,Type=String,Description="Type of structural variant">\n'
+              "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tSAMPLE\n")
+
+
+def write_vcf(path, lines, pad=0):
+    """pad > 0 appends junk lines: the reference drops up to 2t queued lines at EOF."""
+    with open(path, "w") as f:
+        f.write(VCF_HEADER)
+        for ln in lines:
+            f.write(ln + "\n")
+        for _ in range(pad):
+            f.write("pad\n")
+
+
+def cigar_string(words) -> str:
+    return "".join(f"{int(w) >> 4}{OPCHARS[int(w) & 15]}" for w in words)
+
+
+def write_sam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr", random_seq=True):
+    """SAM text for small sets (reference runs). SEQ/QUAL are uniform random so BGZF compresses realistically."""
+    rng = np.random.default_rng(seed)
+    bases = np.frombuffer(b"ACGT", dtype=np.uint8)
+    with open(path, "wb") as f:
+        f.write(b"@HD\tVN:1.6\tSO:coordinate\n")
+        for t, L in enumerate(rs.contig_len):
+            f.write(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L}\n".encode())
+        for t in range(rs.n_tid):
+            for r in range(int(rs.tid_off[t]), int(rs.tid_off[t + 1])):
+                w = rs.cigar[int(rs.cigar_off[r]):int(rs.cigar_off[r + 1])]
+                op = w & 15
+                qlen = int(((w >> 4)[(op == OP_M) | (op == OP_I) | (op == OP_S) | (op == OP_EQ) | (op == OP_X)]).sum())
+                if random_seq and qlen > 0:
+                    seq = bases[rng.integers(0, 4, qlen)].tobytes()
+                    qual = (rng.integers(10, 41, qlen) + 33).astype(np.uint8).tobytes()
+                else:
+                    seq, qual = b"*", b"*"
+                flag = 0 if flags is None else int(flags[r])
+                f.write(f"r{r}\t{flag}\t{chr_prefix}{t + 1}\t{int(rs.pos[r]) + 1}\t60\t{cigar_string(w)}\t*\t0\t0\t".encode())
+                f.write(seq + b"\t" + qual + b"\n")

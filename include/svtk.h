@@ -1,0 +1,163 @@
+/* svtk.h -- C ABI of libsvtk_b200.so: the B200 (sm_100a) drop-in for SVTrek's `audt` breakpoint-refinement
+ * hot path.  Plain C, plain pointers and sizes; no CUDA or torch types cross this boundary.
+ *
+ * The reference (akmami/SVTrek) has no FFI of its own; the seams this library replaces are
+ *   - the per-record seam   deletion()/insertion()/inversion()           refinement.h:25,42,60
+ *     (called only from thread_func, audit.c:180,195,228), which fan out to
+ *     refine_start/refine_end/refine_ins/refine_point                    refinement.c:103,169,278,231
+ *     and consensus_pos                                                  refinement.c:41
+ *   - the batch seam        process_vcf(audt_args*)                      audit.c:250
+ *   - the (dead) discovery entry sliding_window_ins()                    sliding_window.c:8
+ * and the vocabulary is params.h's: `interval` (params.h:123-126), the six tunables of audt_args/t_arg
+ * (params.h:57-62, 82-87), CIGAR op codes (params.h:10-18), __SV_MIN_LENGTH (params.h:33).
+ *
+ * Where the reference hands each call an open BAM (t_arg.hargs, params.h:75-79) and re-inflates it per
+ * window, this library holds the decoded reads once, in HBM, as SoA arrays (svtk_reads): the caller (the
+ * host driver, after HTSlib / the bundled BGZF reader decoded the BAM) packs pos / endpos / n_cigar /
+ * CIGAR words in coordinate order and uploads them with svtk_load_reads().  "Which reads does a window
+ * see" (sam_itr_queryi + sam_itr_next, hts.c:3049-3090, 3905-3921) is reproduced on the device.
+ *
+ * Conventions: every function returns 0 on success and a negative svtk_status on failure; the message is
+ * available from svtk_last_error().  Results use the reference's own encoding: -1 (0xFFFFFFFF) == "NA".
+ * The caller owns every host buffer it passes.  One ctx drives one GPU; a ctx is not re-entrant (use one
+ * per host thread / per GPU, like the reference's one t_arg per worker, audit.c:269-285).
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with SVTK_ERR_CUDA. */
+#ifndef SVTK_H
+#define SVTK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVTK_VERSION 100 /* 0.1.0 */
+
+typedef enum {
+    SVTK_OK = 0,
+    SVTK_ERR_ARG = -1,    /* bad argument */
+    SVTK_ERR_CUDA = -2,   /* CUDA runtime error or no device */
+    SVTK_ERR_ALLOC = -3,  /* host or device allocation failed */
+    SVTK_ERR_STATE = -4,  /* e.g. no reads loaded */
+    SVTK_ERR_IO = -5      /* file could not be opened / parsed */
+} svtk_status;
+
+/* window kinds: which reference walker a window runs */
+enum {
+    SVTK_DEL_START = 0, /* refine_start(SV_DEL, ...)  refinement.c:103 */
+    SVTK_DEL_END = 1,   /* refine_end(SV_DEL, ...)    refinement.c:169 */
+    SVTK_INS = 2,       /* refine_ins(...)            refinement.c:278 */
+    SVTK_POINT = 3      /* refine_point(SV_INV, ...)  refinement.c:231 -- never collects a position */
+};
+
+/* params.h:123-126 */
+typedef struct { uint32_t start, end; } svtk_interval;
+
+/* the six tunables of audt_args / t_arg (params.h:57-62); defaults params.h:27-32 */
+typedef struct {
+    int32_t wider_interval;           /* 20000 */
+    int32_t median_interval;          /* 10000 */
+    int32_t narrow_interval;          /* 2000  */
+    int32_t consensus_interval_range; /* 500   */
+    int32_t consensus_interval;       /* 5     */
+    int32_t consensus_min_count;      /* 3     */
+} svtk_params;
+
+/* Decoded reads, SoA, sorted by (tid, pos) == BAM coordinate order.  cigar words are BAM-native
+ * (oplen << 4 | op, htslib/sam.h:124-125).  `end` is bam_endpos() (sam.c:638-643): pos + max(1, reference
+ * length), and pos + 1 for reads flagged unmapped.  Reads with n_cigar == 0 contribute no signature
+ * (the reference indexes cigar[-1] / cigar[0] for them, refinement.c:120,210 -- undefined behaviour). */
+typedef struct {
+    int32_t n_tid;
+    int64_t n_reads;
+    int64_t n_words;
+    const int64_t *tid_off;    /* [n_tid + 1] read index range of each contig */
+    const uint32_t *pos;       /* [n_reads] bam1_core_t.pos, 0-based */
+    const uint32_t *end;       /* [n_reads] */
+    const uint32_t *n_cigar;   /* [n_reads] */
+    const uint64_t *cigar_off; /* [n_reads] word offset of each read's CIGAR inside `cigar` */
+    const uint32_t *cigar;     /* [n_words] */
+} svtk_reads;
+
+/* A batch of windows, SoA.  One window == one refine_* call of the reference:
+ * (kind, chrom, inter, imprecise_pos) -- refinement.c:103,169,231,278.  chrom is 1-based (tid = chrom-1). */
+typedef struct {
+    int32_t n_win;
+    const int32_t *chrom;
+    const uint32_t *start; /* inter.start */
+    const uint32_t *end;   /* inter.end   */
+    const uint32_t *pos;   /* imprecise_pos */
+    const uint8_t *kind;   /* SVTK_DEL_START .. SVTK_POINT */
+} svtk_windows;
+
+/* Work counters of the last instrumented pass (svtk_measure_windows): the algorithmic bytes of SURVEY 8(d). */
+typedef struct {
+    uint64_t n_windows;
+    uint64_t n_pairs;          /* (window, read) pairs the reference's iterators would yield */
+    uint64_t n_words_visited;  /* CIGAR words the reference's walk loops touch */
+    uint64_t n_signatures;     /* positions pushed into the per-window arrays */
+    uint64_t n_overflow;       /* windows that left the shared-memory fast path */
+    uint64_t algorithmic_bytes;/* 4*words + 16*pairs + 4*signatures + 24*windows + 4*windows(result) */
+} svtk_stats;
+
+typedef struct svtk_ctx svtk_ctx;
+
+int svtk_version(void);
+const char *svtk_last_error(void);
+int svtk_device_count(void);
+
+/* lifetime.  `cuda_stream` may be NULL (the ctx creates its own non-blocking stream) or a cudaStream_t
+ * owned by the caller (so a harness can bracket launches with its own events). */
+svtk_ctx *svtk_create(int device, const svtk_params *params, void *cuda_stream);
+void svtk_destroy(svtk_ctx *ctx);
+int svtk_set_params(svtk_ctx *ctx, const svtk_params *params);
+int svtk_get_params(const svtk_ctx *ctx, svtk_params *params);
+
+/* reads: host SoA -> HBM (pinned staging, async copies on the ctx stream).  Replaces what
+ * hts_open/sam_index_load (audit.c:270-272) give the reference: access to every read of the BAM. */
+int svtk_load_reads(svtk_ctx *ctx, const svtk_reads *host_reads);
+/* adopt arrays that already live in device memory (pointers in *dev_reads are device pointers; tid_off is a
+ * HOST pointer).  The ctx does not take ownership.  Used when the packer itself runs on the GPU. */
+int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *dev_reads);
+
+/* ---- batch seam: N refine_* calls in one go.  result[i] == the reference's return value (-1 == NA). */
+/* host buffers in, host buffer out; H2D + kernels + D2H, synchronous */
+int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *host_windows, int32_t *host_result);
+/* device buffers in/out; asynchronous on the ctx stream (svtk_sync to wait) */
+int svtk_refine_windows_device(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result);
+/* same as svtk_refine_windows_device but with work counters; slower, for roofline accounting only */
+int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result, svtk_stats *stats);
+int svtk_sync(svtk_ctx *ctx);
+/* number of kernel launches this ctx has issued so far */
+uint64_t svtk_launch_count(const svtk_ctx *ctx);
+
+/* ---- per-record seam: same meaning as refinement.h:25,42,60 with `params` replaced by the ctx. */
+int svtk_deletion(svtk_ctx *ctx, int chrom, svtk_interval begin, svtk_interval end, svtk_interval sv_inter, svtk_interval *res_inter);
+int svtk_insertion(svtk_ctx *ctx, int chrom, svtk_interval begin, uint32_t pos, uint32_t *res_start);
+int svtk_inversion(svtk_ctx *ctx, int chrom, svtk_interval begin, svtk_interval end, svtk_interval sv_inter, svtk_interval *res_inter);
+
+/* ---- pieces of the path, exposed for parity tests against the reference's non-static functions */
+/* consensus_pos (refinement.c:41) on n_seg independent arrays: values[offsets[s] .. offsets[s+1]) with its own
+ * imprecise position pos[s]; min_count / interval / range come from the ctx params.  Runs on the device. */
+int svtk_consensus_pos_batch(svtk_ctx *ctx, const int32_t *values, const int64_t *offsets, int32_t n_seg,
+                             const int32_t *pos, int32_t *result);
+/* the raw signature multiset of one window (what the reference collects before quicksort, refinement.c:54),
+ * ascending.  *n_sig receives the full count even when it exceeds cap. */
+int svtk_window_signatures(svtk_ctx *ctx, int kind, int chrom, svtk_interval inter, int32_t *sig_out, int64_t cap, int64_t *n_sig);
+/* sliding_window_ins (sliding_window.c:8).  Per-tile "INS Discovery ..." lines (sliding_window.c:87) are
+ * written to lines_buf (NUL-terminated, truncated to cap) when it is non-NULL. */
+int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int window_size, int slide_size,
+                            int32_t *best, char *lines_buf, size_t cap);
+
+/* ---- whole path: process_vcf (audit.c:250).  Parses the VCF exactly like thread_func (audit.c:65-173),
+ * refines every record on the GPU and writes the reference's stdout lines in VCF order to out_path
+ * (NULL or "-" == stdout); the reference's stderr messages go to stderr.  Every record is processed (the
+ * reference's end-of-file tail drop, audit.c:35-41,342, is not reproduced).  *n_records (may be NULL)
+ * receives the number of (INS)/(DEL)/(INV) lines written. */
+int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTK_H */

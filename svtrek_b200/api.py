@@ -1,0 +1,237 @@
+"""ctypes mirror of include/svtk.h -- the host-side face of the B200 audt refinement path.
+
+Names follow the reference's own (refinement.h / audit.c): deletion, insertion, inversion, consensus_pos,
+sliding_window_ins, process_vcf.  Everything here calls into libsvtk_b200.so (hand-written sm_100a kernels);
+there is no Python or CPU fallback -- a missing library or a missing GPU raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsvtk_b200.so")
+
+DEL_START, DEL_END, INS, POINT = 0, 1, 2, 3
+DEFAULT_PARAMS = dict(wider_interval=20000, median_interval=10000, narrow_interval=2000,
+                      consensus_interval_range=500, consensus_interval=5, consensus_min_count=3)   # params.h:27-32
+
+
+class SvtkError(RuntimeError):
+    pass
+
+
+class Interval(C.Structure):
+    _fields_ = [("start", C.c_uint32), ("end", C.c_uint32)]
+
+
+class Params(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in DEFAULT_PARAMS]
+
+
+class Reads(C.Structure):
+    _fields_ = [("n_tid", C.c_int32), ("n_reads", C.c_int64), ("n_words", C.c_int64), ("tid_off", C.c_void_p),
+                ("pos", C.c_void_p), ("end", C.c_void_p), ("n_cigar", C.c_void_p), ("cigar_off", C.c_void_p), ("cigar", C.c_void_p)]
+
+
+class Windows(C.Structure):
+    _fields_ = [("n_win", C.c_int32), ("chrom", C.c_void_p), ("start", C.c_void_p), ("end", C.c_void_p), ("pos", C.c_void_p),
+                ("kind", C.c_void_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("n_windows", "n_pairs", "n_words_visited", "n_signatures", "n_overflow", "algorithmic_bytes")]
+
+
+EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
+           "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
+           "svtk_sync", "svtk_launch_count", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
+           "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf"]
+
+_lib = None
+
+
+def load_library():
+    """dlopen libsvtk_b200.so (built in-tree by svtrek_b200.build). Raises if it is missing: no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SvtkError(f"{LIB_PATH} is missing -- run `python -m svtrek_b200.build` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    L.svtk_last_error.restype = C.c_char_p
+    L.svtk_create.restype = C.c_void_p
+    L.svtk_create.argtypes = [C.c_int, C.POINTER(Params), C.c_void_p]
+    L.svtk_destroy.argtypes = [C.c_void_p]
+    L.svtk_set_params.argtypes = [C.c_void_p, C.POINTER(Params)]
+    L.svtk_get_params.argtypes = [C.c_void_p, C.POINTER(Params)]
+    L.svtk_load_reads.argtypes = [C.c_void_p, C.POINTER(Reads)]
+    L.svtk_attach_reads_device.argtypes = [C.c_void_p, C.POINTER(Reads)]
+    L.svtk_refine_windows.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p]
+    L.svtk_refine_windows_device.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p]
+    L.svtk_measure_windows.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p, C.POINTER(Stats)]
+    L.svtk_sync.argtypes = [C.c_void_p]
+    L.svtk_launch_count.argtypes = [C.c_void_p]
+    L.svtk_launch_count.restype = C.c_uint64
+    L.svtk_deletion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
+    L.svtk_insertion.argtypes = [C.c_void_p, C.c_int, Interval, C.c_uint32, C.POINTER(C.c_uint32)]
+    L.svtk_inversion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
+    L.svtk_consensus_pos_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.svtk_window_signatures.argtypes = [C.c_void_p, C.c_int, C.c_int, Interval, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+    L.svtk_sliding_window_ins.argtypes = [C.c_void_p, C.c_int, Interval, C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]
+    L.svtk_process_vcf.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise SvtkError(f"svtk error {rc}: {load_library().svtk_last_error().decode()}")
+
+
+def _u32(a):
+    return np.ascontiguousarray(np.asarray(a).astype(np.int64) & 0xFFFFFFFF, dtype=np.uint32)
+
+
+class Auditor:
+    """One GPU's refinement context (svtk_ctx): holds the decoded reads in HBM and runs batches of windows.
+
+    Plays the role of one reference worker's t_arg (params.h:81-95): the tunables plus access to the reads."""
+
+    def __init__(self, device=0, params=None, cuda_stream=None):
+        self.lib = load_library()
+        p = dict(DEFAULT_PARAMS); p.update(params or {})
+        self._params = Params(**p)
+        self.ctx = self.lib.svtk_create(int(device), C.byref(self._params), C.c_void_p(cuda_stream) if cuda_stream else None)
+        if not self.ctx:
+            raise SvtkError(f"svtk_create failed: {self.lib.svtk_last_error().decode()}")
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.svtk_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- tunables (audt_args, params.h:57-62)
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if k not in DEFAULT_PARAMS:
+                raise KeyError(k)
+            setattr(self._params, k, int(v))
+        _check(self.lib.svtk_set_params(self.ctx, C.byref(self._params)))
+
+    @property
+    def params(self):
+        return {k: getattr(self._params, k) for k in DEFAULT_PARAMS}
+
+    # ---- reads
+    def load_reads(self, rs):
+        """Upload a host SoA read set (anything with tid_off/pos/end/n_cigar/cigar_off/cigar numpy arrays)."""
+        arrs = [np.ascontiguousarray(rs.tid_off, dtype=np.int64), np.ascontiguousarray(rs.pos, dtype=np.uint32),
+                np.ascontiguousarray(rs.end, dtype=np.uint32), np.ascontiguousarray(rs.n_cigar, dtype=np.uint32),
+                np.ascontiguousarray(rs.cigar_off, dtype=np.uint64), np.ascontiguousarray(rs.cigar, dtype=np.uint32)]
+        r = Reads(int(arrs[0].shape[0] - 1), int(arrs[1].shape[0]), int(arrs[5].shape[0]), *[a.ctypes.data for a in arrs])
+        _check(self.lib.svtk_load_reads(self.ctx, C.byref(r)))
+
+    def attach_reads_device(self, tid_off, pos_ptr, end_ptr, n_cigar_ptr, cigar_off_ptr, cigar_ptr, n_reads, n_words):
+        """Adopt device-resident arrays (raw device pointers, e.g. torch tensor .data_ptr()); tid_off is a host array."""
+        t = np.ascontiguousarray(tid_off, dtype=np.int64)
+        r = Reads(int(t.shape[0] - 1), int(n_reads), int(n_words), t.ctypes.data, pos_ptr, end_ptr, n_cigar_ptr, cigar_off_ptr, cigar_ptr)
+        _check(self.lib.svtk_attach_reads_device(self.ctx, C.byref(r)))
+
+    # ---- batch seam
+    def refine_windows(self, chrom, start, end, pos, kind):
+        """N refine_start/refine_end/refine_ins/refine_point calls; host arrays in, int32 results out (-1 == NA)."""
+        chrom = np.ascontiguousarray(chrom, dtype=np.int32)
+        start, end, pos = _u32(start), _u32(end), _u32(pos)
+        kind = np.ascontiguousarray(kind, dtype=np.uint8)
+        n = int(chrom.shape[0])
+        out = np.empty(n, dtype=np.int32)
+        w = Windows(n, chrom.ctypes.data, start.ctypes.data, end.ctypes.data, pos.ctypes.data, kind.ctypes.data)
+        _check(self.lib.svtk_refine_windows(self.ctx, C.byref(w), out.ctypes.data))
+        return out
+
+    def refine_windows_device(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
+        w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
+        _check(self.lib.svtk_refine_windows_device(self.ctx, C.byref(w), result_ptr))
+
+    def measure_windows(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
+        w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
+        st = Stats()
+        _check(self.lib.svtk_measure_windows(self.ctx, C.byref(w), result_ptr, C.byref(st)))
+        return {k: int(getattr(st, k)) for k, _ in Stats._fields_}
+
+    def sync(self):
+        _check(self.lib.svtk_sync(self.ctx))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.svtk_launch_count(self.ctx))
+
+    # ---- per-record seam (refinement.h:25,42,60)
+    def deletion(self, chrom, begin, end, sv_inter):
+        res = Interval()
+        _check(self.lib.svtk_deletion(self.ctx, int(chrom), Interval(*[x & 0xFFFFFFFF for x in begin]), Interval(*[x & 0xFFFFFFFF for x in end]),
+                                      Interval(*[x & 0xFFFFFFFF for x in sv_inter]), C.byref(res)))
+        return res.start, res.end
+
+    def insertion(self, chrom, begin, pos):
+        res = C.c_uint32()
+        _check(self.lib.svtk_insertion(self.ctx, int(chrom), Interval(*[x & 0xFFFFFFFF for x in begin]), pos & 0xFFFFFFFF, C.byref(res)))
+        return res.value
+
+    def inversion(self, chrom, begin, end, sv_inter):
+        res = Interval()
+        _check(self.lib.svtk_inversion(self.ctx, int(chrom), Interval(*[x & 0xFFFFFFFF for x in begin]), Interval(*[x & 0xFFFFFFFF for x in end]),
+                                       Interval(*[x & 0xFFFFFFFF for x in sv_inter]), C.byref(res)))
+        return res.start, res.end
+
+    # ---- pieces (parity aids)
+    def consensus_pos_batch(self, values, offsets, pos):
+        values = np.ascontiguousarray(values, dtype=np.int32)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        pos = np.ascontiguousarray(pos, dtype=np.int32)
+        n = int(pos.shape[0])
+        out = np.empty(n, dtype=np.int32)
+        _check(self.lib.svtk_consensus_pos_batch(self.ctx, values.ctypes.data, offsets.ctypes.data, n, pos.ctypes.data, out.ctypes.data))
+        return out
+
+    def consensus_pos(self, locations, pos):
+        """consensus_pos(locations, size, pos, ...) of refinement.c:41 with the ctx's min-count/interval/range."""
+        v = np.ascontiguousarray(locations, dtype=np.int32)
+        return int(self.consensus_pos_batch(v, [0, v.shape[0]], [pos])[0])
+
+    def window_signatures(self, kind, chrom, start, end, cap=1 << 16):
+        buf = np.empty(cap, dtype=np.int32)
+        n = C.c_int64(0)
+        _check(self.lib.svtk_window_signatures(self.ctx, int(kind), int(chrom), Interval(start & 0xFFFFFFFF, end & 0xFFFFFFFF), buf.ctypes.data, cap, C.byref(n)))
+        if n.value > cap:
+            return self.window_signatures(kind, chrom, start, end, cap=int(n.value))
+        return buf[:n.value].copy()
+
+    def sliding_window_ins(self, chrom, start, end, window_size, slide_size, want_lines=False):
+        best = C.c_int32(-1)
+        cap = 1 << 22
+        buf = C.create_string_buffer(cap) if want_lines else None
+        _check(self.lib.svtk_sliding_window_ins(self.ctx, int(chrom), Interval(start & 0xFFFFFFFF, end & 0xFFFFFFFF), int(window_size), int(slide_size),
+                                                C.byref(best), buf, cap if want_lines else 0))
+        return (best.value, buf.value.decode()) if want_lines else best.value
+
+    # ---- whole path (audit.c:250 process_vcf)
+    def process_vcf(self, vcf_path, out_path):
+        n = C.c_int64(0)
+        _check(self.lib.svtk_process_vcf(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, C.byref(n)))
+        return n.value

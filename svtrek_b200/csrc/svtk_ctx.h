@@ -1,0 +1,63 @@
+// svtk_ctx.h -- the context behind svtk_ctx*: one GPU, one stream, the resident read set and reusable buffers.
+#pragma once
+#include "../../include/svtk.h"
+#include "svtk_launch.h"
+
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+namespace svtk {
+
+int fail(int code, const char *fmt, ...);
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);   // grow-only; contents are NOT preserved
+    void release();
+};
+
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);
+    void release();
+};
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    svtk_params params{};
+
+    // resident read set (HBM).  r_* own the memory when loaded from the host; attach leaves them empty.
+    bool have_reads = false;
+    LaunchReads reads{};
+    std::vector<int64_t> h_tid_off;
+    DevBuf r_tid_off, r_pos, r_end, r_ncig, r_off, r_cigar;
+
+    // per-batch scratch
+    DevBuf range;        // int2 per window: candidate read range
+    DevBuf ov_items;     // int2 per window: (window, signature count) of fast-path overflows
+    DevBuf ov_count;     // [0] overflow count, [1] fail flag, [2..3] arena top
+    DevBuf arena;        // global signature segments for windows beyond the big shared segment
+    DevBuf counters;     // WorkCounters
+    DevBuf scratch4;
+    DevBuf win_blob, result;       // device copies for the host-buffer API
+    DevBuf tmp_a, tmp_b, tmp_c;
+    PinBuf stage[2];
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
+    PinBuf h_flags, h_win, h_result;
+
+    // a launched batch whose overflow windows have not been resolved yet
+    bool pending = false;
+    LaunchWindows pend_win{};
+    int32_t *pend_result = nullptr;
+    int last_overflow = 0;
+
+    uint64_t launches = 0;
+    uint64_t h2d_bytes = 0, d2h_bytes = 0;
+};
+
+}  // namespace svtk

@@ -1,0 +1,45 @@
+// svtk_launch.h -- host-side launch interface between the C ABI (svtk_capi.cpp) and the kernels (svtk_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace svtk {
+
+struct LaunchReads {            // device pointers
+    int n_tid;
+    long long n_reads;
+    const long long *tid_off;
+    const uint32_t *pos, *end, *n_cigar;
+    const unsigned long long *cigar_off;
+    const uint32_t *cigar;
+    uint32_t max_span;
+};
+
+struct LaunchWindows {          // device pointers
+    int n_win;
+    const int32_t *chrom;
+    const uint32_t *start, *end, *pos;
+    const uint8_t *kind;
+};
+
+int big_segment_ints();
+int consensus_segment_smem_ints();
+
+cudaError_t launch_max_span(const uint32_t *pos, const uint32_t *end, long long n, uint32_t *out, cudaStream_t s);
+cudaError_t launch_plan(const LaunchReads &r, const LaunchWindows &w, int2 *range, cudaStream_t s);
+cudaError_t launch_refine_fused(const LaunchReads &r, const LaunchWindows &w, const int2 *range, int range_, int interval,
+                                int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity,
+                                unsigned long long *counters, cudaStream_t s);
+cudaError_t launch_refine_overflow(const LaunchReads &r, const LaunchWindows &w, const int2 *range, int range_, int interval,
+                                   int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
+                                   int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag,
+                                   cudaStream_t s);
+cudaError_t launch_consensus_segments(const int32_t *values, const long long *offsets, const int32_t *pos, int n_seg, int range_,
+                                      int interval, int min_count, int *scratch, const long long *scratch_off, int32_t *result,
+                                      cudaStream_t s);
+cudaError_t launch_slide_tiles(const LaunchReads &r, const LaunchWindows &w, const int2 *range, int window_size, int slide,
+                               int min_count, int *gseg, long long gseg_stride, int2 *out, int *need, cudaStream_t s);
+cudaError_t launch_window_signatures(const LaunchReads &r, const LaunchWindows &w, const int2 *range, int *buf, int cap, int *n_out,
+                                     cudaStream_t s);
+
+}  // namespace svtk

@@ -373,3 +373,33 @@ def write_sam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr", random_se
                 flag = 0 if flags is None else int(flags[r])
                 f.write(f"r{r}\t{flag}\t{chr_prefix}{t + 1}\t{int(rs.pos[r]) + 1}\t60\t{cigar_string(w)}\t*\t0\t0\t".encode())
                 f.write(seq + b"\t" + qual + b"\n")
+
+
+def windows_from_truth(truth: SVTruth, seed=1, *, pos_noise=40, wider=20000, median=10000, narrow=2000):
+    """The refine_* windows the reference builds for vcf_lines(truth, seed, end_first=True) (audit.c:178,191-193),
+    as SoA arrays: INS -> one SVTK_INS window, DEL -> SVTK_DEL_START + SVTK_DEL_END.  Same noise draws as vcf_lines.
+    Returns dict(chrom,start,end,pos,kind) plus `record` (index of the SV each window belongs to)."""
+    rng = np.random.default_rng(seed)
+    n = truth.pos0.shape[0]
+    noise = rng.integers(-pos_noise, pos_noise + 1, n)
+    noise_e = rng.integers(-pos_noise, pos_noise + 1, n)
+    pos = (truth.pos0 + noise).astype(np.int64)
+    end = np.where(truth.is_del, truth.pos0 + truth.length + noise_e, pos + 1).astype(np.int64)
+    chrom = truth.tid.astype(np.int64) + 1
+    is_del = truth.is_del & (end - pos > 50)
+    nwin = np.where(truth.is_del, np.where(is_del, 2, 0), 1)
+    first = np.cumsum(nwin) - nwin
+    tot = int(nwin.sum())
+    w_chrom = np.zeros(tot, np.int32); w_start = np.zeros(tot, np.int64); w_end = np.zeros(tot, np.int64)
+    w_pos = np.zeros(tot, np.int64); w_kind = np.zeros(tot, np.uint8); w_rec = np.zeros(tot, np.int64)
+    ins = ~truth.is_del
+    i = first[ins]
+    w_chrom[i] = chrom[ins]; w_start[i] = pos[ins] - median; w_end[i] = pos[ins] + median; w_pos[i] = pos[ins]; w_kind[i] = 2; w_rec[i] = np.flatnonzero(ins)
+    d = first[is_del]
+    w_chrom[d] = chrom[is_del]; w_start[d] = pos[is_del] - wider; w_end[d] = pos[is_del] + narrow; w_pos[d] = pos[is_del]; w_kind[d] = 0
+    w_rec[d] = np.flatnonzero(is_del)
+    w_chrom[d + 1] = chrom[is_del]; w_start[d + 1] = end[is_del] - narrow; w_end[d + 1] = end[is_del] + narrow; w_pos[d + 1] = end[is_del]
+    w_kind[d + 1] = 1; w_rec[d + 1] = np.flatnonzero(is_del)
+    m = 0xFFFFFFFF
+    return dict(chrom=w_chrom, start=(w_start & m).astype(np.uint32), end=(w_end & m).astype(np.uint32),
+                pos=(w_pos & m).astype(np.uint32), kind=w_kind, record=w_rec)

@@ -101,6 +101,14 @@ typedef struct {
     uint64_t algorithmic_bytes;/* 4*words + 16*pairs + 4*signatures + 24*windows + 4*windows(result) */
 } svtk_stats;
 
+/* Live timing of the dominant kernel (the fused CIGAR-walk + consensus kernel), taken with CUDA events on the
+ * ctx stream while svtk_set_profiling(ctx, 1) is in force; plus the bytes the host-buffer entry points moved. */
+typedef struct {
+    double refine_kernel_ms;          /* sum of launch durations since profiling was switched on */
+    uint64_t refine_kernel_launches;
+    uint64_t h2d_bytes, d2h_bytes;    /* since svtk_create */
+} svtk_timing;
+
 typedef struct svtk_ctx svtk_ctx;
 
 int svtk_version(void);
@@ -131,6 +139,10 @@ int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t
 int svtk_sync(svtk_ctx *ctx);
 /* number of kernel launches this ctx has issued so far */
 uint64_t svtk_launch_count(const svtk_ctx *ctx);
+/* bracket every fused refinement kernel with CUDA events (on = 1) and read the running totals; switching
+ * profiling on or off resets them.  No reference counterpart: measurement aid for bench.py's roofline. */
+int svtk_set_profiling(svtk_ctx *ctx, int on);
+int svtk_get_timing(svtk_ctx *ctx, svtk_timing *timing);
 
 /* ---- per-record seam: same meaning as refinement.h:25,42,60 with `params` replaced by the ctx. */
 int svtk_deletion(svtk_ctx *ctx, int chrom, svtk_interval begin, svtk_interval end, svtk_interval sv_inter, svtk_interval *res_inter);

@@ -44,9 +44,14 @@ class Stats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("n_windows", "n_pairs", "n_words_visited", "n_signatures", "n_overflow", "algorithmic_bytes")]
 
 
+class Timing(C.Structure):
+    _fields_ = [("refine_kernel_ms", C.c_double), ("refine_kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64),
+                ("d2h_bytes", C.c_uint64)]
+
+
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
-           "svtk_sync", "svtk_launch_count", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
+           "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf"]
 
 _lib = None
@@ -74,6 +79,8 @@ def load_library():
     L.svtk_sync.argtypes = [C.c_void_p]
     L.svtk_launch_count.argtypes = [C.c_void_p]
     L.svtk_launch_count.restype = C.c_uint64
+    L.svtk_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    L.svtk_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
     L.svtk_deletion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
     L.svtk_insertion.argtypes = [C.c_void_p, C.c_int, Interval, C.c_uint32, C.POINTER(C.c_uint32)]
     L.svtk_inversion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
@@ -180,6 +187,24 @@ class Auditor:
     @property
     def launch_count(self):
         return int(self.lib.svtk_launch_count(self.ctx))
+
+    def set_profiling(self, on=True):
+        _check(self.lib.svtk_set_profiling(self.ctx, 1 if on else 0))
+
+    def timing(self):
+        t = Timing()
+        _check(self.lib.svtk_get_timing(self.ctx, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timing._fields_}
+
+    def load_reads_ptr(self, n_tid, n_reads, n_words, tid_off_ptr, pos_ptr, end_ptr, n_cigar_ptr, cigar_off_ptr, cigar_ptr):
+        """svtk_load_reads on raw HOST pointers (e.g. pinned torch tensors): no numpy conversion on the timed path."""
+        r = Reads(int(n_tid), int(n_reads), int(n_words), tid_off_ptr, pos_ptr, end_ptr, n_cigar_ptr, cigar_off_ptr, cigar_ptr)
+        _check(self.lib.svtk_load_reads(self.ctx, C.byref(r)))
+
+    def refine_windows_ptr(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
+        """svtk_refine_windows on raw HOST pointers."""
+        w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
+        _check(self.lib.svtk_refine_windows(self.ctx, C.byref(w), result_ptr))
 
     # ---- per-record seam (refinement.h:25,42,60)
     def deletion(self, chrom, begin, end, sv_inter):

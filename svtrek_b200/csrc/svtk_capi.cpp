@@ -59,6 +59,14 @@ void PinBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 // host (pageable) -> device through two pinned staging buffers so the CPU copy of chunk k+1 overlaps the DMA of chunk k
 static int upload(Ctx *c, void *dst, const void *src, size_t bytes) {
     if (bytes == 0) return 0;
+    {   // caller's buffer already page-locked (cudaHostAlloc / cudaHostRegister): DMA straight from it
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+            CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
+            return 0;
+        }
+        cudaGetLastError();
+    }
     const size_t CH = 32u << 20;
     for (int i = 0; i < 2; ++i) {
         if (int rc = c->stage[i].reserve(std::min(bytes, CH))) return rc;
@@ -105,6 +113,18 @@ static int ensure_batch(Ctx *c, int n_win) {
     return 0;
 }
 
+// fold the event pair of the previous profiled batch into the running totals (waits for that batch's kernel)
+static int collect_timing(Ctx *c) {
+    if (!c->prof_pending) return 0;
+    c->prof_pending = false;
+    CU(cudaEventSynchronize(c->prof_ev[1]));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->prof_ev[0], c->prof_ev[1]));
+    c->fused_ms += (double)ms;
+    c->fused_launches += 1;
+    return 0;
+}
+
 static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, bool stats) {
     if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded (svtk_load_reads / svtk_attach_reads_device)");
     if (int rc = set_device(c)) return rc;
@@ -119,9 +139,17 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, boo
         counters = (unsigned long long *)c->counters.p;
     }
     CU(launch_plan(c->reads, w, (int2 *)c->range.p, c->stream));
+    if (c->profile) {
+        if (int rc = collect_timing(c)) return rc;
+        CU(cudaEventRecord(c->prof_ev[0], c->stream));
+    }
     CU(launch_refine_fused(c->reads, w, (const int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
                            c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
                            c->stream));
+    if (c->profile) {
+        CU(cudaEventRecord(c->prof_ev[1], c->stream));
+        c->prof_pending = true;
+    }
     c->launches += 2;
     CU(cudaMemcpyAsync(c->h_flags.p, c->ov_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     c->pending = true;
@@ -207,6 +235,7 @@ void svtk_destroy(svtk_ctx *ctx) {
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_win, &c->h_result}) b->release();
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
+    for (int i = 0; i < 2; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -297,6 +326,32 @@ int svtk_sync(svtk_ctx *ctx) {
 }
 
 uint64_t svtk_launch_count(const svtk_ctx *ctx) { return ctx ? reinterpret_cast<const Ctx *>(ctx)->launches : 0; }
+
+int svtk_set_profiling(svtk_ctx *ctx, int on) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail(SVTK_ERR_ARG, "null ctx");
+    if (int rc = set_device(c)) return rc;
+    if (on && !c->prof_ev[0]) {
+        CU(cudaEventCreate(&c->prof_ev[0]));
+        CU(cudaEventCreate(&c->prof_ev[1]));
+    }
+    if (int rc = collect_timing(c)) return rc;
+    c->profile = on != 0;
+    c->fused_ms = 0.0; c->fused_launches = 0;
+    return 0;
+}
+
+int svtk_get_timing(svtk_ctx *ctx, svtk_timing *t) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !t) return fail(SVTK_ERR_ARG, "null argument");
+    if (int rc = set_device(c)) return rc;
+    if (int rc = collect_timing(c)) return rc;
+    t->refine_kernel_ms = c->fused_ms;
+    t->refine_kernel_launches = c->fused_launches;
+    t->h2d_bytes = c->h2d_bytes;
+    t->d2h_bytes = c->d2h_bytes;
+    return 0;
+}
 
 int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *w, int32_t *dev_result, svtk_stats *st) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);

@@ -58,6 +58,12 @@ struct Ctx {
 
     uint64_t launches = 0;
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
+
+    // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
+    bool profile = false, prof_pending = false;
+    cudaEvent_t prof_ev[2] = {nullptr, nullptr};
+    double fused_ms = 0.0;
+    uint64_t fused_launches = 0;
 };
 
 }  // namespace svtk

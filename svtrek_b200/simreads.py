@@ -137,8 +137,10 @@ def gen_contig(rng, contig_len, n_reads, read_len, small_rate, sv_pos0, sv_len, 
             e[r[left_part]] = bp[cand[left_part]]
             trail[r[left_part]] = cl[left_part]
             nb = np.where(isd[cand[~left_part]], bp[cand[~left_part]] + ln[cand[~left_part]], bp[cand[~left_part]])
-            s[r[~left_part]] = nb
-            lead[r[~left_part]] = cl[~left_part]
+            rb, clb = r[~left_part], cl[~left_part]
+            fits = nb <= e[rb] - 50                          # a deletion reaching past the read end cannot be a B split
+            s[rb[fits]] = nb[fits]
+            lead[rb[fits]] = clb[fits]
         ev_rid = [rid_sv]
         ev_pos = [bp]
         ev_op = [np.where(isd, OP_D, OP_I)]

@@ -76,7 +76,8 @@ typedef struct {
     const uint32_t *pos;       /* [n_reads] bam1_core_t.pos, 0-based */
     const uint32_t *end;       /* [n_reads] */
     const uint32_t *n_cigar;   /* [n_reads] */
-    const uint64_t *cigar_off; /* [n_reads] word offset of each read's CIGAR inside `cigar` */
+    const uint64_t *cigar_off; /* [n_reads] word offset of each read's CIGAR inside `cigar`; CIGARs are packed back to
+                                  back in read order: cigar_off[0] == 0, cigar_off[r] + n_cigar[r] == cigar_off[r+1] */
     const uint32_t *cigar;     /* [n_words] */
 } svtk_reads;
 
@@ -104,10 +105,23 @@ typedef struct {
 /* Live timing of the dominant kernel (the fused CIGAR-walk + consensus kernel), taken with CUDA events on the
  * ctx stream while svtk_set_profiling(ctx, 1) is in force; plus the bytes the host-buffer entry points moved. */
 typedef struct {
-    double refine_kernel_ms;          /* sum of launch durations since profiling was switched on */
+    double refine_kernel_ms;          /* per-window kernel: sum of launch durations since profiling was switched on */
     uint64_t refine_kernel_launches;
+    double index_kernel_ms;           /* per-read CIGAR pass (signature index) */
+    uint64_t index_kernel_launches;
     uint64_t h2d_bytes, d2h_bytes;    /* since svtk_create */
 } svtk_timing;
+
+/* Work counters of the product path (svtk_measure_index): the bytes each of its two kernels has to move. */
+typedef struct {
+    uint64_t n_reads, n_words, n_chunks;   /* the resident read set; chunks of 32 reads */
+    uint64_t n_events, n_segments;         /* signature events (D > 50, I >= 50, soft clips) the index holds */
+    uint64_t index_bytes;                  /* one index pass: 4*n_words + 24*n_reads + 16*n_events + 16*n_chunks */
+    uint64_t n_windows;
+    uint64_t refine_events_scanned, refine_segments, refine_reads_in_range;
+    uint64_t n_signatures, n_overflow;
+    uint64_t refine_bytes;                 /* one refine pass: 16*events scanned + 16*segments + 28*n_windows */
+} svtk_index_stats;
 
 typedef struct svtk_ctx svtk_ctx;
 
@@ -134,7 +148,8 @@ int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *dev_reads);
 int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *host_windows, int32_t *host_result);
 /* device buffers in/out; asynchronous on the ctx stream (svtk_sync to wait) */
 int svtk_refine_windows_device(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result);
-/* same as svtk_refine_windows_device but with work counters; slower, for roofline accounting only */
+/* same results through the reference-shaped walker (one CIGAR walk per (window, read) pair, like refinement.c) with
+ * the work counters of SURVEY 8(d); slower -- an independent cross-check and the reference-equivalent byte count */
 int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result, svtk_stats *stats);
 int svtk_sync(svtk_ctx *ctx);
 /* number of kernel launches this ctx has issued so far */
@@ -143,6 +158,12 @@ uint64_t svtk_launch_count(const svtk_ctx *ctx);
  * profiling on or off resets them.  No reference counterpart: measurement aid for bench.py's roofline. */
 int svtk_set_profiling(svtk_ctx *ctx, int on);
 int svtk_get_timing(svtk_ctx *ctx, svtk_timing *timing);
+/* The product path walks every CIGAR once (the "signature index": one coalesced pass over the resident reads) and
+ * then answers each window from the events it found.  The first svtk_refine_* call after svtk_load_reads builds the
+ * index; svtk_index_reads rebuilds it explicitly (asynchronous, ctx stream) -- bench.py calls it every step so that a
+ * timed step always contains the whole job.  svtk_measure_index: rebuild + refine with work counters. */
+int svtk_index_reads(svtk_ctx *ctx);
+int svtk_measure_index(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result, svtk_index_stats *stats);
 
 /* ---- per-record seam: same meaning as refinement.h:25,42,60 with `params` replaced by the ctx. */
 int svtk_deletion(svtk_ctx *ctx, int chrom, svtk_interval begin, svtk_interval end, svtk_interval sv_inter, svtk_interval *res_inter);

@@ -45,13 +45,19 @@ class Stats(C.Structure):
 
 
 class Timing(C.Structure):
-    _fields_ = [("refine_kernel_ms", C.c_double), ("refine_kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64),
-                ("d2h_bytes", C.c_uint64)]
+    _fields_ = [("refine_kernel_ms", C.c_double), ("refine_kernel_launches", C.c_uint64), ("index_kernel_ms", C.c_double),
+                ("index_kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+
+
+class IndexStats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("n_reads", "n_words", "n_chunks", "n_events", "n_segments", "index_bytes", "n_windows",
+                                          "refine_events_scanned", "refine_segments", "refine_reads_in_range", "n_signatures",
+                                          "n_overflow", "refine_bytes")]
 
 
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
-           "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
+           "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf"]
 
 _lib = None
@@ -81,6 +87,8 @@ def load_library():
     L.svtk_launch_count.restype = C.c_uint64
     L.svtk_set_profiling.argtypes = [C.c_void_p, C.c_int]
     L.svtk_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+    L.svtk_index_reads.argtypes = [C.c_void_p]
+    L.svtk_measure_index.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p, C.POINTER(IndexStats)]
     L.svtk_deletion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
     L.svtk_insertion.argtypes = [C.c_void_p, C.c_int, Interval, C.c_uint32, C.POINTER(C.c_uint32)]
     L.svtk_inversion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
@@ -180,6 +188,16 @@ class Auditor:
         st = Stats()
         _check(self.lib.svtk_measure_windows(self.ctx, C.byref(w), result_ptr, C.byref(st)))
         return {k: int(getattr(st, k)) for k, _ in Stats._fields_}
+
+    def measure_index(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
+        w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
+        st = IndexStats()
+        _check(self.lib.svtk_measure_index(self.ctx, C.byref(w), result_ptr, C.byref(st)))
+        return {k: int(getattr(st, k)) for k, _ in IndexStats._fields_}
+
+    def index_reads(self):
+        """(Re)build the signature index of the resident reads (one pass over every CIGAR word), asynchronously."""
+        _check(self.lib.svtk_index_reads(self.ctx))
 
     def sync(self):
         _check(self.lib.svtk_sync(self.ctx))

@@ -92,16 +92,72 @@ static int set_device(Ctx *c) {
 }
 
 static int finish_reads(Ctx *c) {
-    // planner look-back bound: max(end - pos) over the read set
+    // planner look-back bound: max(end - pos) over the read set; and the packed-CIGAR contract of svtk_reads
     if (int rc = c->scratch4.reserve(64)) return rc;
-    CU(cudaMemsetAsync(c->scratch4.p, 0, 4, c->stream));
+    CU(cudaMemsetAsync(c->scratch4.p, 0, 8, c->stream));
     CU(launch_max_span(c->reads.pos, c->reads.end, c->reads.n_reads, (uint32_t *)c->scratch4.p, c->stream));
-    c->launches += c->reads.n_reads > 0;
-    uint32_t ms = 1;
-    CU(cudaMemcpyAsync(&ms, c->scratch4.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(launch_check_layout(c->reads, (unsigned long long)c->n_words, (unsigned int *)c->scratch4.p + 1, c->stream));
+    c->launches += 2 * (c->reads.n_reads > 0);
+    uint32_t ms[2] = {1, 0};
+    CU(cudaMemcpyAsync(ms, c->scratch4.p, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    c->reads.max_span = std::max(ms, 1u);
+    if (ms[1]) return fail(SVTK_ERR_ARG, "svtk_reads: CIGARs must be packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1], cigar_off[0] == 0, last end == n_words)");
+    c->reads.max_span = std::max(ms[0], 1u);
     c->have_reads = true;
+    c->index_valid = false;
+    return 0;
+}
+
+// ---- signature index (svtk_index.cu)
+static int ensure_index_buffers(Ctx *c, uint64_t ev_cap, uint64_t seg_cap) {
+    const long long nr = c->reads.n_reads;
+    const int per = index_reads_per_chunk();
+    const long long n_chunks = (nr + per - 1) / per;
+    if (ev_cap >= (1ull << 31) || seg_cap >= (1ull << 31)) return fail(SVTK_ERR_ARG, "signature index beyond 2^31 events: shard the read set");
+    if (int rc = c->idx_events.reserve(16 * (size_t)ev_cap)) return rc;
+    if (int rc = c->idx_chunks.reserve(16 * (size_t)std::max(n_chunks, 1ll))) return rc;
+    if (int rc = c->idx_segs.reserve(16 * (size_t)seg_cap)) return rc;
+    if (int rc = c->idx_rend.reserve(4 * (size_t)std::max(nr, 1ll))) return rc;
+    if (int rc = c->idx_ctrl.reserve(64)) return rc;
+    c->idx = LaunchIndex{c->idx_events.p, c->idx_chunks.p, c->idx_segs.p, (uint32_t *)c->idx_rend.p, (unsigned int *)c->idx_ctrl.p,
+                         (unsigned int)ev_cap, (unsigned int)seg_cap, (int)n_chunks};
+    return 0;
+}
+
+// fold the event pairs of the previous profiled batch into the running totals (waits for that batch's kernels)
+static int collect_timing(Ctx *c) {
+    if (c->prof_pending) {
+        c->prof_pending = false;
+        CU(cudaEventSynchronize(c->prof_ev[1]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->prof_ev[0], c->prof_ev[1]));
+        c->refine_ms += (double)ms;
+        c->refine_launches += 1;
+    }
+    if (c->prof_idx_pending) {
+        c->prof_idx_pending = false;
+        CU(cudaEventSynchronize(c->prof_ev[3]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->prof_ev[2], c->prof_ev[3]));
+        c->index_ms += (double)ms;
+        c->index_launches += 1;
+    }
+    return 0;
+}
+
+static int build_index(Ctx *c) {
+    if (c->idx.ev_cap == 0 || c->idx.n_chunks != (int)((c->reads.n_reads + index_reads_per_chunk() - 1) / index_reads_per_chunk())) {
+        // first guess: one event per 16 CIGAR words plus both clip events of every read; grown on demand (resolve)
+        const uint64_t ev = (uint64_t)c->n_words / 16 + 2 * (uint64_t)c->reads.n_reads + 4096;
+        if (int rc = ensure_index_buffers(c, std::max<uint64_t>(ev, c->idx.ev_cap), std::max<uint64_t>(ev / 256 + 1024, c->idx.seg_cap))) return rc;
+    }
+    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, 16, c->stream));
+    if (c->profile) { if (int rc = collect_timing(c)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
+    CU(launch_index_reads(c->reads, c->idx, c->stream));
+    if (c->profile) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
+    c->launches += c->reads.n_reads > 0;
+    c->index_valid = true;
+    c->index_fresh = true;
     return 0;
 }
 
@@ -109,23 +165,13 @@ static int ensure_batch(Ctx *c, int n_win) {
     if (int rc = c->range.reserve((size_t)n_win * sizeof(int2))) return rc;
     if (int rc = c->ov_items.reserve((size_t)n_win * sizeof(int2))) return rc;
     if (int rc = c->ov_count.reserve(64)) return rc;      // [0] overflow count  [1] fail flag  [2..3] arena top (u64)
-    if (int rc = c->h_flags.reserve(64)) return rc;
+    if (int rc = c->h_flags.reserve(64)) return rc;       // [0] overflow count  [1] fail flag  [4..7] index ctrl
     return 0;
 }
 
-// fold the event pair of the previous profiled batch into the running totals (waits for that batch's kernel)
-static int collect_timing(Ctx *c) {
-    if (!c->prof_pending) return 0;
-    c->prof_pending = false;
-    CU(cudaEventSynchronize(c->prof_ev[1]));
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, c->prof_ev[0], c->prof_ev[1]));
-    c->fused_ms += (double)ms;
-    c->fused_launches += 1;
-    return 0;
-}
+enum { MODE_INDEXED = 0, MODE_WALKER_STATS = 1, MODE_INDEXED_STATS = 2 };
 
-static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, bool stats) {
+static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int mode) {
     if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded (svtk_load_reads / svtk_attach_reads_device)");
     if (int rc = set_device(c)) return rc;
     if (int rc = ensure_batch(c, std::max(w.n_win, 1))) return rc;
@@ -133,35 +179,67 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, boo
     if (w.n_win <= 0) return 0;
     CU(cudaMemsetAsync(c->ov_count.p, 0, 64, c->stream));
     unsigned long long *counters = nullptr;
-    if (stats) {
+    if (mode != MODE_INDEXED) {
         if (int rc = c->counters.reserve(64)) return rc;
         CU(cudaMemsetAsync(c->counters.p, 0, 64, c->stream));
         counters = (unsigned long long *)c->counters.p;
     }
-    CU(launch_plan(c->reads, w, (int2 *)c->range.p, c->stream));
-    if (c->profile) {
-        if (int rc = collect_timing(c)) return rc;
-        CU(cudaEventRecord(c->prof_ev[0], c->stream));
+    if (mode == MODE_WALKER_STATS) {
+        // the reference-shaped walker (one CIGAR walk per (window, read) pair): instrumented cross-check
+        CU(launch_plan(c->reads, w, (int2 *)c->range.p, c->stream));
+        CU(launch_refine_fused(c->reads, w, (const int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
+                               c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
+                               c->stream));
+        c->launches += 2;
+    } else {
+        if (!c->index_valid) if (int rc = build_index(c)) return rc;
+        if (c->profile) {
+            if (int rc = collect_timing(c)) return rc;
+            CU(cudaEventRecord(c->prof_ev[0], c->stream));
+        }
+        CU(launch_refine_indexed(c->reads, w, c->idx, (int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
+                                 c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
+                                 c->stream));
+        if (c->profile) {
+            CU(cudaEventRecord(c->prof_ev[1], c->stream));
+            c->prof_pending = true;
+        }
+        c->launches += 1;
+        if (c->index_fresh) CU(cudaMemcpyAsync((int *)c->h_flags.p + 4, c->idx_ctrl.p, 12, cudaMemcpyDeviceToHost, c->stream));
     }
-    CU(launch_refine_fused(c->reads, w, (const int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
-                           c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
-                           c->stream));
-    if (c->profile) {
-        CU(cudaEventRecord(c->prof_ev[1], c->stream));
-        c->prof_pending = true;
-    }
-    c->launches += 2;
     CU(cudaMemcpyAsync(c->h_flags.p, c->ov_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     c->pending = true;
+    c->pend_mode = mode;
     c->pend_win = w;
     c->pend_result = dev_result;
     return 0;
 }
 
-// after the stream drained: windows that overflowed the fast path's shared segment are redone by the overflow kernel
+// after the stream drained: (1) an index built by this batch that ran out of room is rebuilt at its exact size and the
+// batch is redone; (2) windows that overflowed the fast path's shared segment are redone by the overflow kernel
 static int resolve_overflow(Ctx *c) {
     if (!c->pending) return 0;
     c->pending = false;
+    if (c->index_fresh) {
+        c->index_fresh = false;
+        const unsigned int *ctrl = (const unsigned int *)c->h_flags.p + 4;
+        c->idx_n_events = ctrl[0]; c->idx_n_segs = ctrl[1];
+        if (ctrl[2]) {
+            const LaunchWindows w = c->pend_win;
+            int32_t *res = c->pend_result;
+            const int mode = c->pend_mode;
+            c->idx.ev_cap = 0;                                // force re-dimensioning
+            const int per = index_reads_per_chunk();
+            (void)per;
+            if (int rc = ensure_index_buffers(c, (uint64_t)ctrl[0] + 64, (uint64_t)ctrl[1] + (uint64_t)ctrl[0] / 512 + (uint64_t)c->idx.n_chunks + 64)) return rc;
+            c->index_valid = false;
+            if (int rc = launch_batch(c, w, res, mode)) return rc;
+            CU(cudaStreamSynchronize(c->stream));
+            const unsigned int *ctrl2 = (const unsigned int *)c->h_flags.p + 4;
+            if (ctrl2[2]) return fail(SVTK_ERR_STATE, "signature index still out of room after re-dimensioning (events %u, segments %u)", ctrl2[0], ctrl2[1]);
+            return resolve_overflow(c);
+        }
+    }
     const int n_ov = *(int *)c->h_flags.p;
     c->last_overflow = n_ov;
     if (n_ov <= 0) return 0;
@@ -231,11 +309,11 @@ void svtk_destroy(svtk_ctx *ctx) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items, &c->ov_count,
-                      &c->arena, &c->counters, &c->scratch4, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c})
+                      &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_win, &c->h_result}) b->release();
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
-    for (int i = 0; i < 2; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
+    for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -286,6 +364,7 @@ int svtk_load_reads(svtk_ctx *ctx, const svtk_reads *h) {
                            (const uint32_t *)c->r_end.p, (const uint32_t *)c->r_ncig.p, (const unsigned long long *)c->r_off.p,
                            (const uint32_t *)c->r_cigar.p, 1};
     c->h2d_bytes += sizeof(long long) * (size_t)(h->n_tid + 1) + 20 * nr + 4 * nw;
+    c->n_words = h->n_words;
     return finish_reads(c);
 }
 
@@ -303,6 +382,7 @@ int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *d) {
     if (int rc = upload(c, c->r_tid_off.p, c->h_tid_off.data(), sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
     c->reads = LaunchReads{d->n_tid, d->n_reads, (const long long *)c->r_tid_off.p, d->pos, d->end, d->n_cigar,
                            (const unsigned long long *)d->cigar_off, d->cigar, 1};
+    c->n_words = d->n_words;
     return finish_reads(c);
 }
 
@@ -314,7 +394,7 @@ int svtk_refine_windows_device(svtk_ctx *ctx, const svtk_windows *w, int32_t *de
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c || !w || (w->n_win > 0 && !dev_result)) return fail(SVTK_ERR_ARG, "null argument");
     if (c->pending) if (int rc = svtk_sync(ctx)) return rc;
-    return launch_batch(c, as_launch(w), dev_result, false);
+    return launch_batch(c, as_launch(w), dev_result, MODE_INDEXED);
 }
 
 int svtk_sync(svtk_ctx *ctx) {
@@ -331,13 +411,11 @@ int svtk_set_profiling(svtk_ctx *ctx, int on) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c) return fail(SVTK_ERR_ARG, "null ctx");
     if (int rc = set_device(c)) return rc;
-    if (on && !c->prof_ev[0]) {
-        CU(cudaEventCreate(&c->prof_ev[0]));
-        CU(cudaEventCreate(&c->prof_ev[1]));
-    }
+    if (on && !c->prof_ev[0])
+        for (int i = 0; i < 4; ++i) CU(cudaEventCreate(&c->prof_ev[i]));
     if (int rc = collect_timing(c)) return rc;
     c->profile = on != 0;
-    c->fused_ms = 0.0; c->fused_launches = 0;
+    c->refine_ms = c->index_ms = 0.0; c->refine_launches = c->index_launches = 0;
     return 0;
 }
 
@@ -346,10 +424,42 @@ int svtk_get_timing(svtk_ctx *ctx, svtk_timing *t) {
     if (!c || !t) return fail(SVTK_ERR_ARG, "null argument");
     if (int rc = set_device(c)) return rc;
     if (int rc = collect_timing(c)) return rc;
-    t->refine_kernel_ms = c->fused_ms;
-    t->refine_kernel_launches = c->fused_launches;
+    t->refine_kernel_ms = c->refine_ms;
+    t->refine_kernel_launches = c->refine_launches;
+    t->index_kernel_ms = c->index_ms;
+    t->index_kernel_launches = c->index_launches;
     t->h2d_bytes = c->h2d_bytes;
     t->d2h_bytes = c->d2h_bytes;
+    return 0;
+}
+
+// (re)build the signature index of the resident reads now, asynchronously on the ctx stream
+int svtk_index_reads(svtk_ctx *ctx) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail(SVTK_ERR_ARG, "null ctx");
+    if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded");
+    if (int rc = set_device(c)) return rc;
+    if (c->pending) if (int rc = svtk_sync(ctx)) return rc;
+    return build_index(c);
+}
+
+int svtk_measure_index(svtk_ctx *ctx, const svtk_windows *w, int32_t *dev_result, svtk_index_stats *st) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !w || !st) return fail(SVTK_ERR_ARG, "null argument");
+    if (c->pending) if (int rc = svtk_sync(ctx)) return rc;
+    c->index_valid = false;
+    if (int rc = launch_batch(c, as_launch(w), dev_result, MODE_INDEXED_STATS)) return rc;
+    if (int rc = svtk_sync(ctx)) return rc;
+    unsigned long long cnt[5] = {0, 0, 0, 0, 0};
+    if (w->n_win > 0) CU(cudaMemcpy(cnt, c->counters.p, sizeof cnt, cudaMemcpyDeviceToHost));
+    const uint64_t nr = (uint64_t)c->reads.n_reads, nw = (uint64_t)c->n_words, nc = (uint64_t)c->idx.n_chunks;
+    st->n_reads = nr; st->n_words = nw; st->n_chunks = nc;
+    st->n_events = c->idx_n_events; st->n_segments = c->idx_n_segs;
+    st->index_bytes = 4 * nw + 20 * nr + 16 * c->idx_n_events + 4 * nr + 16 * nc;
+    st->n_windows = (uint64_t)w->n_win;
+    st->refine_events_scanned = cnt[0]; st->refine_segments = cnt[1]; st->refine_reads_in_range = cnt[2];
+    st->n_signatures = cnt[3]; st->n_overflow = cnt[4];
+    st->refine_bytes = 16 * cnt[0] + 16 * cnt[1] + 28ull * (uint64_t)w->n_win;
     return 0;
 }
 
@@ -357,7 +467,7 @@ int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *w, int32_t *dev_resu
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c || !w || !st) return fail(SVTK_ERR_ARG, "null argument");
     if (c->pending) if (int rc = svtk_sync(ctx)) return rc;
-    if (int rc = launch_batch(c, as_launch(w), dev_result, true)) return rc;
+    if (int rc = launch_batch(c, as_launch(w), dev_result, MODE_WALKER_STATS)) return rc;
     if (int rc = svtk_sync(ctx)) return rc;
     unsigned long long cnt[4] = {0, 0, 0, 0};
     if (w->n_win > 0) CU(cudaMemcpy(cnt, c->counters.p, sizeof cnt, cudaMemcpyDeviceToHost));
@@ -390,14 +500,16 @@ int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *w, int32_t *host_resu
     char *db = (char *)c->win_blob.p;
     const LaunchWindows lw{w->n_win, (const int32_t *)db, (const uint32_t *)(db + n4), (const uint32_t *)(db + 2 * n4),
                            (const uint32_t *)(db + 3 * n4), (const uint8_t *)(db + 4 * n4)};
-    if (int rc = launch_batch(c, lw, (int32_t *)c->result.p, false)) return rc;
+    if (int rc = launch_batch(c, lw, (int32_t *)c->result.p, MODE_INDEXED)) return rc;
     CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (*(int *)c->h_flags.p > 0) {        // some windows left the fast path: finish them, then fetch again
+    if (*(int *)c->h_flags.p > 0 || (c->index_fresh && ((const unsigned int *)c->h_flags.p)[6])) {
+        // some windows left the fast path, or the fresh index ran out of room: finish them, then fetch again
         if (int rc = resolve_overflow(c)) return rc;
         CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
     }
+    if (c->index_fresh) { c->index_fresh = false; c->idx_n_events = ((const unsigned int *)c->h_flags.p)[4]; c->idx_n_segs = ((const unsigned int *)c->h_flags.p)[5]; }
     c->pending = false;
     memcpy(host_result, c->h_result.p, 4 * n);
     c->h2d_bytes += blob;

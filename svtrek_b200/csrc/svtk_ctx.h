@@ -37,6 +37,14 @@ struct Ctx {
     std::vector<int64_t> h_tid_off;
     DevBuf r_tid_off, r_pos, r_end, r_ncig, r_off, r_cigar;
 
+    // signature index over the resident reads (svtk_index.cu): rebuilt by the first refine after a load
+    long long n_words = 0;
+    bool index_valid = false;
+    bool index_fresh = false;      // built by the batch in flight: its error bits still have to be checked at sync
+    LaunchIndex idx{};
+    DevBuf idx_events, idx_chunks, idx_segs, idx_rend, idx_ctrl;
+    uint64_t idx_n_events = 0, idx_n_segs = 0;
+
     // per-batch scratch
     DevBuf range;        // int2 per window: candidate read range
     DevBuf ov_items;     // int2 per window: (window, signature count) of fast-path overflows
@@ -52,6 +60,7 @@ struct Ctx {
 
     // a launched batch whose overflow windows have not been resolved yet
     bool pending = false;
+    int pend_mode = 0;
     LaunchWindows pend_win{};
     int32_t *pend_result = nullptr;
     int last_overflow = 0;
@@ -60,10 +69,10 @@ struct Ctx {
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
 
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
-    bool profile = false, prof_pending = false;
-    cudaEvent_t prof_ev[2] = {nullptr, nullptr};
-    double fused_ms = 0.0;
-    uint64_t fused_launches = 0;
+    bool profile = false, prof_pending = false, prof_idx_pending = false;
+    cudaEvent_t prof_ev[4] = {nullptr, nullptr, nullptr, nullptr};     // [0,1] refine kernel, [2,3] index kernel
+    double refine_ms = 0.0, index_ms = 0.0;
+    uint64_t refine_launches = 0, index_launches = 0;
 };
 
 }  // namespace svtk

@@ -42,6 +42,14 @@ struct DevWindows {
 
 struct Tunables { int range, interval, min_count; };
 
+constexpr int IDX_READS = 32;              // reads per chunk of the signature index (svtk_index.cu)
+
+struct OverflowList {
+    int *count;        // number of overflowed windows
+    int2 *items;       // (window index, signature count)
+    int capacity;
+};
+
 struct WorkCounters {            // svtk_stats, accumulated with atomics by the instrumented instantiation only
     unsigned long long pairs, words, signatures, overflow;
 };

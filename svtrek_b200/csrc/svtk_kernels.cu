@@ -6,7 +6,7 @@
 //   k_refine_fused      one CTA per window: CIGAR walk (one warp per read, uint4 loads) -> signatures in shared
 //                       memory -> bitonic sort -> consensus_pos.  Signatures never touch HBM.
 //   k_refine_overflow   windows whose signature count exceeded the fast path's shared-memory segment: same
-//                       pipeline with a 190 KB segment, or a global-memory segment beyond that
+//                       pipeline with a 128 KB segment, or a global-memory segment beyond that
 //   k_consensus_segments / k_slide_tiles / k_window_signatures   parity aids + sliding_window_ins
 //
 // HBM-bound integer work: grids are one CTA per window (thousands of windows per batch, >> 148 SMs), loads are
@@ -100,12 +100,6 @@ __device__ __forceinline__ void collect_window(const DevReads &R, int kind, uint
         __syncthreads();
     }
 }
-
-struct OverflowList {
-    int *count;        // number of overflowed windows
-    int2 *items;       // (window index, signature count)
-    int capacity;
-};
 
 // ---------------------------------------------------------------------------------------------------------
 // Fast path: one CTA per window, signatures in a CAP-int shared segment.
@@ -285,8 +279,9 @@ static DevWindows to_dev(const LaunchWindows &w) {
 }
 
 int big_segment_ints() {
-    // dynamic shared memory available to the overflow kernel next to its static arrays (227 KB opt-in per CTA)
-    return (200 * 1024) / 4;
+    // dynamic shared memory of the overflow kernel next to its static arrays (227 KB opt-in per CTA); a power of two
+    // because the bitonic sort pads a segment to next_pow2(n)
+    return 32768;
 }
 
 cudaError_t launch_max_span(const uint32_t *pos, const uint32_t *end, long long n, uint32_t *out, cudaStream_t s) {

@@ -84,7 +84,7 @@ def test_edge_windows(auditor):
 
 def test_overflow_tiers(auditor):
     """Windows with more signatures than the fast path's shared segment (1024), than the big shared segment
-    (51200) and beyond (global arena)."""
+    (32768) and beyond (global arena)."""
     rng = np.random.default_rng(9)
     reads = []
     L = 3_000_000
@@ -101,6 +101,7 @@ def test_overflow_tiers(auditor):
     add(40, 100_000, 3)          # ~120 signatures (fast path)
     add(300, 300_000, 12)        # ~3.6k (big shared segment)
     add(700, 600_000, 100)       # ~70k (global arena)
+    add(400, 900_000, 100)       # ~40k: between 2^15 and the old 51200-int segment (bitonic padding to 2^16 must not fit in shared)
     reads.sort(key=lambda r: r[0])
     pos = np.array([r[0] for r in reads], dtype=np.uint32)
     ncig = np.array([len(r[1]) for r in reads], dtype=np.uint32)
@@ -111,14 +112,14 @@ def test_overflow_tiers(auditor):
     auditor.load_reads(rs)
     auditor.set_params(**api.DEFAULT_PARAMS)
     orc = B.OracleReads(rs)
-    centers = np.array([100_000, 300_000, 600_000, 300_000, 600_000, 100_000])
-    kinds = np.array([0, 0, 0, 1, 1, 1])
+    centers = np.array([100_000, 300_000, 600_000, 300_000, 600_000, 100_000, 900_000, 900_000])
+    kinds = np.array([0, 0, 0, 1, 1, 1, 0, 1])
     st, en, ps = centers - 20000, centers + 20000, centers - 8000
-    got = auditor.refine_windows(np.ones(6), st, en, ps, kinds)
-    want = B.refine_batch(orc, np.ones(6), st, en, ps, kinds)
+    got = auditor.refine_windows(np.ones(8), st, en, ps, kinds)
+    want = B.refine_batch(orc, np.ones(8), st, en, ps, kinds)
     assert list(got) == list(want)
     n_sig = [len(auditor.window_signatures(0, 1, int(s), int(e))) for s, e in zip(st[:3], en[:3])]
-    assert n_sig[0] <= 1024 < n_sig[1] <= 51200 < n_sig[2], n_sig
+    assert n_sig[0] <= 1024 < n_sig[1] <= 32768 < n_sig[2], n_sig
     for i in range(3):
         _, osig = B.refine(orc, 0, 1, int(st[i]), int(en[i]), int(ps[i]), want_sig=True, cap=1 << 20)
         assert np.array_equal(auditor.window_signatures(0, 1, int(st[i]), int(en[i])), osig)

@@ -109,18 +109,20 @@ static int finish_reads(Ctx *c) {
 }
 
 // ---- signature index (svtk_index.cu)
-static int ensure_index_buffers(Ctx *c, uint64_t ev_cap, uint64_t seg_cap) {
+static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     const long long nr = c->reads.n_reads;
     const int per = index_reads_per_chunk();
     const long long n_chunks = (nr + per - 1) / per;
+    const uint64_t ev_cap = pool_cap * (uint64_t)index_pools();
     if (ev_cap >= (1ull << 31) || seg_cap >= (1ull << 31)) return fail(SVTK_ERR_ARG, "signature index beyond 2^31 events: shard the read set");
     if (int rc = c->idx_events.reserve(16 * (size_t)ev_cap)) return rc;
     if (int rc = c->idx_chunks.reserve(16 * (size_t)std::max(n_chunks, 1ll))) return rc;
     if (int rc = c->idx_segs.reserve(16 * (size_t)seg_cap)) return rc;
     if (int rc = c->idx_rend.reserve(4 * (size_t)std::max(nr, 1ll))) return rc;
-    if (int rc = c->idx_ctrl.reserve(64)) return rc;
+    if (int rc = c->idx_ctrl.reserve(4 * (size_t)index_ctrl_words())) return rc;
+    if (int rc = c->h_idx.reserve(4 * (size_t)index_ctrl_words())) return rc;
     c->idx = LaunchIndex{c->idx_events.p, c->idx_chunks.p, c->idx_segs.p, (uint32_t *)c->idx_rend.p, (unsigned int *)c->idx_ctrl.p,
-                         (unsigned int)ev_cap, (unsigned int)seg_cap, (int)n_chunks};
+                         (unsigned int)pool_cap, (unsigned int)seg_cap, (int)n_chunks};
     return 0;
 }
 
@@ -146,12 +148,15 @@ static int collect_timing(Ctx *c) {
 }
 
 static int build_index(Ctx *c) {
-    if (c->idx.ev_cap == 0 || c->idx.n_chunks != (int)((c->reads.n_reads + index_reads_per_chunk() - 1) / index_reads_per_chunk())) {
-        // first guess: one event per 16 CIGAR words plus both clip events of every read; grown on demand (resolve)
-        const uint64_t ev = (uint64_t)c->n_words / 16 + 2 * (uint64_t)c->reads.n_reads + 4096;
-        if (int rc = ensure_index_buffers(c, std::max<uint64_t>(ev, c->idx.ev_cap), std::max<uint64_t>(ev / 256 + 1024, c->idx.seg_cap))) return rc;
+    const int per = index_reads_per_chunk();
+    if (c->idx.pool_cap == 0 || c->idx.n_chunks != (int)((c->reads.n_reads + per - 1) / per)) {
+        // first guess: one event per 16 CIGAR words plus both clip events of every read, spread over the sub-pools with
+        // 25% slack for imbalance; grown on demand (resolve_overflow)
+        const uint64_t ev = (uint64_t)c->n_words / 16 + 2 * (uint64_t)c->reads.n_reads;
+        const uint64_t pool = ev / (uint64_t)index_pools() * 5 / 4 + 1024;
+        if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 64 + 1024, c->idx.seg_cap))) return rc;
     }
-    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, 16, c->stream));
+    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, 4 * (size_t)index_ctrl_words(), c->stream));
     if (c->profile) { if (int rc = collect_timing(c)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
     CU(launch_index_reads(c->reads, c->idx, c->stream));
     if (c->profile) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
@@ -165,7 +170,7 @@ static int ensure_batch(Ctx *c, int n_win) {
     if (int rc = c->range.reserve((size_t)n_win * sizeof(int2))) return rc;
     if (int rc = c->ov_items.reserve((size_t)n_win * sizeof(int2))) return rc;
     if (int rc = c->ov_count.reserve(64)) return rc;      // [0] overflow count  [1] fail flag  [2..3] arena top (u64)
-    if (int rc = c->h_flags.reserve(64)) return rc;       // [0] overflow count  [1] fail flag  [4..7] index ctrl
+    if (int rc = c->h_flags.reserve(64)) return rc;       // [0] overflow count  [1] fail flag
     return 0;
 }
 
@@ -205,7 +210,7 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
             c->prof_pending = true;
         }
         c->launches += 1;
-        if (c->index_fresh) CU(cudaMemcpyAsync((int *)c->h_flags.p + 4, c->idx_ctrl.p, 12, cudaMemcpyDeviceToHost, c->stream));
+        if (c->index_fresh) CU(cudaMemcpyAsync(c->h_idx.p, c->idx_ctrl.p, 4 * (size_t)index_ctrl_words(), cudaMemcpyDeviceToHost, c->stream));
     }
     CU(cudaMemcpyAsync(c->h_flags.p, c->ov_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     c->pending = true;
@@ -217,26 +222,35 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
 
 // after the stream drained: (1) an index built by this batch that ran out of room is rebuilt at its exact size and the
 // batch is redone; (2) windows that overflowed the fast path's shared segment are redone by the overflow kernel
+// totals of the index control block the last fresh build copied to the host
+static void index_totals(const Ctx *c, uint64_t *events, uint64_t *segs, unsigned int *max_pool, unsigned int *err) {
+    const unsigned int *ctrl = (const unsigned int *)c->h_idx.p;
+    const int st = index_ctrl_stride(), np = index_pools();
+    uint64_t ev = 0; unsigned int mx = 0;
+    for (int p = 0; p < np; ++p) { ev += ctrl[p * st]; mx = std::max(mx, ctrl[p * st]); }
+    *events = ev; *segs = ctrl[np * st]; *max_pool = mx; *err = ctrl[(np + 1) * st];
+}
+
 static int resolve_overflow(Ctx *c) {
     if (!c->pending) return 0;
     c->pending = false;
     if (c->index_fresh) {
         c->index_fresh = false;
-        const unsigned int *ctrl = (const unsigned int *)c->h_flags.p + 4;
-        c->idx_n_events = ctrl[0]; c->idx_n_segs = ctrl[1];
-        if (ctrl[2]) {
+        unsigned int max_pool = 0, err = 0;
+        index_totals(c, &c->idx_n_events, &c->idx_n_segs, &max_pool, &err);
+        if (err) {
             const LaunchWindows w = c->pend_win;
             int32_t *res = c->pend_result;
             const int mode = c->pend_mode;
-            c->idx.ev_cap = 0;                                // force re-dimensioning
-            const int per = index_reads_per_chunk();
-            (void)per;
-            if (int rc = ensure_index_buffers(c, (uint64_t)ctrl[0] + 64, (uint64_t)ctrl[1] + (uint64_t)ctrl[0] / 512 + (uint64_t)c->idx.n_chunks + 64)) return rc;
+            // every flush bumped its counter even when it found no room: the tops are the exact need
+            if (int rc = ensure_index_buffers(c, (uint64_t)max_pool + 64, c->idx_n_segs + c->idx_n_events / 64 + 1024)) return rc;
             c->index_valid = false;
             if (int rc = launch_batch(c, w, res, mode)) return rc;
             CU(cudaStreamSynchronize(c->stream));
-            const unsigned int *ctrl2 = (const unsigned int *)c->h_flags.p + 4;
-            if (ctrl2[2]) return fail(SVTK_ERR_STATE, "signature index still out of room after re-dimensioning (events %u, segments %u)", ctrl2[0], ctrl2[1]);
+            unsigned int err2 = 0; uint64_t e2 = 0, s2 = 0;
+            index_totals(c, &e2, &s2, &max_pool, &err2);
+            if (err2) return fail(SVTK_ERR_STATE, "signature index still out of room after re-dimensioning (events %llu, segments %llu)",
+                                  (unsigned long long)e2, (unsigned long long)s2);
             return resolve_overflow(c);
         }
     }
@@ -246,17 +260,26 @@ static int resolve_overflow(Ctx *c) {
     std::vector<int2> items((size_t)n_ov);
     CU(cudaMemcpyAsync(items.data(), c->ov_items.p, sizeof(int2) * (size_t)n_ov, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    const bool walker = c->pend_mode == MODE_WALKER_STATS;
     unsigned long long arena_need = 0;
-    const int big = big_segment_ints();
-    for (const int2 &it : items)
-        if (it.y > big) { unsigned long long p = 1; while (p < (unsigned long long)it.y) p <<= 1; arena_need += p; }
+    const int big = walker ? big_segment_ints() : refine_block_segment_ints();
+    for (const int2 &it : items) {
+        unsigned long long p = 1; while (p < (unsigned long long)it.y) p <<= 1;
+        if (p > (unsigned long long)big) arena_need += p;
+    }
     if (arena_need) if (int rc = c->arena.reserve(arena_need * 4)) return rc;
     int *flags = (int *)c->ov_count.p;
     CU(cudaMemsetAsync(flags + 1, 0, 12, c->stream));     // fail flag + arena top
-    CU(launch_refine_overflow(c->reads, c->pend_win, (const int2 *)c->range.p, c->params.consensus_interval_range,
-                              c->params.consensus_interval, c->params.consensus_min_count, c->pend_result, flags, (int2 *)c->ov_items.p,
-                              c->pend_win.n_win, n_ov, (int *)c->arena.p, arena_need, (unsigned long long *)(flags + 2), flags + 1,
-                              c->stream));
+    if (walker)
+        CU(launch_refine_overflow(c->reads, c->pend_win, (const int2 *)c->range.p, c->params.consensus_interval_range,
+                                  c->params.consensus_interval, c->params.consensus_min_count, c->pend_result, flags, (int2 *)c->ov_items.p,
+                                  c->pend_win.n_win, n_ov, (int *)c->arena.p, arena_need, (unsigned long long *)(flags + 2), flags + 1,
+                                  c->stream));
+    else
+        CU(launch_refine_block(c->reads, c->pend_win, c->idx, (const int2 *)c->range.p, c->params.consensus_interval_range,
+                               c->params.consensus_interval, c->params.consensus_min_count, c->pend_result, flags, (int2 *)c->ov_items.p,
+                               c->pend_win.n_win, n_ov, (int *)c->arena.p, arena_need, (unsigned long long *)(flags + 2), flags + 1,
+                               c->stream));
     c->launches += 1;
     CU(cudaMemcpyAsync((int *)c->h_flags.p + 1, flags + 1, 4, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -311,7 +334,7 @@ void svtk_destroy(svtk_ctx *ctx) {
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items, &c->ov_count,
                       &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c})
         b->release();
-    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_win, &c->h_result}) b->release();
+    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result}) b->release();
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -503,13 +526,13 @@ int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *w, int32_t *host_resu
     if (int rc = launch_batch(c, lw, (int32_t *)c->result.p, MODE_INDEXED)) return rc;
     CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (*(int *)c->h_flags.p > 0 || (c->index_fresh && ((const unsigned int *)c->h_flags.p)[6])) {
+    if (*(int *)c->h_flags.p > 0 || (c->index_fresh && ((const unsigned int *)c->h_idx.p)[(index_pools() + 1) * index_ctrl_stride()])) {
         // some windows left the fast path, or the fresh index ran out of room: finish them, then fetch again
         if (int rc = resolve_overflow(c)) return rc;
         CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
     }
-    if (c->index_fresh) { c->index_fresh = false; c->idx_n_events = ((const unsigned int *)c->h_flags.p)[4]; c->idx_n_segs = ((const unsigned int *)c->h_flags.p)[5]; }
+    if (c->index_fresh) { c->index_fresh = false; unsigned int mp, er; index_totals(c, &c->idx_n_events, &c->idx_n_segs, &mp, &er); }
     c->pending = false;
     memcpy(host_result, c->h_result.p, 4 * n);
     c->h2d_bytes += blob;

@@ -56,7 +56,7 @@ struct Ctx {
     DevBuf tmp_a, tmp_b, tmp_c;
     PinBuf stage[2];
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};
-    PinBuf h_flags, h_win, h_result;
+    PinBuf h_flags, h_idx, h_win, h_result;
 
     // a launched batch whose overflow windows have not been resolved yet
     bool pending = false;

@@ -42,7 +42,8 @@ struct DevWindows {
 
 struct Tunables { int range, interval, min_count; };
 
-constexpr int IDX_READS = 32;              // reads per chunk of the signature index (svtk_index.cu)
+constexpr int IDX_READS = 8;               // reads per chunk of the signature index: one warp's share (svtk_index.cu)
+constexpr int IDX_POOLS = 16;              // event sub-pools (spreads the per-flush atomicAdd over 16 L2 lines)
 
 struct OverflowList {
     int *count;        // number of overflowed windows

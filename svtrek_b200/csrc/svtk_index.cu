@@ -7,13 +7,15 @@
 //     - the clip rules compare the read's start / final cursor with [W.start, W.end]  (:147-159, :210-221)
 // so the walk itself is window independent.  This file splits the path accordingly:
 //
-//   k_index_reads     ONE coalesced pass over all CIGAR words (HBM-bound, 128-bit loads, block-wide scan of the
-//                     reference cursor): every read yields its signature events {cursor, len|type, read, endpos}
-//                     -- D > 50, I >= 50, trailing / leading soft clip -- and its final cursor.  Events of a
-//                     chunk of 32 reads land contiguously in HBM (one atomicAdd per chunk).
-//   k_refine_indexed  one CTA per window: 32-ary search of the read range the BAM iterator would yield
-//                     (hts.c:3049-3090, 3905-3921), gather of the events of the covering chunks under the two
-//                     rules above into shared memory, bitonic sort, consensus_pos (refinement.c:41-101).
+//   k_index_reads     ONE coalesced pass over all CIGAR words (HBM-bound): a warp owns a chunk of 8 consecutive
+//                     reads, streams their packed CIGAR words with 128-bit loads, 256 words per step, keeps the
+//                     reference cursor with a warp scan, and emits the chunk's signature events
+//                     {cursor, len|type, read, endpos} -- D > 50, I >= 50, trailing / leading soft clip -- plus
+//                     every read's final cursor.  No block-level barrier anywhere.
+//   k_refine_warp     one WARP per window: 32-ary search of the read range the BAM iterator would yield
+//                     (hts.c:3049-3090, 3905-3921), gather of the covering chunks' events under the two rules
+//                     above, register bitonic sort (<= 256 signatures), consensus_pos (refinement.c:41-101).
+//   k_refine_block    windows with more signatures: one CTA each, shared-memory or global segment.
 //
 // Results are bit-identical to the per-(window, read) walker in svtk_kernels.cu (kept as the instrumented
 // cross-check behind svtk_measure_windows).
@@ -24,25 +26,27 @@ namespace svtk {
 
 constexpr int EV_DEL = 0, EV_INS = 1, EV_TCLIP = 2, EV_LCLIP = 3;
 
-constexpr int IDX_NT = 256;                 // threads per CTA
-constexpr int IDX_WPT = 8;                  // CIGAR words per thread and tile
-constexpr int IDX_TILE = IDX_NT * IDX_WPT;  // 2048 words = 8 KB per tile
-constexpr int IDX_EVCAP = 512;              // events staged in shared memory between flushes
+constexpr int IDX_WARPS = 4;                // warps (= chunks) per CTA of k_index_reads
+constexpr int IDX_WPT = 8;                  // CIGAR words per lane and step
+constexpr int IDX_TILE = 32 * IDX_WPT;      // 256 words = 1 KB per warp step
+constexpr int IDX_EVCAP = 128;              // events a warp stages in shared memory between flushes
+constexpr int CTRL_STRIDE = 32;             // u32 words between counters: one 128-byte line each
+constexpr int CTRL_SEG = IDX_POOLS * CTRL_STRIDE, CTRL_ERR = CTRL_SEG + CTRL_STRIDE;
 
 struct DevIndex {
-    uint4 *events;       // {x, len << 4 | type, read index, read endpos}
-    uint4 *chunks;       // per chunk of IDX_READS reads: newest segment {base, count, next segment or -1, 0}
+    uint4 *events;       // {x, len << 4 | type, read index, read endpos}; IDX_POOLS sub-pools of pool_cap events
+    uint4 *chunks;       // per chunk of IDX_READS reads: newest segment {base, count, next segment or -1, first pos}
     uint4 *segs;         // older segments of chunks that flushed more than once
     uint32_t *rend;      // per read: reference cursor after the whole CIGAR
-    unsigned int *ctrl;  // [0] event top  [1] segment top  [2] error bits (1 event pool, 2 segment pool)
-    unsigned int ev_cap, seg_cap;
+    unsigned int *ctrl;  // [p * CTRL_STRIDE] top of sub-pool p, [CTRL_SEG] segment top, [CTRL_ERR] error bits (1 events, 2 segments)
+    unsigned int pool_cap, seg_cap;
     int n_chunks;
 };
 
 static DevIndex to_dev(const LaunchIndex &x) {
     DevIndex d;
     d.events = reinterpret_cast<uint4 *>(x.events); d.chunks = reinterpret_cast<uint4 *>(x.chunks);
-    d.segs = reinterpret_cast<uint4 *>(x.segs); d.rend = x.rend; d.ctrl = x.ctrl; d.ev_cap = x.ev_cap; d.seg_cap = x.seg_cap;
+    d.segs = reinterpret_cast<uint4 *>(x.segs); d.rend = x.rend; d.ctrl = x.ctrl; d.pool_cap = x.pool_cap; d.seg_cap = x.seg_cap;
     d.n_chunks = x.n_chunks;
     return d;
 }
@@ -59,71 +63,73 @@ static DevWindows to_dev(const LaunchWindows &w) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-struct IndexShared {
-    uint32_t P[IDX_TILE];                // exclusive cursor prefix (chunk relative) of every word of the tile
-    unsigned short cand[IDX_TILE];       // tile-local indices of D > 50 / I >= 50 words
+struct IndexWarpShared {
+    uint32_t P[IDX_TILE];                // exclusive cursor prefix (chunk relative) of every word of the step
     uint4 ev[IDX_EVCAP];
+    unsigned short cand[IDX_TILE];       // step-local indices of D > 50 / I >= 50 words
     uint32_t rel[IDX_READS + 1];         // word offset of each read, relative to the aligned chunk start
     uint32_t pos[IDX_READS], endp[IDX_READS];
     uint32_t base[IDX_READS + 1];        // P at each read's first word
-    uint32_t wtot[IDX_NT / 32];
-    int ncand[2];
-    int nclip;
-    uint32_t flush_base;
-    uint4 head;                          // newest segment of this chunk
+    int ncand;
 };
 
-// write the staged events as one more segment of the chunk (uniform call; nev > 0)
-__device__ __forceinline__ void index_flush(IndexShared &s, const DevIndex &X, int nev) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int b = atomicAdd(&X.ctrl[0], (unsigned int)nev);
-        uint32_t fb = 0xffffffffu;
-        if ((unsigned long long)b + (unsigned long long)nev > (unsigned long long)X.ev_cap) atomicOr(&X.ctrl[2], 1u);
+// append the warp's staged events to the chunk as one more segment; `head` (uniform) is the chunk's newest segment
+__device__ __forceinline__ void index_flush_warp(IndexWarpShared &s, const DevIndex &X, int pool, int nev, uint4 &head) {
+    const int lane = lane_id();
+    __syncwarp();
+    uint32_t fb = 0xffffffffu;
+    uint4 nh = head;
+    if (lane == 0) {
+        const unsigned int b = atomicAdd(&X.ctrl[pool * CTRL_STRIDE], (unsigned int)nev);
+        if ((unsigned long long)b + (unsigned long long)nev > (unsigned long long)X.pool_cap) atomicOr(&X.ctrl[CTRL_ERR], 1u);
         else {
-            int next = -1;
+            uint32_t next = 0xffffffffu;
             bool ok = true;
-            if (s.head.y != 0u) {                            // push the previous segment down the chain
-                const unsigned int si = atomicAdd(&X.ctrl[1], 1u);
-                if (si >= X.seg_cap) { atomicOr(&X.ctrl[2], 2u); ok = false; }
-                else { X.segs[si] = s.head; next = (int)si; }
+            if (head.y != 0u) {                              // push the previous segment down the chain
+                const unsigned int si = atomicAdd(&X.ctrl[CTRL_SEG], 1u);
+                if (si >= X.seg_cap) { atomicOr(&X.ctrl[CTRL_ERR], 2u); ok = false; }
+                else { X.segs[si] = head; next = si; }
             }
-            if (ok) { s.head = make_uint4(b, (uint32_t)nev, (uint32_t)next, 0u); fb = b; }
+            if (ok) { fb = (uint32_t)pool * X.pool_cap + b; nh = make_uint4(fb, (uint32_t)nev, next, head.w); }
         }
-        s.flush_base = fb;
     }
-    __syncthreads();
-    const uint32_t fb = s.flush_base;
+    fb = __shfl_sync(FULL, fb, 0);
+    nh.x = __shfl_sync(FULL, nh.x, 0); nh.y = __shfl_sync(FULL, nh.y, 0); nh.z = __shfl_sync(FULL, nh.z, 0);
+    head = nh;
     if (fb != 0xffffffffu)
-        for (int i = threadIdx.x; i < nev; i += IDX_NT) X.events[(size_t)fb + i] = s.ev[i];
-    __syncthreads();
+        for (int i = lane; i < nev; i += 32) X.events[(size_t)fb + i] = s.ev[i];
+    __syncwarp();
 }
 
-__global__ void __launch_bounds__(IDX_NT) k_index_reads(DevReads R, DevIndex X) {
-    __shared__ IndexShared s;
-    constexpr int NW = IDX_NT / 32;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const long long r0 = (long long)blockIdx.x * IDX_READS;
+__global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevIndex X) {
+    __shared__ IndexWarpShared sh[IDX_WARPS];
+    const int lane = lane_id(), warp = threadIdx.x >> 5;
+    const long long c = (long long)blockIdx.x * IDX_WARPS + warp;
+    if (c >= X.n_chunks) return;
+    IndexWarpShared &s = sh[warp];
+    const int pool = (int)(blockIdx.x % IDX_POOLS);
+    const long long r0 = c * IDX_READS;
     const int nr = (int)min((long long)IDX_READS, R.n_reads - r0);
-    const unsigned long long w0 = __ldg(R.cigar_off + r0);
-    const unsigned long long w0a = w0 & ~3ull;
-    if (t <= nr) {
-        const long long r = r0 + t;
-        const unsigned long long off = (t < nr) ? __ldg(R.cigar_off + r) : __ldg(R.cigar_off + r - 1) + __ldg(R.n_cigar + r - 1);
-        s.rel[t] = (uint32_t)(off - w0a);
-        if (t < nr) { s.pos[t] = __ldg(R.pos + r); s.endp[t] = __ldg(R.end + r); }
+    unsigned long long off = 0;
+    if (lane <= nr) {
+        const long long r = r0 + lane;
+        off = (lane < nr) ? __ldg(R.cigar_off + r) : __ldg(R.cigar_off + r - 1) + __ldg(R.n_cigar + r - 1);
+        if (lane < nr) { s.pos[lane] = __ldg(R.pos + r); s.endp[lane] = __ldg(R.end + r); }
     }
-    if (t == 0) { s.ncand[0] = 0; s.ncand[1] = 0; s.nclip = 0; s.head = make_uint4(0u, 0u, 0xffffffffu, 0u); }
-    __syncthreads();
+    const unsigned long long w0 = __shfl_sync(FULL, off, 0);
+    const unsigned long long w0a = w0 & ~3ull;
+    if (lane <= nr) s.rel[lane] = (uint32_t)(off - w0a);
+    __syncwarp();
     const uint32_t head_pad = (uint32_t)(w0 - w0a);
     const uint32_t span = s.rel[nr];
     const uint32_t *__restrict__ cg = R.cigar + w0a;
+    uint4 head = make_uint4(0u, 0u, 0xffffffffu, s.pos[0]);
 
-    uint32_t run = 0;       // cursor advance of all words before the current tile (uniform)
+    uint32_t run = 0;       // cursor advance of all words before the current step (uniform)
     int nev = 0;            // staged events (uniform)
-    int par = 0;
-    for (uint32_t tb = 0; tb < span; tb += IDX_TILE, par ^= 1) {
-        const uint32_t i0 = tb + (uint32_t)t * IDX_WPT;
+    for (uint32_t tb = 0; tb < span; tb += IDX_TILE) {
+        if (lane == 0) s.ncand = 0;
+        const uint32_t i0 = tb + (uint32_t)lane * IDX_WPT;
         uint32_t w[IDX_WPT];
 #pragma unroll
         for (int q = 0; q < IDX_WPT / 4; ++q) {
@@ -131,13 +137,15 @@ __global__ void __launch_bounds__(IDX_NT) k_index_reads(DevReads R, DevIndex X) 
             if (i0 + 4u * q < span) v = __ldg(reinterpret_cast<const uint4 *>(cg + i0 + 4u * q));
             w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
         }
+        if (tb == 0 || tb + IDX_TILE > span) {               // edge steps: blank the neighbouring chunks' words ("0M", inert)
+#pragma unroll
+            for (int k = 0; k < IDX_WPT; ++k) { const uint32_t gi = i0 + k; if (gi < head_pad || gi >= span) w[k] = 0u; }
+        }
         uint32_t p[IDX_WPT];
         uint32_t sum = 0;
         unsigned candm = 0;
 #pragma unroll
         for (int k = 0; k < IDX_WPT; ++k) {
-            const uint32_t gi = i0 + k;
-            if (gi < head_pad || gi >= span) w[k] = 0u;      // the neighbouring chunks' words: "0M", inert
             const uint32_t op = w[k] & 15u, len = w[k] >> 4;
             p[k] = sum;
             sum += ((0x12u >> op) & 1u) ? 0u : len;          // every op except I(1) and S(4) advances (refinement.c:137)
@@ -145,36 +153,30 @@ __global__ void __launch_bounds__(IDX_NT) k_index_reads(DevReads R, DevIndex X) 
                 candm |= 1u << k;
         }
         const uint32_t incl = warp_inclusive_scan(sum);
-        if (lane == 31) s.wtot[warp] = incl;
-        __syncthreads();                                     // #1
-        if (t == 0) s.ncand[par ^ 1] = 0;
-        uint32_t woff = 0, ttot = 0;
-#pragma unroll
-        for (int v = 0; v < NW; ++v) { const uint32_t x = s.wtot[v]; ttot += x; if (v < warp) woff += x; }
-        const uint32_t mybase = run + woff + (incl - sum);
+        const uint32_t mybase = run + (incl - sum);
 #pragma unroll
         for (int q = 0; q < IDX_WPT / 4; ++q)
-            *reinterpret_cast<uint4 *>(&s.P[t * IDX_WPT + 4 * q]) =
+            *reinterpret_cast<uint4 *>(&s.P[lane * IDX_WPT + 4 * q]) =
                 make_uint4(mybase + p[4 * q], mybase + p[4 * q + 1], mybase + p[4 * q + 2], mybase + p[4 * q + 3]);
+        __syncwarp();
         if (candm) {
-            const int slot = atomicAdd(&s.ncand[par], __popc(candm));
+            const int slot = atomicAdd(&s.ncand, __popc(candm));
             int j = 0;
 #pragma unroll
             for (int k = 0; k < IDX_WPT; ++k)
-                if (candm & (1u << k)) s.cand[slot + j++] = (unsigned short)(t * IDX_WPT + k);
+                if (candm & (1u << k)) s.cand[slot + j++] = (unsigned short)(lane * IDX_WPT + k);
         }
-        __syncthreads();                                     // #2
-        if (t < nr) {
-            const uint32_t rel = s.rel[t];
-            if (rel >= tb && rel < tb + IDX_TILE && rel < span) s.base[t] = s.P[rel - tb];
+        if (lane < nr) {
+            const uint32_t rel = s.rel[lane];
+            if (rel >= tb && rel < tb + IDX_TILE && rel < span) s.base[lane] = s.P[rel - tb];
         }
-        __syncthreads();                                     // #3
-        const int ncand = s.ncand[par];
+        __syncwarp();
+        const int ncand = s.ncand;
         int done = 0;
         while (done < ncand) {
-            if (nev == IDX_EVCAP) { index_flush(s, X, nev); nev = 0; }
+            if (nev == IDX_EVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
             const int take = min(IDX_EVCAP - nev, ncand - done);
-            for (int ci = t; ci < take; ci += IDX_NT) {
+            for (int ci = lane; ci < take; ci += 32) {
                 const uint32_t i = s.cand[done + ci];
                 const uint32_t gi = tb + i;
                 int lo = 0, hi = nr;                         // the read owning word gi: last r with rel[r] <= gi
@@ -186,55 +188,69 @@ __global__ void __launch_bounds__(IDX_NT) k_index_reads(DevReads R, DevIndex X) 
             }
             nev += take; done += take;
         }
-        run += ttot;
+        run += __shfl_sync(FULL, incl, 31);
+        __syncwarp();                                        // P / cand / ncand are rewritten by the next step
     }
     // reads that start at the very end of the chunk's span (empty CIGARs) and the end-of-span sentinel
-    if (t <= nr && s.rel[t] >= span) s.base[t] = run;
-    __syncthreads();
-    if (nev + 2 * IDX_READS > IDX_EVCAP && nev > 0) { index_flush(s, X, nev); nev = 0; }
-    if (t < nr) {
-        const uint32_t n = s.rel[t + 1] - s.rel[t];
-        uint32_t rendv = s.pos[t];
+    if (lane <= nr && s.rel[lane] >= span) s.base[lane] = run;
+    __syncwarp();
+    if (nev + 2 * IDX_READS > IDX_EVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
+    bool tclip = false, lclip = false;
+    uint32_t rendv = 0;
+    if (lane < nr) {
+        const uint32_t n = s.rel[lane + 1] - s.rel[lane];
+        rendv = s.pos[lane];
         if (n > 0) {
-            rendv += s.base[t + 1] - s.base[t];
-            const uint32_t first = __ldg(cg + s.rel[t]), last = __ldg(cg + s.rel[t + 1] - 1);
-            if ((last & 15u) == (uint32_t)OP_SOFT) {         // refinement.c:120,147: trailing soft clip, value = final cursor
-                const int k = atomicAdd(&s.nclip, 1);
-                s.ev[nev + k] = make_uint4(rendv, EV_TCLIP, (uint32_t)(r0 + t), s.endp[t]);
-            }
-            if ((first & 15u) == (uint32_t)OP_SOFT) {        // refinement.c:210: leading soft clip, keyed by core.pos
-                const int k = atomicAdd(&s.nclip, 1);
-                s.ev[nev + k] = make_uint4(s.pos[t], EV_LCLIP, (uint32_t)(r0 + t), s.endp[t]);
-            }
+            rendv += s.base[lane + 1] - s.base[lane];
+            const uint32_t first = __ldg(cg + s.rel[lane]), last = __ldg(cg + s.rel[lane + 1] - 1);
+            tclip = (last & 15u) == (uint32_t)OP_SOFT;       // refinement.c:120,147: trailing soft clip, value = final cursor
+            lclip = (first & 15u) == (uint32_t)OP_SOFT;      // refinement.c:210: leading soft clip, keyed by core.pos
         }
-        X.rend[r0 + t] = rendv;
+        X.rend[r0 + lane] = rendv;
     }
-    __syncthreads();
-    nev += s.nclip;
-    if (nev > 0) index_flush(s, X, nev);
-    if (t == 0) X.chunks[blockIdx.x] = s.head;
+    const unsigned mt = __ballot_sync(FULL, tclip), ml = __ballot_sync(FULL, lclip);
+    const unsigned below = (1u << lane) - 1u;
+    if (tclip) s.ev[nev + __popc(mt & below)] = make_uint4(rendv, EV_TCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
+    if (lclip) s.ev[nev + __popc(mt) + __popc(ml & below)] = make_uint4(s.pos[lane], EV_LCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
+    nev += __popc(mt) + __popc(ml);
+    if (nev > 0) index_flush_warp(s, X, pool, nev, head);
+    if (lane == 0) X.chunks[c] = head;
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// first index in [a,b) with pos[idx] >= key, by the whole warp: 32 probes per round instead of one
-__device__ __forceinline__ long long warp_lower_bound_pos(const uint32_t *__restrict__ pos, long long a, long long b, long long key) {
+// Two lower bounds at once over pos[t0,t1) -- first index with pos >= keyA / keyB -- by the whole warp, 32 probes
+// per round and both probe loads in flight together (hts.c:3913: yielded reads have pos < end; look-back bound).
+__device__ __forceinline__ void warp_lower_bound_pos2(const uint32_t *__restrict__ pos, long long t0, long long t1, long long keyA,
+                                                      long long keyB, long long &resA, long long &resB) {
     const int lane = lane_id();
-    while (b - a > 32) {
-        const long long step = (b - a + 31) / 32;
-        long long idx = a + (long long)(lane + 1) * step - 1;
-        if (idx > b - 1) idx = b - 1;
-        const bool ge = (long long)__ldg(pos + idx) >= key;
-        const unsigned m = __ballot_sync(FULL, ge);
-        if (!m) return b;
-        const int L = __ffs(m) - 1;
-        const long long na = a + (long long)L * step;
-        b = __shfl_sync(FULL, idx, L);                       // pos[b] >= key: the answer lies in [na, b]
-        a = na;
+    long long aA = t0, bA = t1, aB = t0, bB = t1;
+    resA = -1; resB = -1;
+    while (resA < 0 || resB < 0) {
+        long long iA = 0, iB = 0, sA = 1, sB = 1;
+        bool finA = false, finB = false, okA = false, okB = false;
+        if (resA < 0) {
+            if (bA - aA > 32) { sA = (bA - aA + 31) / 32; iA = aA + (long long)(lane + 1) * sA - 1; if (iA > bA - 1) iA = bA - 1; okA = true; }
+            else { finA = true; iA = aA + lane; okA = iA < bA; }
+        }
+        if (resB < 0) {
+            if (bB - aB > 32) { sB = (bB - aB + 31) / 32; iB = aB + (long long)(lane + 1) * sB - 1; if (iB > bB - 1) iB = bB - 1; okB = true; }
+            else { finB = true; iB = aB + lane; okB = iB < bB; }
+        }
+        const uint32_t vA = okA ? __ldg(pos + iA) : 0u;
+        const uint32_t vB = okB ? __ldg(pos + iB) : 0u;
+        if (resA < 0) {
+            const unsigned m = __ballot_sync(FULL, okA && (long long)vA >= keyA);
+            if (finA) resA = m ? aA + (__ffs(m) - 1) : bA;
+            else if (!m) resA = bA;
+            else { const int L = __ffs(m) - 1; const long long nb = __shfl_sync(FULL, iA, L); aA += (long long)L * sA; bA = nb; }
+        }
+        if (resB < 0) {
+            const unsigned m = __ballot_sync(FULL, okB && (long long)vB >= keyB);
+            if (finB) resB = m ? aB + (__ffs(m) - 1) : bB;
+            else if (!m) resB = bB;
+            else { const int L = __ffs(m) - 1; const long long nb = __shfl_sync(FULL, iB, L); aB += (long long)L * sB; bB = nb; }
+        }
     }
-    const long long idx = a + lane;
-    const bool ge = idx < b && (long long)__ldg(pos + idx) >= key;
-    const unsigned m = __ballot_sync(FULL, ge);
-    return m ? a + (__ffs(m) - 1) : b;
 }
 
 // cursor right after the op that first pushes it past w_end (refinement.c:141-144); the caller knows it exists
@@ -255,128 +271,178 @@ __device__ __forceinline__ uint32_t warp_stop_cursor(const uint32_t *__restrict_
     return carry;
 }
 
-struct RefineShared {
-    long long lo, hi;
-    int count;
-    int n_defer;
-    int defer[32];                    // reads whose leading-clip rule needs the stop cursor (rare)
-    ScanResult res[2];
+// What one signature event contributes to a window.  Returns 1 = emit `val`, 2 = leading-clip read whose
+// walk stops inside the window (needs warp_stop_cursor), 0 = nothing.
+__device__ __forceinline__ int event_for_window(const uint4 ev, int kind, uint32_t w_start, uint32_t w_end, uint32_t beg, long long lo,
+                                                long long hi, const uint32_t *__restrict__ rend, int &val) {
+    const uint32_t type = ev.y & 15u, len = ev.y >> 4;
+    const long long ri = (long long)ev.z;
+    if (!(ri >= lo && ri < hi && ev.w > beg)) return 0;      // the iterator yields this read iff endpos > beg (hts.c:3914)
+    if (kind == KIND_DEL_START) {
+        if (type == EV_DEL) { val = (int)ev.x; return ev.x <= w_end; }
+        if (type == EV_TCLIP) { val = (int)ev.x; return w_start <= ev.x && ev.x <= w_end; }
+        return 0;
+    }
+    if (kind == KIND_DEL_END) {
+        if (type == EV_DEL) { val = (int)(ev.x + len + 1u); return ev.x <= w_end; }
+        if (type == EV_LCLIP && w_start <= ev.x && ev.x <= w_end) {
+            const uint32_t rendv = __ldg(rend + ri);
+            if (rendv <= w_end) { val = (int)(rendv + 1u); return 1; }   // walk never stopped: final cursor + 1
+            val = (int)ev.z;
+            return 2;
+        }
+        return 0;
+    }
+    if (type == EV_INS) { val = (int)ev.x; return ev.x <= w_end; }       // KIND_INS
+    return 0;
+}
+
+// ascending bitonic sort of 32*K ints held K per lane, element index = k*32 + lane; no shared memory, no barrier
+template <int K>
+__device__ __forceinline__ void warp_bitonic_sort(int (&v)[K]) {
+    const int lane = lane_id();
+#pragma unroll
+    for (int size = 2; size <= 32 * K; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (stride >= 32) {
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    const int kk = k ^ (stride >> 5);
+                    if (kk > k) {
+                        const bool asc = ((k * 32) & size) == 0;
+                        const int lo = min(v[k], v[kk]), hi = max(v[k], v[kk]);
+                        v[k] = asc ? lo : hi; v[kk] = asc ? hi : lo;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    const int o = __shfl_xor_sync(FULL, v[k], stride);
+                    const bool asc = (((k * 32) | lane) & size) == 0;
+                    const bool lower = (lane & stride) == 0;
+                    v[k] = (asc == lower) ? min(v[k], o) : max(v[k], o);
+                }
+            }
+        }
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void warp_sort_segment(int *a, int n) {
+    const int lane = lane_id();
+    int v[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { const int i = k * 32 + lane; v[k] = i < n ? a[i] : 0x7fffffff; }
+    warp_bitonic_sort<K>(v);
+#pragma unroll
+    for (int k = 0; k < K; ++k) { const int i = k * 32 + lane; if (i < n) a[i] = v[k]; }
+    __syncwarp();
+}
+
+constexpr int RW_WARPS = 4;            // windows per CTA of k_refine_warp
+constexpr int RW_CAP = 256;            // signatures a warp sorts in registers (8 per lane)
+constexpr int RW_DEFER = 8;
+
+struct RefineWarpShared {
+    int sig[RW_CAP];
+    int defer[RW_DEFER];
 };
 
 struct IndexCounters {                // instrumented instantiation only
     unsigned long long events_scanned, segments, pairs_range, signatures, overflow;
 };
 
-// One CTA per window.  NT threads, CAP-int signature segment in shared memory; windows with more signatures go to
-// the overflow list exactly like the fused walker's.
-template <int NT, int CAP, bool STATS>
-__global__ void __launch_bounds__(NT) k_refine_indexed(DevReads R, DevWindows W, DevIndex X, Tunables t, int32_t *__restrict__ result,
-                                                       OverflowList ov, int2 *__restrict__ range_out, IndexCounters *ic) {
-    __shared__ int s_sig[CAP];
-    __shared__ RefineShared s;
-    constexpr int NWARP = NT / 32;
-    const int w = blockIdx.x;
-    const int warp = threadIdx.x >> 5, lane = lane_id();
+// ---------------------------------------------------------------------------------------------------------
+// One warp per window.  Windows with more than RW_CAP signatures go to the overflow list (window, exact count).
+template <bool STATS>
+__global__ void __launch_bounds__(RW_WARPS * 32) k_refine_warp(DevReads R, DevWindows W, DevIndex X, Tunables t, int32_t *__restrict__ result,
+                                                               OverflowList ov, int2 *__restrict__ range_out, IndexCounters *ic) {
+    __shared__ RefineWarpShared sh[RW_WARPS];
+    const int lane = lane_id(), warp = threadIdx.x >> 5;
+    const int w = blockIdx.x * RW_WARPS + warp;
+    if (w >= W.n_win) return;
+    RefineWarpShared &s = sh[warp];
     const int kind = W.kind[w];
     const uint32_t w_start = W.start[w], w_end = W.end[w];
     const int tid = W.chrom[w] - 1;                              // refinement.c:114
     const uint32_t beg = w_start - 1u;
     const long long begq = (long long)beg, endq = (long long)(uint32_t)(w_end - 1u);   // uint32 arithmetic, then widened
-    const bool live = tid >= 0 && tid < R.n_tid && endq >= begq && kind != KIND_POINT;
-    if (threadIdx.x == 0) { s.count = 0; s.n_defer = 0; s.lo = 0; s.hi = 0; }
-    __syncthreads();
-    if (live && warp < 2) {
-        const long long t0 = R.tid_off[tid], t1 = R.tid_off[tid + 1];
+    long long lo = 0, hi = 0;
+    if (tid >= 0 && tid < R.n_tid && endq >= begq && kind != KIND_POINT) {
         // yielded reads have pos < endq (hts.c:3913) and pos + span > beg; span <= max_span bounds the look-back
-        const long long key = warp == 0 ? endq : begq - (long long)R.max_span + 1;
-        const long long v = warp_lower_bound_pos(R.pos, t0, t1, key);
-        if (lane == 0) { if (warp == 0) s.hi = v; else s.lo = v; }
+        warp_lower_bound_pos2(R.pos, R.tid_off[tid], R.tid_off[tid + 1], endq, begq - (long long)R.max_span + 1, hi, lo);
+        if (lo > hi) lo = hi;
     }
-    __syncthreads();
-    const long long hi = s.hi, lo = s.lo < s.hi ? s.lo : s.hi;
-    if (range_out && threadIdx.x == 0) range_out[w] = make_int2((int)lo, (int)hi);
+    if (lane == 0) range_out[w] = make_int2((int)lo, (int)hi);
     if (hi <= lo) {                                              // no iterator / no reads / refine_point
-        if (threadIdx.x == 0) result[w] = -1;
+        if (lane == 0) result[w] = -1;
         return;
     }
-    const SigSink sink{s_sig, &s.count, CAP};
-    const long long c0 = lo / IDX_READS, c1 = (hi - 1) / IDX_READS;
+    const unsigned below = (1u << lane) - 1u;
+    int n = 0, nd = 0;                                           // signatures, deferred leading-clip reads (uniform)
     unsigned long long n_scan = 0, n_seg = 0;
-    for (long long c = c0 + warp; c <= c1; c += NWARP) {
-        uint4 seg = __ldg(X.chunks + c);
-        while (true) {
-            const uint32_t base = seg.x, cnt = seg.y;
-            if (STATS) { n_scan += cnt; n_seg += 1; }
-            for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
-                const uint32_t e = e0 + lane;
-                bool emit = false;
-                int val = 0;
-                if (e < cnt) {
-                    const uint4 ev = __ldg(X.events + (size_t)base + e);
-                    const uint32_t type = ev.y & 15u, len = ev.y >> 4;
-                    const long long ri = (long long)ev.z;
-                    if (ri >= lo && ri < hi && ev.w > beg) {         // the iterator yields this read (endpos > beg, hts.c:3914)
-                        if (kind == KIND_DEL_START) {
-                            if (type == EV_DEL) { emit = ev.x <= w_end; val = (int)ev.x; }
-                            else if (type == EV_TCLIP) { emit = w_start <= ev.x && ev.x <= w_end; val = (int)ev.x; }
-                        } else if (kind == KIND_DEL_END) {
-                            if (type == EV_DEL) { emit = ev.x <= w_end; val = (int)(ev.x + len + 1u); }
-                            else if (type == EV_LCLIP && w_start <= ev.x && ev.x <= w_end) {
-                                const uint32_t rendv = __ldg(X.rend + ri);
-                                if (rendv <= w_end) { emit = true; val = (int)(rendv + 1u); }    // walk never stopped: final cursor + 1
-                                else { const int k = atomicAdd(&s.n_defer, 1); if (k < 32) s.defer[k] = (int)ri; }
-                            }
-                        } else {                                     // KIND_INS
-                            if (type == EV_INS) { emit = ev.x <= w_end; val = (int)ev.x; }
-                        }
+    const long long c0 = lo / IDX_READS, c1 = (hi - 1) / IDX_READS;
+    for (long long cb = c0; cb <= c1; cb += 32) {
+        uint4 myh = make_uint4(0u, 0u, 0xffffffffu, 0u);
+        if (cb + lane <= c1) myh = __ldg(X.chunks + cb + lane);
+        const int nb = (int)min(32ll, c1 - cb + 1);
+        for (int j = 0; j < nb; ++j) {
+            uint4 seg;
+            seg.x = __shfl_sync(FULL, myh.x, j); seg.y = __shfl_sync(FULL, myh.y, j); seg.z = __shfl_sync(FULL, myh.z, j);
+            while (true) {
+                const uint32_t base = seg.x, cnt = seg.y;
+                if (STATS) { n_scan += cnt; n_seg += 1; }
+                for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
+                    int code = 0, val = 0;
+                    if (e0 + lane < cnt) code = event_for_window(__ldg(X.events + (size_t)base + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);
+                    const unsigned m = __ballot_sync(FULL, code == 1);
+                    if (code == 1) { const int slot = n + __popc(m & below); if (slot < RW_CAP) s.sig[slot] = val; }
+                    n += __popc(m);
+                    const unsigned md = __ballot_sync(FULL, code == 2);
+                    if (md) {
+                        if (code == 2) { const int slot = nd + __popc(md & below); if (slot < RW_DEFER) s.defer[slot] = val; }
+                        nd += __popc(md);
                     }
                 }
-                const unsigned m = __ballot_sync(FULL, emit);
-                if (m) {
-                    int b = 0;
-                    if (lane == 0) b = atomicAdd(&s.count, __popc(m));
-                    b = __shfl_sync(FULL, b, 0);
-                    if (emit) { const int slot = b + __popc(m & ((1u << lane) - 1u)); if (slot < CAP) s_sig[slot] = val; }
-                }
+                if (seg.z == 0xffffffffu) break;
+                seg = __ldg(X.segs + seg.z);
             }
-            if (seg.z == 0xffffffffu) break;
-            seg = __ldg(X.segs + seg.z);
         }
     }
-    __syncthreads();
+    __syncwarp();
     // leading-clip reads whose walk stops inside the window: value = cursor after the crossing op, + 1 (refinement.c:210-220)
-    const int nd = s.n_defer;
     if (nd > 0) {
-        if (nd <= 32) {
-            for (int k = warp; k < nd; k += NWARP) {
+        if (nd <= RW_DEFER) {
+            for (int k = 0; k < nd; ++k) {
                 const long long ri = s.defer[k];
                 const uint32_t sr = warp_stop_cursor(R.cigar, __ldg(R.cigar_off + ri), __ldg(R.n_cigar + ri), __ldg(R.pos + ri), w_end);
-                if (lane == 0) sink.push((int)(sr + 1u));
+                if (lane == 0 && n < RW_CAP) s.sig[n] = (int)(sr + 1u);
+                ++n;
             }
         } else {
-            // more than the defer list holds: rescan the read range for them (still rare)
-            for (long long ri = lo + warp; ri < hi; ri += NWARP) {
-                const uint32_t n = __ldg(R.n_cigar + ri), rp = __ldg(R.pos + ri);
-                if (n == 0 || !(__ldg(R.end + ri) > beg) || !(w_start <= rp && rp <= w_end)) continue;
+            for (long long ri = lo; ri < hi; ++ri) {             // more than the defer list holds: rescan the read range (rare)
+                const uint32_t nc = __ldg(R.n_cigar + ri), rp = __ldg(R.pos + ri);
+                if (nc == 0 || !(__ldg(R.end + ri) > beg) || !(w_start <= rp && rp <= w_end)) continue;
                 const unsigned long long off = __ldg(R.cigar_off + ri);
                 if ((__ldg(R.cigar + off) & 15u) != (uint32_t)OP_SOFT || __ldg(X.rend + ri) <= w_end) continue;
-                const uint32_t sr = warp_stop_cursor(R.cigar, off, n, rp, w_end);
-                if (lane == 0) sink.push((int)(sr + 1u));
+                const uint32_t sr = warp_stop_cursor(R.cigar, off, nc, rp, w_end);
+                if (lane == 0 && n < RW_CAP) s.sig[n] = (int)(sr + 1u);
+                ++n;
             }
         }
-        __syncthreads();
+        __syncwarp();
     }
-    const int n = s.count;
-    if (STATS) {
-        if (lane == 0) { atomicAdd(&ic->events_scanned, n_scan); atomicAdd(&ic->segments, n_seg); }
-        if (threadIdx.x == 0) { atomicAdd(&ic->pairs_range, (unsigned long long)(hi - lo)); atomicAdd(&ic->signatures, (unsigned long long)n); }
+    if (STATS && lane == 0) {
+        atomicAdd(&ic->events_scanned, n_scan); atomicAdd(&ic->segments, n_seg);
+        atomicAdd(&ic->pairs_range, (unsigned long long)(hi - lo)); atomicAdd(&ic->signatures, (unsigned long long)n);
     }
     if (n < t.min_count || n <= 0) {                             // refinement.c:43
-        if (threadIdx.x == 0) result[w] = -1;
+        if (lane == 0) result[w] = -1;
         return;
     }
-    if (n > CAP) {
-        if (threadIdx.x == 0) {
+    if (n > RW_CAP) {
+        if (lane == 0) {
             const int slot = atomicAdd(ov.count, 1);
             if (slot < ov.capacity) ov.items[slot] = make_int2(w, n);
             result[w] = -1;
@@ -384,40 +450,112 @@ __global__ void __launch_bounds__(NT) k_refine_indexed(DevReads R, DevWindows W,
         }
         return;
     }
-    block_bitonic_sort(s_sig, n);
-    const int res = block_consensus(s_sig, n, (int)W.pos[w], t, s.res);
-    if (threadIdx.x == 0) result[w] = res;
+    if (n <= 32) warp_sort_segment<1>(s.sig, n);
+    else if (n <= 64) warp_sort_segment<2>(s.sig, n);
+    else if (n <= 128) warp_sort_segment<4>(s.sig, n);
+    else warp_sort_segment<8>(s.sig, n);
+    const int pos = (int)W.pos[w];
+    int res;
+    const ScanResult L = consensus_scan_warp(s.sig, n, pos, t, true);
+    if (L.early) res = L.value;
+    else {
+        const ScanResult Rr = consensus_scan_warp(s.sig, n, pos, t, false);
+        res = Rr.early ? Rr.value : (L.dist < Rr.dist ? L.best : Rr.best);
+    }
+    if (lane == 0) result[w] = res;
 }
 
-// =========================================================================================================
-constexpr int RI_NT = 128;
-constexpr int RI_CAP = 1024;
+// ---------------------------------------------------------------------------------------------------------
+// Overflow tier: persistent CTAs walk the list (window, signature count) left by k_refine_warp.  Segment = dynamic shared
+// memory when next_pow2(count) fits, else a slice of the global arena (bump-allocated).  Same gather, block-wide.
+struct RefineBlockShared {
+    int count, n_defer;
+    int defer[32];
+    unsigned long long base;
+    ScanResult res[2];
+};
 
-int index_reads_per_chunk() { return IDX_READS; }
-
-cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaStream_t s) {
-    if (r.n_reads <= 0) return cudaSuccess;
-    k_index_reads<<<x.n_chunks, IDX_NT, 0, s>>>(to_dev(r), to_dev(x));
-    return cudaGetLastError();
+template <int NT>
+__global__ void __launch_bounds__(NT) k_refine_block(DevReads R, DevWindows W, DevIndex X, const int2 *__restrict__ range, Tunables t,
+                                                     int32_t *__restrict__ result, OverflowList ov, int cap_smem, int *arena,
+                                                     unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag) {
+    extern __shared__ int s_dyn[];
+    __shared__ RefineBlockShared s;
+    constexpr int NWARP = NT / 32;
+    const int warp = threadIdx.x >> 5, lane = lane_id();
+    const int n_items = min(*ov.count, ov.capacity);
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int2 item = ov.items[it];
+        const int w = item.x, n_expect = item.y;
+        int *seg = s_dyn;
+        int cap = cap_smem;
+        if (next_pow2(n_expect) > cap_smem) {
+            if (threadIdx.x == 0) s.base = atomicAdd(arena_top, (unsigned long long)next_pow2(n_expect));
+            __syncthreads();
+            if (s.base + (unsigned long long)next_pow2(n_expect) > arena_ints) {     // arena exhausted: host retries with a bigger one
+                if (threadIdx.x == 0) atomicExch(fail_flag, 1);
+                __syncthreads();
+                continue;
+            }
+            seg = arena + s.base;
+            cap = n_expect;
+        }
+        if (threadIdx.x == 0) { s.count = 0; s.n_defer = 0; }
+        __syncthreads();
+        const int kind = W.kind[w];
+        const uint32_t w_start = W.start[w], w_end = W.end[w], beg = w_start - 1u;
+        const long long lo = range[w].x, hi = range[w].y;
+        const SigSink sink{seg, &s.count, cap};
+        const long long c0 = lo / IDX_READS, c1 = (hi - 1) / IDX_READS;
+        for (long long c = c0 + warp; c <= c1; c += NWARP) {
+            uint4 sg = __ldg(X.chunks + c);
+            while (true) {
+                const uint32_t base = sg.x, cnt = sg.y;
+                for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
+                    int code = 0, val = 0;
+                    if (e0 + lane < cnt) code = event_for_window(__ldg(X.events + (size_t)base + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);
+                    if (code == 2) { const int k = atomicAdd(&s.n_defer, 1); if (k < 32) s.defer[k] = val; }
+                    const unsigned m = __ballot_sync(FULL, code == 1);
+                    if (m) {
+                        int b = 0;
+                        if (lane == 0) b = atomicAdd(&s.count, __popc(m));
+                        b = __shfl_sync(FULL, b, 0);
+                        if (code == 1) { const int slot = b + __popc(m & ((1u << lane) - 1u)); if (slot < cap) seg[slot] = val; }
+                    }
+                }
+                if (sg.z == 0xffffffffu) break;
+                sg = __ldg(X.segs + sg.z);
+            }
+        }
+        __syncthreads();
+        const int nd = s.n_defer;
+        if (nd > 0) {
+            if (nd <= 32) {
+                for (int k = warp; k < nd; k += NWARP) {
+                    const long long ri = s.defer[k];
+                    const uint32_t sr = warp_stop_cursor(R.cigar, __ldg(R.cigar_off + ri), __ldg(R.n_cigar + ri), __ldg(R.pos + ri), w_end);
+                    if (lane == 0) sink.push((int)(sr + 1u));
+                }
+            } else {
+                for (long long ri = lo + warp; ri < hi; ri += NWARP) {
+                    const uint32_t nc = __ldg(R.n_cigar + ri), rp = __ldg(R.pos + ri);
+                    if (nc == 0 || !(__ldg(R.end + ri) > beg) || !(w_start <= rp && rp <= w_end)) continue;
+                    const unsigned long long off = __ldg(R.cigar_off + ri);
+                    if ((__ldg(R.cigar + off) & 15u) != (uint32_t)OP_SOFT || __ldg(X.rend + ri) <= w_end) continue;
+                    const uint32_t sr = warp_stop_cursor(R.cigar, off, nc, rp, w_end);
+                    if (lane == 0) sink.push((int)(sr + 1u));
+                }
+            }
+            __syncthreads();
+        }
+        __threadfence_block();
+        const int n = s.count;                  // == n_expect
+        block_bitonic_sort(seg, n);
+        const int res = block_consensus(seg, n, (int)W.pos[w], t, s.res);
+        if (threadIdx.x == 0) result[w] = res;
+        __syncthreads();
+    }
 }
-
-cudaError_t launch_refine_indexed(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, int2 *range, int range_, int interval,
-                                  int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity,
-                                  unsigned long long *counters, cudaStream_t s) {
-    if (w.n_win <= 0) return cudaSuccess;
-    const Tunables t{range_, interval, min_count};
-    const OverflowList ov{ov_count, ov_items, ov_capacity};
-    if (counters)
-        k_refine_indexed<RI_NT, RI_CAP, true><<<w.n_win, RI_NT, 0, s>>>(to_dev(r), to_dev(w), to_dev(x), t, result, ov, range,
-                                                                         reinterpret_cast<IndexCounters *>(counters));
-    else
-        k_refine_indexed<RI_NT, RI_CAP, false><<<w.n_win, RI_NT, 0, s>>>(to_dev(r), to_dev(w), to_dev(x), t, result, ov, range, nullptr);
-    return cudaGetLastError();
-}
-
-}  // namespace svtk
-
-namespace svtk {
 
 // svtk_reads contract check: CIGARs packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1])
 __global__ void k_check_layout(const unsigned long long *__restrict__ off, const uint32_t *__restrict__ n, long long n_reads,
@@ -428,11 +566,59 @@ __global__ void k_check_layout(const unsigned long long *__restrict__ off, const
     }
 }
 
+// =========================================================================================================
+constexpr int RB_NT = 1024;
+
+int index_reads_per_chunk() { return IDX_READS; }
+int index_pools() { return IDX_POOLS; }
+int index_ctrl_words() { return CTRL_ERR + CTRL_STRIDE; }
+int index_ctrl_stride() { return CTRL_STRIDE; }
+int refine_block_segment_ints() { return 32768; }      // power of two: the bitonic sort pads a segment to next_pow2(n)
+
 cudaError_t launch_check_layout(const LaunchReads &r, unsigned long long n_words, unsigned int *flag, cudaStream_t s) {
     if (r.n_reads <= 0) return cudaSuccess;
     const long long want = (r.n_reads + 255) / 256;
     const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
     k_check_layout<<<blocks, 256, 0, s>>>(r.cigar_off, r.n_cigar, r.n_reads, n_words, flag);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaStream_t s) {
+    if (r.n_reads <= 0) return cudaSuccess;
+    k_index_reads<<<(x.n_chunks + IDX_WARPS - 1) / IDX_WARPS, IDX_WARPS * 32, 0, s>>>(to_dev(r), to_dev(x));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_refine_indexed(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, int2 *range, int range_, int interval,
+                                  int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity,
+                                  unsigned long long *counters, cudaStream_t s) {
+    if (w.n_win <= 0) return cudaSuccess;
+    const Tunables t{range_, interval, min_count};
+    const OverflowList ov{ov_count, ov_items, ov_capacity};
+    const int grid = (w.n_win + RW_WARPS - 1) / RW_WARPS;
+    if (counters)
+        k_refine_warp<true><<<grid, RW_WARPS * 32, 0, s>>>(to_dev(r), to_dev(w), to_dev(x), t, result, ov, range,
+                                                            reinterpret_cast<IndexCounters *>(counters));
+    else
+        k_refine_warp<false><<<grid, RW_WARPS * 32, 0, s>>>(to_dev(r), to_dev(w), to_dev(x), t, result, ov, range, nullptr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_refine_block(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, const int2 *range, int range_,
+                                int interval, int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
+                                int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag, cudaStream_t s) {
+    static bool attr_set = false;
+    const int cap = refine_block_segment_ints();
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_refine_block<RB_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap * 4);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const Tunables t{range_, interval, min_count};
+    const OverflowList ov{ov_count, ov_items, ov_capacity};
+    const int grid = n_items < 148 ? n_items : 148;
+    k_refine_block<RB_NT><<<grid, RB_NT, cap * 4, s>>>(to_dev(r), to_dev(w), to_dev(x), range, t, result, ov, cap, arena, arena_ints,
+                                                       arena_top, fail_flag);
     return cudaGetLastError();
 }
 

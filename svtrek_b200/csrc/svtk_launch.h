@@ -23,20 +23,27 @@ struct LaunchWindows {          // device pointers
 };
 
 struct LaunchIndex {            // the signature index built by k_index_reads (device pointers)
-    void *events;               // uint4 per event
+    void *events;               // uint4 per event; index_pools() sub-pools of pool_cap events each
     void *chunks;               // uint4 per chunk of index_reads_per_chunk() reads
     void *segs;                 // uint4 per extra segment
     uint32_t *rend;             // per read
-    unsigned int *ctrl;         // [0] event top  [1] segment top  [2] error bits
-    unsigned int ev_cap, seg_cap;
+    unsigned int *ctrl;         // index_ctrl_words() u32: [p * stride] sub-pool tops, [pools * stride] segment top, then error bits
+    unsigned int pool_cap, seg_cap;
     int n_chunks;
 };
 
 int index_reads_per_chunk();
+int index_pools();
+int index_ctrl_words();
+int index_ctrl_stride();
+int refine_block_segment_ints();
 cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaStream_t s);
 cudaError_t launch_refine_indexed(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, int2 *range, int range_, int interval,
                                   int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity,
                                   unsigned long long *counters, cudaStream_t s);
+cudaError_t launch_refine_block(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, const int2 *range, int range_,
+                                int interval, int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
+                                int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag, cudaStream_t s);
 cudaError_t launch_check_layout(const LaunchReads &r, unsigned long long n_words, unsigned int *flag, cudaStream_t s);
 
 int big_segment_ints();

@@ -126,8 +126,8 @@ def test_deferred_leading_clip_walks(auditor):
 
 
 def test_empty_cigars_and_chunk_boundaries(auditor):
-    """Reads with n_cigar == 0 (no signature), chunk sizes around the 32-read boundary, single-read sets."""
-    for n_reads in (1, 31, 32, 33, 65):
+    """Reads with n_cigar == 0 (no signature), chunk sizes around the 8- and 32-read boundaries, single-read sets."""
+    for n_reads in (1, 7, 8, 9, 31, 32, 33, 65):
         reads = []
         for i in range(n_reads):
             pos = 100_000 + 37 * i
@@ -143,7 +143,7 @@ def test_empty_cigars_and_chunk_boundaries(auditor):
         indexed, walker, st, _ = _both_paths(auditor, w)
         want = B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"], 1, 5, 500)
         assert list(indexed) == list(want) and list(walker) == list(want), n_reads
-        assert st["n_chunks"] == (n_reads + 31) // 32
+        assert st["n_chunks"] == (n_reads + 7) // 8
     auditor.set_params(**api.DEFAULT_PARAMS)
 
 

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsvtk_b200.so")
+LIB_PATH = os.environ.get("SVTK_LIB") or os.path.join(HERE, "libsvtk_b200.so")    # SVTK_LIB: kernel experiments only
 
 DEL_START, DEL_END, INS, POINT = 0, 1, 2, 3
 DEFAULT_PARAMS = dict(wider_interval=20000, median_interval=10000, narrow_interval=2000,

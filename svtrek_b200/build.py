@@ -8,7 +8,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libsvtk_b200.so")
+LIB = os.environ.get("SVTK_LIB_OUT") or os.path.join(HERE, "libsvtk_b200.so")
 SOURCES = ["svtk_kernels.cu", "svtk_index.cu", "svtk_capi.cpp", "svtk_host.cpp"]
 HEADERS = ["svtk_device.cuh", "svtk_launch.h", "svtk_ctx.h", os.path.join("..", "..", "include", "svtk.h")]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-Xcompiler", "-fPIC",
@@ -32,7 +32,7 @@ def stale() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
-    cmd = [nvcc(), *NVCC_FLAGS, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
+    cmd = [nvcc(), *NVCC_FLAGS, *os.environ.get("SVTK_NVCC_EXTRA", "").split(), "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas"); cmd.insert(2, "-v")
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -22,6 +22,13 @@
 #include "svtk_device.cuh"
 #include "svtk_launch.h"
 
+#ifndef SVTK_IDX_TABLE
+#define SVTK_IDX_TABLE 1       // decode through the shared-memory op table + IMAD.HI (else: funnel-shift bit tables)
+#endif
+#ifndef SVTK_IDX_PREFETCH
+#define SVTK_IDX_PREFETCH 1    // software-pipelined loads
+#endif
+
 namespace svtk {
 
 constexpr int EV_DEL = 0, EV_INS = 1, EV_TCLIP = 2, EV_LCLIP = 3;
@@ -29,7 +36,7 @@ constexpr int EV_DEL = 0, EV_INS = 1, EV_TCLIP = 2, EV_LCLIP = 3;
 constexpr int IDX_WARPS = 4;                // warps (= chunks) per CTA of k_index_reads
 constexpr int IDX_WPT = 8;                  // CIGAR words per lane and step
 constexpr int IDX_TILE = 32 * IDX_WPT;      // 256 words = 1 KB per warp step
-constexpr int IDX_EVCAP = 128;              // events a warp stages in shared memory between flushes
+constexpr int IDX_EVCAP = 256;              // events a warp stages in shared memory between flushes (>= one step's worst case)
 constexpr int CTRL_STRIDE = 32;             // u32 words between counters: one 128-byte line each
 constexpr int CTRL_SEG = IDX_POOLS * CTRL_STRIDE, CTRL_ERR = CTRL_SEG + CTRL_STRIDE;
 
@@ -66,12 +73,18 @@ static DevWindows to_dev(const LaunchWindows &w) {
 struct IndexWarpShared {
     uint32_t P[IDX_TILE];                // exclusive cursor prefix (chunk relative) of every word of the step
     uint4 ev[IDX_EVCAP];
-    unsigned short cand[IDX_TILE];       // step-local indices of D > 50 / I >= 50 words
-    uint32_t rel[IDX_READS + 1];         // word offset of each read, relative to the aligned chunk start
+    uint32_t rel[IDX_READS + 4];         // word offset of each read, relative to the aligned chunk start; 0xffffffff beyond nr
     uint32_t pos[IDX_READS], endp[IDX_READS];
     uint32_t base[IDX_READS + 1];        // P at each read's first word
-    int ncand;
+    uint2 optab[16];                     // per CIGAR op: {advance multiplier, smallest word that is a signature}
 };
+
+// high half of a * b, plus c: one IMAD.HI on the FMA pipe (the decode loop is ALU-pipe bound otherwise)
+__device__ __forceinline__ uint32_t mad_hi_u32(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // append the warp's staged events to the chunk as one more segment; `head` (uniform) is the chunk's newest segment
 __device__ __forceinline__ void index_flush_warp(IndexWarpShared &s, const DevIndex &X, int pool, int nev, uint4 &head) {
@@ -101,8 +114,8 @@ __device__ __forceinline__ void index_flush_warp(IndexWarpShared &s, const DevIn
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevIndex X) {
-    __shared__ IndexWarpShared sh[IDX_WARPS];
+__global__ void __launch_bounds__(IDX_WARPS * 32, 10) k_index_reads(DevReads R, DevIndex X) {
+    __shared__ __align__(16) IndexWarpShared sh[IDX_WARPS];
     const int lane = lane_id(), warp = threadIdx.x >> 5;
     const long long c = (long long)blockIdx.x * IDX_WARPS + warp;
     if (c >= X.n_chunks) return;
@@ -118,7 +131,15 @@ __global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevI
     }
     const unsigned long long w0 = __shfl_sync(FULL, off, 0);
     const unsigned long long w0a = w0 & ~3ull;
-    if (lane <= nr) s.rel[lane] = (uint32_t)(off - w0a);
+    if (lane < IDX_READS + 4) s.rel[lane] = lane <= nr ? (uint32_t)(off - w0a) : 0xffffffffu;
+    if (lane < 16) {
+        // x = 2^28 for ops that advance the reference cursor (all but I and S, refinement.c:137): hi32(word * 2^28) == len.
+        // y = first word value that is a signature: I with len >= 50 (refinement.c:299), D with len > 50 (refinement.c:124).
+        const uint32_t adv = (lane == OP_INS || lane == OP_SOFT) ? 0u : (1u << 28);
+        const uint32_t thr = lane == OP_INS ? ((uint32_t)SV_MIN_LENGTH << 4 | OP_INS)
+                           : lane == OP_DEL ? ((uint32_t)(SV_MIN_LENGTH + 1) << 4 | OP_DEL) : 0xffffffffu;
+        s.optab[lane] = make_uint2(adv, thr);
+    }
     __syncwarp();
     const uint32_t head_pad = (uint32_t)(w0 - w0a);
     const uint32_t span = s.rel[nr];
@@ -127,15 +148,29 @@ __global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevI
 
     uint32_t run = 0;       // cursor advance of all words before the current step (uniform)
     int nev = 0;            // staged events (uniform)
+#if SVTK_IDX_PREFETCH
+    // software pipeline: the next step's 32 bytes per lane are in flight while the current step is decoded
+    uint4 nx[IDX_WPT / 4];
+#pragma unroll
+    for (int q = 0; q < IDX_WPT / 4; ++q) {
+        nx[q] = make_uint4(0u, 0u, 0u, 0u);
+        if ((uint32_t)lane * IDX_WPT + 4u * q < span) nx[q] = __ldg(reinterpret_cast<const uint4 *>(cg + lane * IDX_WPT + 4 * q));
+    }
+#endif
     for (uint32_t tb = 0; tb < span; tb += IDX_TILE) {
-        if (lane == 0) s.ncand = 0;
         const uint32_t i0 = tb + (uint32_t)lane * IDX_WPT;
         uint32_t w[IDX_WPT];
 #pragma unroll
         for (int q = 0; q < IDX_WPT / 4; ++q) {
+#if SVTK_IDX_PREFETCH
+            w[4 * q] = nx[q].x; w[4 * q + 1] = nx[q].y; w[4 * q + 2] = nx[q].z; w[4 * q + 3] = nx[q].w;
+            nx[q] = make_uint4(0u, 0u, 0u, 0u);
+            if (i0 + IDX_TILE + 4u * q < span) nx[q] = __ldg(reinterpret_cast<const uint4 *>(cg + i0 + IDX_TILE + 4u * q));
+#else
             uint4 v = make_uint4(0u, 0u, 0u, 0u);
             if (i0 + 4u * q < span) v = __ldg(reinterpret_cast<const uint4 *>(cg + i0 + 4u * q));
             w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+#endif
         }
         if (tb == 0 || tb + IDX_TILE > span) {               // edge steps: blank the neighbouring chunks' words ("0M", inert)
 #pragma unroll
@@ -146,11 +181,19 @@ __global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevI
         unsigned candm = 0;
 #pragma unroll
         for (int k = 0; k < IDX_WPT; ++k) {
-            const uint32_t op = w[k] & 15u, len = w[k] >> 4;
+#if SVTK_IDX_TABLE
+            const uint2 ot = s.optab[w[k] & 15u];            // shared-memory lookup: keeps the ALU pipe for the compares
             p[k] = sum;
-            sum += ((0x12u >> op) & 1u) ? 0u : len;          // every op except I(1) and S(4) advances (refinement.c:137)
-            if ((op == (uint32_t)OP_DEL && len > (uint32_t)SV_MIN_LENGTH) || (op == (uint32_t)OP_INS && len >= (uint32_t)SV_MIN_LENGTH))
-                candm |= 1u << k;
+            sum = mad_hi_u32(w[k], ot.x, sum);               // += len for ops that advance
+            if (w[k] >= ot.y) candm |= 1u << k;
+#else
+            // 16-entry bit tables indexed by the op nibble (rotate by the low 5 bits of the word; the tables have period 16)
+            const uint32_t keep = __funnelshift_r(0xFFEDFFEDu, 0xFFEDFFEDu, w[k]) & 1u;   // every op except I(1), S(4) advances
+            const uint32_t indel = __funnelshift_r(0x00060006u, 0x00060006u, w[k]) & 1u;  // op is I or D
+            p[k] = sum;
+            sum += keep * (w[k] >> 4);
+            if (indel && w[k] >= 0x321u && w[k] != 0x322u) candm |= 1u << k;
+#endif
         }
         const uint32_t incl = warp_inclusive_scan(sum);
         const uint32_t mybase = run + (incl - sum);
@@ -158,38 +201,38 @@ __global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevI
         for (int q = 0; q < IDX_WPT / 4; ++q)
             *reinterpret_cast<uint4 *>(&s.P[lane * IDX_WPT + 4 * q]) =
                 make_uint4(mybase + p[4 * q], mybase + p[4 * q + 1], mybase + p[4 * q + 2], mybase + p[4 * q + 3]);
+        const int myc = __popc(candm);
+        const int tot = __reduce_add_sync(FULL, myc);        // candidates of this step (uniform)
         __syncwarp();
-        if (candm) {
-            const int slot = atomicAdd(&s.ncand, __popc(candm));
-            int j = 0;
-#pragma unroll
-            for (int k = 0; k < IDX_WPT; ++k)
-                if (candm & (1u << k)) s.cand[slot + j++] = (unsigned short)(lane * IDX_WPT + k);
-        }
         if (lane < nr) {
             const uint32_t rel = s.rel[lane];
             if (rel >= tb && rel < tb + IDX_TILE && rel < span) s.base[lane] = s.P[rel - tb];
         }
-        __syncwarp();
-        const int ncand = s.ncand;
-        int done = 0;
-        while (done < ncand) {
-            if (nev == IDX_EVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
-            const int take = min(IDX_EVCAP - nev, ncand - done);
-            for (int ci = lane; ci < take; ci += 32) {
-                const uint32_t i = s.cand[done + ci];
-                const uint32_t gi = tb + i;
-                int lo = 0, hi = nr;                         // the read owning word gi: last r with rel[r] <= gi
-                while (hi - lo > 1) { const int m = (lo + hi) >> 1; if (s.rel[m] <= gi) lo = m; else hi = m; }
+        if (tot) {
+            if (nev + tot > IDX_EVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
+            __syncwarp();
+            int slot = myc;                                  // exclusive prefix of the per-lane candidate counts
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, slot, d); if (lane >= d) slot += o; }
+            slot += nev - myc;
+            unsigned cm = candm;
+            while (cm) {
+                const int k = __ffs(cm) - 1;
+                cm &= cm - 1;
+                const uint32_t i = (uint32_t)(lane * IDX_WPT + k), gi = tb + i;
+                const uint4 ra = *reinterpret_cast<const uint4 *>(&s.rel[0]), rb = *reinterpret_cast<const uint4 *>(&s.rel[4]);
+                // the read owning word gi: last r with rel[r] <= gi (rel[0] <= gi always; entries beyond nr are 0xffffffff)
+                const int r = (int)(ra.y <= gi) + (int)(ra.z <= gi) + (int)(ra.w <= gi) + (int)(rb.x <= gi) + (int)(rb.y <= gi) +
+                              (int)(rb.z <= gi) + (int)(rb.w <= gi);
                 const uint32_t word = __ldg(cg + gi);
-                const uint32_t x = s.pos[lo] + (s.P[i] - s.base[lo]);
+                const uint32_t x = s.pos[r] + (s.P[i] - s.base[r]);
                 const uint32_t type = ((word & 15u) == (uint32_t)OP_DEL) ? EV_DEL : EV_INS;
-                s.ev[nev + ci] = make_uint4(x, (word & ~15u) | type, (uint32_t)(r0 + lo), s.endp[lo]);
+                s.ev[slot++] = make_uint4(x, (word & ~15u) | type, (uint32_t)(r0 + r), s.endp[r]);
             }
-            nev += take; done += take;
+            nev += tot;
         }
         run += __shfl_sync(FULL, incl, 31);
-        __syncwarp();                                        // P / cand / ncand are rewritten by the next step
+        __syncwarp();                                        // P is rewritten by the next step
     }
     // reads that start at the very end of the chunk's span (empty CIGARs) and the end-of-span sentinel
     if (lane <= nr && s.rel[lane] >= span) s.base[lane] = run;
@@ -220,37 +263,43 @@ __global__ void __launch_bounds__(IDX_WARPS * 32) k_index_reads(DevReads R, DevI
 // ---------------------------------------------------------------------------------------------------------
 // Two lower bounds at once over pos[t0,t1) -- first index with pos >= keyA / keyB -- by the whole warp, 32 probes
 // per round and both probe loads in flight together (hts.c:3913: yielded reads have pos < end; look-back bound).
+// Keys are 64-bit (uint32 window arithmetic widened): out-of-range keys are resolved without probing.
+struct WarpSearch {
+    int a, b, res;           // open range [a,b); res >= 0 once found
+    uint32_t key;
+    int idx, step;
+    bool fin, ok;
+    __device__ __forceinline__ void init(int t0, int t1, long long k) {
+        a = t0; b = t1; res = -1; key = (uint32_t)k;
+        if (k <= 0) res = t0; else if (k > 0xffffffffll) res = t1;
+    }
+    __device__ __forceinline__ void probe(int lane) {
+        ok = false; fin = false; idx = a; step = 1;
+        if (res >= 0) return;
+        if (b - a > 32) { step = (b - a + 31) >> 5; idx = min(a + (lane + 1) * step - 1, b - 1); ok = true; }
+        else { fin = true; idx = a + lane; ok = idx < b; }
+    }
+    __device__ __forceinline__ void update(uint32_t v) {
+        if (res >= 0) return;
+        const unsigned m = __ballot_sync(FULL, ok && v >= key);
+        if (fin) res = m ? a + (__ffs(m) - 1) : b;
+        else if (!m) res = b;
+        else { const int L = __ffs(m) - 1; const int nb = __shfl_sync(FULL, idx, L); a += L * step; b = nb; }
+    }
+};
+
 __device__ __forceinline__ void warp_lower_bound_pos2(const uint32_t *__restrict__ pos, long long t0, long long t1, long long keyA,
                                                       long long keyB, long long &resA, long long &resB) {
     const int lane = lane_id();
-    long long aA = t0, bA = t1, aB = t0, bB = t1;
-    resA = -1; resB = -1;
-    while (resA < 0 || resB < 0) {
-        long long iA = 0, iB = 0, sA = 1, sB = 1;
-        bool finA = false, finB = false, okA = false, okB = false;
-        if (resA < 0) {
-            if (bA - aA > 32) { sA = (bA - aA + 31) / 32; iA = aA + (long long)(lane + 1) * sA - 1; if (iA > bA - 1) iA = bA - 1; okA = true; }
-            else { finA = true; iA = aA + lane; okA = iA < bA; }
-        }
-        if (resB < 0) {
-            if (bB - aB > 32) { sB = (bB - aB + 31) / 32; iB = aB + (long long)(lane + 1) * sB - 1; if (iB > bB - 1) iB = bB - 1; okB = true; }
-            else { finB = true; iB = aB + lane; okB = iB < bB; }
-        }
-        const uint32_t vA = okA ? __ldg(pos + iA) : 0u;
-        const uint32_t vB = okB ? __ldg(pos + iB) : 0u;
-        if (resA < 0) {
-            const unsigned m = __ballot_sync(FULL, okA && (long long)vA >= keyA);
-            if (finA) resA = m ? aA + (__ffs(m) - 1) : bA;
-            else if (!m) resA = bA;
-            else { const int L = __ffs(m) - 1; const long long nb = __shfl_sync(FULL, iA, L); aA += (long long)L * sA; bA = nb; }
-        }
-        if (resB < 0) {
-            const unsigned m = __ballot_sync(FULL, okB && (long long)vB >= keyB);
-            if (finB) resB = m ? aB + (__ffs(m) - 1) : bB;
-            else if (!m) resB = bB;
-            else { const int L = __ffs(m) - 1; const long long nb = __shfl_sync(FULL, iB, L); aB += (long long)L * sB; bB = nb; }
-        }
+    WarpSearch A, B;
+    A.init((int)t0, (int)t1, keyA); B.init((int)t0, (int)t1, keyB);
+    while (A.res < 0 || B.res < 0) {
+        A.probe(lane); B.probe(lane);
+        const uint32_t vA = A.ok ? __ldg(pos + A.idx) : 0u;
+        const uint32_t vB = B.ok ? __ldg(pos + B.idx) : 0u;
+        A.update(vA); B.update(vB);
     }
+    resA = A.res; resB = B.res;
 }
 
 // cursor right after the op that first pushes it past w_end (refinement.c:141-144); the caller knows it exists
@@ -384,18 +433,45 @@ __global__ void __launch_bounds__(RW_WARPS * 32) k_refine_warp(DevReads R, DevWi
     unsigned long long n_scan = 0, n_seg = 0;
     const long long c0 = lo / IDX_READS, c1 = (hi - 1) / IDX_READS;
     for (long long cb = c0; cb <= c1; cb += 32) {
+        // 32 chunk heads at a time, then their events as ONE flat list: lane e takes event e of the concatenation
         uint4 myh = make_uint4(0u, 0u, 0xffffffffu, 0u);
         if (cb + lane <= c1) myh = __ldg(X.chunks + cb + lane);
-        const int nb = (int)min(32ll, c1 - cb + 1);
-        for (int j = 0; j < nb; ++j) {
-            uint4 seg;
-            seg.x = __shfl_sync(FULL, myh.x, j); seg.y = __shfl_sync(FULL, myh.y, j); seg.z = __shfl_sync(FULL, myh.z, j);
-            while (true) {
-                const uint32_t base = seg.x, cnt = seg.y;
-                if (STATS) { n_scan += cnt; n_seg += 1; }
-                for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
+        uint32_t incl = myh.y;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += o; }
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        if (STATS) { n_scan += total; n_seg += (unsigned long long)min(32ll, c1 - cb + 1); }
+        for (uint32_t e0 = 0; e0 < total; e0 += 32) {
+            const uint32_t e = e0 + lane;
+            // owner chunk: first lane whose inclusive count exceeds e (5-step search over the lanes' prefix)
+            int j = 0;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) { const uint32_t v = __shfl_sync(FULL, incl, j + d - 1); if (v <= e) j += d; }
+            const uint32_t jbase = __shfl_sync(FULL, myh.x, j), jincl = __shfl_sync(FULL, incl, j), jcnt = __shfl_sync(FULL, myh.y, j);
+            int code = 0, val = 0;
+            if (e < total)
+                code = event_for_window(__ldg(X.events + (size_t)jbase + (e - (jincl - jcnt))), kind, w_start, w_end, beg, lo, hi, X.rend, val);
+            const unsigned m = __ballot_sync(FULL, code == 1);
+            if (code == 1) { const int slot = n + __popc(m & below); if (slot < RW_CAP) s.sig[slot] = val; }
+            n += __popc(m);
+            const unsigned md = __ballot_sync(FULL, code == 2);
+            if (md) {
+                if (code == 2) { const int slot = nd + __popc(md & below); if (slot < RW_DEFER) s.defer[slot] = val; }
+                nd += __popc(md);
+            }
+        }
+        // chunks that flushed more than once chain older segments behind the head (rare): walk those one by one
+        unsigned chained = __ballot_sync(FULL, myh.z != 0xffffffffu);
+        while (chained) {
+            const int j = __ffs(chained) - 1;
+            chained &= chained - 1;
+            uint32_t nxt = __shfl_sync(FULL, myh.z, j);
+            while (nxt != 0xffffffffu) {
+                const uint4 seg = __ldg(X.segs + nxt);
+                if (STATS) { n_scan += seg.y; n_seg += 1; }
+                for (uint32_t e0 = 0; e0 < seg.y; e0 += 32) {
                     int code = 0, val = 0;
-                    if (e0 + lane < cnt) code = event_for_window(__ldg(X.events + (size_t)base + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);
+                    if (e0 + lane < seg.y) code = event_for_window(__ldg(X.events + (size_t)seg.x + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);
                     const unsigned m = __ballot_sync(FULL, code == 1);
                     if (code == 1) { const int slot = n + __popc(m & below); if (slot < RW_CAP) s.sig[slot] = val; }
                     n += __popc(m);
@@ -405,8 +481,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32) k_refine_warp(DevReads R, DevWi
                         nd += __popc(md);
                     }
                 }
-                if (seg.z == 0xffffffffu) break;
-                seg = __ldg(X.segs + seg.z);
+                nxt = seg.z;
             }
         }
     }

@@ -190,6 +190,47 @@ int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int w
  * receives the number of (INS)/(DEL)/(INV) lines written. */
 int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records);
 
+/* ---- K3: insertion consensus (partial-order alignment).  SVTrek builds abPOA but never calls it (no
+ * source includes abpoa.h, Makefile:32-33), so this entry has no call site in audit.c; it replaces what the
+ * north star names "abPOA for insertion consensus": abpoa_msa() with default parameters
+ * (abPOA/src/abpoa_align.c:401, abPOA/include/abpoa.h:154) on one read set per INS record.
+ * A batch is n_sets independent read sets: set s owns reads set_off[s] .. set_off[s+1], read r owns
+ * bases[seq_off[r] .. seq_off[r+1]) with abPOA's nucleotide codes A0 C1 G2 T3 other 4 (abpoa_seq.c:15).
+ * Reads are aligned in input order, as abpoa_poa does (abpoa_align.c:312).  Empty reads are an error. */
+typedef struct {
+    int32_t n_sets;
+    const int64_t *set_off;  /* [n_sets + 1] */
+    const int64_t *seq_off;  /* [n_reads + 1], seq_off[0] == 0 */
+    const uint8_t *bases;    /* [seq_off[n_reads]] */
+} svtk_poa_batch;
+
+/* optional per-read observations (host arrays of n_reads entries; any pointer may be NULL only if all are):
+ * what abpoa_res_t.best_score, abg->node_n after the read, and the alignment (expanded ops: FNV-1a hash) were. */
+typedef struct {
+    int32_t *best_score;
+    int32_t *node_n;
+    int32_t *n_ops;
+    uint64_t *ops_hash;
+    int64_t *cells;          /* band cells of the read's alignment */
+} svtk_poa_trace;
+
+typedef struct {
+    uint64_t n_sets, n_reads, n_bases;
+    uint64_t cells;          /* 5-state convex cell updates actually computed: sum of band widths over all DP rows */
+    uint64_t cells_full;     /* full-matrix equivalent: sum over reads r >= 2 of rows * (qlen + 1) */
+    uint64_t relaunched;     /* read sets that outgrew their first scratch estimate and were rerun with a larger one */
+    uint64_t workers;        /* resident warps (= CTAs) of the largest launch */
+    double kernel_ms;        /* CUDA-event time of the k_poa_sets launches on the ctx stream */
+} svtk_poa_stats;
+
+enum { SVTK_POA_OK = 0, SVTK_POA_FAILED = 1 };
+
+/* cons / cons_cov: host buffers; set s writes at most cons_off[s+1] - cons_off[s] entries at cons_off[s]
+ * (cons_cov may be NULL: abpoa_cons_t.cons_cov, abpoa.h:122).  cons_len[s] receives the full consensus length
+ * (abpoa_cons_t.cons_len) even when it exceeds the room; set_status[s] (may be NULL) is SVTK_POA_OK or SVTK_POA_FAILED. */
+int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *host_batch, uint8_t *cons, const int64_t *cons_off, int32_t *cons_len,
+                       int32_t *cons_cov, int32_t *set_status, const svtk_poa_trace *trace, svtk_poa_stats *stats);
+
 #ifdef __cplusplus
 }
 #endif

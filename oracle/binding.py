@@ -215,3 +215,48 @@ def run_ref_cli(bam, vcf, threads=1, extra=(), capture=True, timeout=3600):
         return p.stdout.decode(), p.stderr.decode()
     subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=timeout, check=True)
     return None, None
+
+
+# ------------------------------------------------------------------------------------------------------------
+# K3 oracle: the compiled, unmodified abPOA library behind oracle/poa_harness.c (oracle/_ref/libabpoa_ref.so).
+def have_abpoa():
+    return os.path.exists(os.path.join(REF_DIR, "libabpoa_ref.so"))
+
+
+_abpoa = None
+
+
+def abpoa():
+    global _abpoa
+    if _abpoa is None:
+        L = C.CDLL(os.path.join(REF_DIR, "libabpoa_ref.so"))
+        V = C.c_void_p
+        L.ref_poa_msa.argtypes = [C.c_int, V, V, V, C.c_int, V]
+        L.ref_poa_steps.argtypes = [C.c_int, V, V, V, V, V, V, V, V, C.c_int, V, C.c_int, V, C.c_int]
+        _abpoa = L
+    return _abpoa
+
+
+def ref_poa_msa(seqs):
+    """abpoa_msa (defaults) on one read set: list of uint8 code arrays -> (consensus codes, coverage)."""
+    lens = [len(s) for s in seqs]
+    off = np.zeros(len(seqs) + 1, np.int64); off[1:] = np.cumsum(lens)
+    b = np.ascontiguousarray(np.concatenate(seqs), dtype=np.uint8)
+    cap = int(off[-1]) + 8
+    cons = np.zeros(cap, np.uint8); cov = np.zeros(cap, np.int32)
+    n = abpoa().ref_poa_msa(len(seqs), off.ctypes.data, b.ctypes.data, cons.ctypes.data, cap, cov.ctypes.data)
+    return cons[:n].copy(), cov[:n].copy()
+
+
+def ref_poa_steps(seqs):
+    """The same default path read by read: consensus, coverage and per-read best_score / node_n / n_ops / ops_hash / cells."""
+    n = len(seqs)
+    lens = [len(s) for s in seqs]
+    off = np.zeros(n + 1, np.int64); off[1:] = np.cumsum(lens)
+    b = np.ascontiguousarray(np.concatenate(seqs), dtype=np.uint8)
+    cap = int(off[-1]) + 8
+    cons = np.zeros(cap, np.uint8); cov = np.zeros(cap, np.int32)
+    bs = np.zeros(n, np.int32); nn = np.zeros(n, np.int32); no = np.zeros(n, np.int32); hh = np.zeros(n, np.uint64); cc = np.zeros(n, np.int64)
+    ln = abpoa().ref_poa_steps(n, off.ctypes.data, b.ctypes.data, bs.ctypes.data, nn.ctypes.data, no.ctypes.data, hh.ctypes.data,
+                               cc.ctypes.data, cons.ctypes.data, cap, cov.ctypes.data, -1, None, 0)
+    return dict(cons=cons[:ln].copy(), cov=cov[:ln].copy(), best_score=bs, node_n=nn, n_ops=no, ops_hash=hh, cells=cc)

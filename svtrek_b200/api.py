@@ -55,10 +55,22 @@ class IndexStats(C.Structure):
                                           "n_overflow", "refine_bytes")]
 
 
+class PoaBatch(C.Structure):
+    _fields_ = [("n_sets", C.c_int32), ("set_off", C.c_void_p), ("seq_off", C.c_void_p), ("bases", C.c_void_p)]
+
+
+class PoaTrace(C.Structure):
+    _fields_ = [("best_score", C.c_void_p), ("node_n", C.c_void_p), ("n_ops", C.c_void_p), ("ops_hash", C.c_void_p), ("cells", C.c_void_p)]
+
+
+class PoaStats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("n_sets", "n_reads", "n_bases", "cells", "cells_full", "relaunched", "workers")] + [("kernel_ms", C.c_double)]
+
+
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
-           "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf"]
+           "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus"]
 
 _lib = None
 
@@ -96,6 +108,8 @@ def load_library():
     L.svtk_window_signatures.argtypes = [C.c_void_p, C.c_int, C.c_int, Interval, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
     L.svtk_sliding_window_ins.argtypes = [C.c_void_p, C.c_int, Interval, C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]
     L.svtk_process_vcf.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
+    L.svtk_poa_consensus.argtypes = [C.c_void_p, C.POINTER(PoaBatch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.POINTER(PoaTrace), C.POINTER(PoaStats)]
     _lib = L
     return L
 
@@ -272,6 +286,44 @@ class Auditor:
         _check(self.lib.svtk_sliding_window_ins(self.ctx, int(chrom), Interval(start & 0xFFFFFFFF, end & 0xFFFFFFFF), int(window_size), int(slide_size),
                                                 C.byref(best), buf, cap if want_lines else 0))
         return (best.value, buf.value.decode()) if want_lines else best.value
+
+    # ---- K3: insertion consensus (abpoa_msa, abPOA/src/abpoa_align.c:401)
+    def poa_consensus(self, set_off, seq_off, bases, cons_cap=None, want_cov=False, want_trace=False):
+        """abpoa_msa (default parameters) on every read set of the batch.  bases: uint8 codes A0 C1 G2 T3 N4.
+        Returns (list of consensus code arrays, stats dict[, coverage list][, trace dict of per-read arrays])."""
+        set_off = np.ascontiguousarray(set_off, dtype=np.int64)
+        seq_off = np.ascontiguousarray(seq_off, dtype=np.int64)
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        ns = int(set_off.shape[0] - 1)
+        n_reads = int(seq_off.shape[0] - 1)
+        if cons_cap is None:                                   # room per set: twice its longest read + 64
+            lens = np.diff(seq_off)
+            cons_cap = np.array([2 * int(lens[set_off[s]:set_off[s + 1]].max(initial=0)) + 64 for s in range(ns)], dtype=np.int64)
+        cons_off = np.zeros(ns + 1, dtype=np.int64)
+        cons_off[1:] = np.cumsum(np.asarray(cons_cap, dtype=np.int64))
+        cons = np.zeros(max(int(cons_off[-1]), 1), dtype=np.uint8)
+        cov = np.zeros(max(int(cons_off[-1]), 1), dtype=np.int32) if want_cov else None
+        clen = np.zeros(max(ns, 1), dtype=np.int32)
+        status = np.zeros(max(ns, 1), dtype=np.int32)
+        b = PoaBatch(ns, set_off.ctypes.data, seq_off.ctypes.data, bases.ctypes.data)
+        st = PoaStats()
+        tr = None
+        tra = {}
+        if want_trace:
+            tra = dict(best_score=np.zeros(max(n_reads, 1), np.int32), node_n=np.zeros(max(n_reads, 1), np.int32), n_ops=np.zeros(max(n_reads, 1), np.int32),
+                       ops_hash=np.zeros(max(n_reads, 1), np.uint64), cells=np.zeros(max(n_reads, 1), np.int64))
+            tr = PoaTrace(*[tra[k].ctypes.data for k in ("best_score", "node_n", "n_ops", "ops_hash", "cells")])
+        _check(self.lib.svtk_poa_consensus(self.ctx, C.byref(b), cons.ctypes.data, cons_off.ctypes.data, clen.ctypes.data,
+                                           cov.ctypes.data if want_cov else None, status.ctypes.data, C.byref(tr) if tr else None, C.byref(st)))
+        if ns and (clen[:ns] > np.diff(cons_off)).any():       # a consensus longer than its room: rerun with the reported lengths
+            return self.poa_consensus(set_off, seq_off, bases, cons_cap=np.maximum(clen[:ns], 1) + 8, want_cov=want_cov, want_trace=want_trace)
+        out = [cons[cons_off[s]:cons_off[s] + clen[s]].copy() for s in range(ns)]
+        res = [out, {k: (getattr(st, k)) for k, _ in PoaStats._fields_}]
+        if want_cov:
+            res.append([cov[cons_off[s]:cons_off[s] + clen[s]].copy() for s in range(ns)])
+        if want_trace:
+            res.append({k: v[:n_reads] for k, v in tra.items()})
+        return tuple(res)
 
     # ---- whole path (audit.c:250 process_vcf)
     def process_vcf(self, vcf_path, out_path):

@@ -57,7 +57,7 @@ int PinBuf::reserve(size_t bytes) {
 void PinBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 
 // host (pageable) -> device through two pinned staging buffers so the CPU copy of chunk k+1 overlaps the DMA of chunk k
-static int upload(Ctx *c, void *dst, const void *src, size_t bytes) {
+int upload(Ctx *c, void *dst, const void *src, size_t bytes) {
     if (bytes == 0) return 0;
     {   // caller's buffer already page-locked (cudaHostAlloc / cudaHostRegister): DMA straight from it
         cudaPointerAttributes at;
@@ -86,7 +86,7 @@ static int upload(Ctx *c, void *dst, const void *src, size_t bytes) {
     return 0;
 }
 
-static int set_device(Ctx *c) {
+int set_device(Ctx *c) {
     CU(cudaSetDevice(c->device));
     return 0;
 }
@@ -332,9 +332,11 @@ void svtk_destroy(svtk_ctx *ctx) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items, &c->ov_count,
-                      &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c})
+                      &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
+                      &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl})
         b->release();
-    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result}) b->release();
+    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
+    for (int i = 0; i < 2; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);

@@ -68,11 +68,19 @@ struct Ctx {
     uint64_t launches = 0;
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
 
+    // K3 (svtk_poa.cu): device copies of one batch of read sets, per-worker scratch, events
+    DevBuf poa_in, poa_out, poa_scratch, poa_ctl;
+    PinBuf poa_h;
+    cudaEvent_t poa_ev[2] = {nullptr, nullptr};
+
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;
     cudaEvent_t prof_ev[4] = {nullptr, nullptr, nullptr, nullptr};     // [0,1] refine kernel, [2,3] index kernel
     double refine_ms = 0.0, index_ms = 0.0;
     uint64_t refine_launches = 0, index_launches = 0;
 };
+
+int upload(Ctx *c, void *dst, const void *src, size_t bytes);   // host -> device on the ctx stream (pinned staging)
+int set_device(Ctx *c);
 
 }  // namespace svtk

@@ -1,0 +1,329 @@
+// svtk_poa.cu -- K3 on the device: k_poa_sets (one warp-sized CTA per read set, persistent workers pulling
+// sets from an atomic queue) and the host driver behind svtk_poa_consensus (include/svtk.h).
+//
+// Work unit = one INS record's read set (abpoa_msa, abPOA/src/abpoa_align.c:401).  Sets are independent, reads
+// inside a set are strictly sequential (the graph grows), so the device is filled with sets, not with cells of
+// one alignment: up to 32 resident CTAs per SM x 148 SMs read sets are in flight, each warp alternating between
+// its column-parallel row DP and its lane-0 graph phases (svtk_poa_core.cuh) while the other warps of the SM
+// hide the latency.  Every worker owns one scratch block in HBM (graph SoA, edge pool, band-only DP rows with
+// all five score planes for the backtrack, cigar); blocks are sized per size class (read sets binned by
+// ceil(log2(longest read))) so that a 100 bp set does not reserve a 10 kb set's 200 MB.  A set that outgrows
+// its estimate reports which resource ran out and is rerun with a larger block -- never silently truncated.
+#include "svtk_ctx.h"
+#include "svtk_poa_core.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace svtk {
+
+using namespace svtk_poa;
+
+struct PoaCaps {
+    int node_cap, edge_cap, cigar_cap;
+    long long cell_bytes;
+};
+
+// layout of one worker's scratch block (byte offsets, 16-byte aligned sections)
+struct PoaLayout {
+    long long base, ints, row_off, edge_id, edge_w, cigar, cells, total;
+};
+constexpr int POA_INT_ARRAYS = 17 + ALN_MAX;
+
+__host__ __device__ inline long long a16(long long x) { return (x + 15) & ~15ll; }
+__host__ __device__ inline PoaLayout poa_layout(const PoaCaps &c) {
+    PoaLayout L;
+    long long o = 0;
+    L.base = o; o = a16(o + c.node_cap);
+    L.ints = o; o = a16(o + 4ll * POA_INT_ARRAYS * c.node_cap);
+    L.row_off = o; o = a16(o + 8ll * c.node_cap);
+    L.edge_id = o; o = a16(o + 4ll * c.edge_cap);
+    L.edge_w = o; o = a16(o + 4ll * c.edge_cap);
+    L.cigar = o; o = a16(o + 8ll * c.cigar_cap);
+    L.cells = o; o = a16(o + c.cell_bytes);
+    L.total = (o + 255) & ~255ll;
+    return L;
+}
+
+struct PoaLaunch {
+    int n_items;
+    const int *items;                  // read-set ids of this launch, heaviest first
+    int *next;                         // atomic cursor into items
+    const long long *set_off, *seq_off;
+    const uint8_t *bases;
+    uint8_t *cons;
+    int32_t *cov;                      // may be null
+    const long long *cons_off;
+    int32_t *cons_len, *status;
+    unsigned long long *cells;         // [0] band cells, [1] full-matrix equivalent
+    unsigned char *scratch;
+    PoaCaps caps;
+    PoaTrace trace;
+    int have_trace;
+};
+
+__global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
+    __shared__ PoaState s;
+    __shared__ int s_item;
+    const int lane = threadIdx.x;
+    if (lane == 0) {
+        const PoaLayout lay = poa_layout(L.caps);
+        unsigned char *blk = L.scratch + (long long)blockIdx.x * lay.total;
+        const int N = L.caps.node_cap;
+        s.node_cap = N; s.edge_cap = L.caps.edge_cap; s.cigar_cap = L.caps.cigar_cap; s.cell_bytes = L.caps.cell_bytes;
+        s.base = blk + lay.base;
+        int *p = reinterpret_cast<int *>(blk + lay.ints);
+        s.in_off = p; p += N; s.in_n = p; p += N; s.in_cap = p; p += N; s.out_off = p; p += N; s.out_n = p; p += N; s.out_cap = p; p += N;
+        s.aln_n = p; p += N; s.aln_id = p; p += (long long)ALN_MAX * N; s.n_read = p; p += N;
+        s.idx2id = p; p += N; s.id2idx = p; p += N; s.max_left = p; p += N; s.max_right = p; p += N; s.remain = p; p += N;
+        s.deg = p; p += N; s.queue = p; p += N; s.dp_beg = p; p += N; s.dp_end = p; p += N;
+        s.row_off = reinterpret_cast<long long *>(blk + lay.row_off);
+        s.edge_id = reinterpret_cast<int *>(blk + lay.edge_id);
+        s.edge_w = reinterpret_cast<int *>(blk + lay.edge_w);
+        s.cigar = reinterpret_cast<int2 *>(blk + lay.cigar);
+        s.cells = blk + lay.cells;
+    }
+    __syncwarp();
+    while (true) {
+        if (lane == 0) s_item = atomicAdd(L.next, 1);
+        __syncwarp();
+        const int it = s_item;
+        __syncwarp();
+        if (it >= L.n_items) break;
+        const int sv = L.items[it];
+        const long long co = L.cons_off[sv];
+        const int cap = (int)(L.cons_off[sv + 1] - co);
+        const int len = poa_run_set(s, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
+                                    L.have_trace ? &L.trace : nullptr);
+        if (lane == 0) {
+            L.status[sv] = s.status;
+            L.cons_len[sv] = len;
+            if (!s.status) { atomicAdd(&L.cells[0], (unsigned long long)s.cells_done); atomicAdd(&L.cells[1], (unsigned long long)s.cells_full); }
+        }
+        __syncwarp();
+    }
+}
+
+#define CU(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t e_ = (call);                                                                              \
+        if (e_ != cudaSuccess) return fail(SVTK_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct SetInfo {
+    int id, n, maxlen, minlen, cls;
+    long long total;
+    double work;
+};
+
+static PoaCaps caps_for(const SetInfo &si, double scale) {
+    PoaCaps c;
+    const long long worst_nodes = si.total + 2;
+    long long nodes = (long long)(scale * 5.0 * si.maxlen) + 256;
+    if (nodes > worst_nodes) nodes = worst_nodes;
+    if (nodes < 8) nodes = 8;
+    c.node_cap = (int)nodes;
+    c.edge_cap = (int)std::min<long long>(8 * nodes + 4ll * si.n + 1024, 0x7fffffffll);
+    c.cigar_cap = (int)std::min<long long>(nodes + si.maxlen + 16, 0x7fffffffll);
+    const int w = EXTRA_B + (int)(EXTRA_F * (float)si.maxlen);
+    long long width = (long long)(scale * (2 * w + 64 + (si.maxlen - si.minlen)));
+    if (width > si.maxlen + 1) width = si.maxlen + 1;
+    const long long len = std::max<long long>(si.maxlen, nodes);
+    const int sc_bytes = (std::max<long long>(si.maxlen * MATCH, len * GAP_E1 + GAP_O1) <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2) ? 2 : 4;
+    c.cell_bytes = a16(nodes * width * 5 * sc_bytes);
+    return c;
+}
+
+static PoaCaps caps_max(const PoaCaps &a, const PoaCaps &b) {
+    PoaCaps c;
+    c.node_cap = std::max(a.node_cap, b.node_cap); c.edge_cap = std::max(a.edge_cap, b.edge_cap);
+    c.cigar_cap = std::max(a.cigar_cap, b.cigar_cap); c.cell_bytes = std::max(a.cell_bytes, b.cell_bytes);
+    return c;
+}
+
+}  // namespace svtk
+
+using namespace svtk;
+
+extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_t *cons, const int64_t *cons_off, int32_t *cons_len,
+                                  int32_t *cons_cov, int32_t *set_status, const svtk_poa_trace *trace, svtk_poa_stats *stats) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !b || !cons || !cons_off || !cons_len) return fail(SVTK_ERR_ARG, "null argument");
+    if (b->n_sets < 0 || (b->n_sets > 0 && (!b->set_off || !b->seq_off || !b->bases))) return fail(SVTK_ERR_ARG, "bad poa batch");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    const int ns = b->n_sets;
+    if (ns == 0) return 0;
+    if (int rc = set_device(c)) return rc;
+    const long long n_reads = b->set_off[ns];
+    if (b->set_off[0] != 0 || n_reads < 0) return fail(SVTK_ERR_ARG, "poa batch: set_off must start at 0");
+    if (b->seq_off[0] != 0) return fail(SVTK_ERR_ARG, "poa batch: seq_off must start at 0");
+    const long long n_bases = b->seq_off[n_reads];
+    if (trace && !(trace->best_score && trace->node_n && trace->n_ops && trace->ops_hash && trace->cells))
+        return fail(SVTK_ERR_ARG, "poa trace: all five arrays are required");
+
+    std::vector<SetInfo> info(ns);
+    for (int s = 0; s < ns; ++s) {
+        SetInfo &si = info[s];
+        si.id = s; si.n = (int)(b->set_off[s + 1] - b->set_off[s]); si.maxlen = 0; si.minlen = 0x7fffffff; si.total = 0;
+        if (si.n < 0) return fail(SVTK_ERR_ARG, "poa batch: set_off not monotone at set %d", s);
+        if (cons_off[s + 1] < cons_off[s]) return fail(SVTK_ERR_ARG, "cons_off not monotone at set %d", s);
+        double work = 0;
+        for (long long r = b->set_off[s]; r < b->set_off[s + 1]; ++r) {
+            const long long l = b->seq_off[r + 1] - b->seq_off[r];
+            if (l <= 0 || l > (1 << 28)) return fail(SVTK_ERR_ARG, "poa batch: read %lld of set %d has length %lld (must be 1 .. 2^28)", r, s, l);
+            si.maxlen = std::max(si.maxlen, (int)l); si.minlen = std::min(si.minlen, (int)l); si.total += l;
+            work += (double)l;
+        }
+        if (si.n == 0) { si.minlen = 0; }
+        si.work = work * std::max(si.maxlen, 1);
+        int cls = 0;
+        while ((1 << cls) < std::max(si.maxlen, 1)) ++cls;
+        si.cls = cls;
+    }
+    const long long cons_total = cons_off[ns] - cons_off[0];
+    if (cons_off[0] != 0) return fail(SVTK_ERR_ARG, "cons_off must start at 0");
+
+    // ---- device copies of the batch and of the outputs
+    const size_t in_bytes = a16(8 * (ns + 1)) + a16(8 * (n_reads + 1)) + a16(n_bases) + a16(8 * (ns + 1));
+    if (int rc = c->poa_in.reserve(in_bytes)) return rc;
+    unsigned char *din = (unsigned char *)c->poa_in.p;
+    long long *d_set_off = (long long *)din; din += a16(8 * (ns + 1));
+    long long *d_seq_off = (long long *)din; din += a16(8 * (n_reads + 1));
+    uint8_t *d_bases = din; din += a16(n_bases);
+    long long *d_cons_off = (long long *)din;
+    if (int rc = upload(c, d_set_off, b->set_off, 8 * (size_t)(ns + 1))) return rc;
+    if (int rc = upload(c, d_seq_off, b->seq_off, 8 * (size_t)(n_reads + 1))) return rc;
+    if (int rc = upload(c, d_bases, b->bases, (size_t)n_bases)) return rc;
+    if (int rc = upload(c, d_cons_off, cons_off, 8 * (size_t)(ns + 1))) return rc;
+    c->h2d_bytes += 16ull * (ns + 1) + 8ull * (n_reads + 1) + (uint64_t)n_bases;
+
+    const size_t tr_bytes = trace ? (size_t)(a16(4 * n_reads) * 3 + a16(8 * n_reads) * 2) : 0;
+    const size_t out_bytes = a16(cons_total) + (cons_cov ? a16(4 * cons_total) : 0) + a16(4 * ns) * 2 + tr_bytes + 64;
+    if (int rc = c->poa_out.reserve(out_bytes)) return rc;
+    unsigned char *dout = (unsigned char *)c->poa_out.p;
+    uint8_t *d_cons = dout; dout += a16(cons_total);
+    int32_t *d_cov = nullptr;
+    if (cons_cov) { d_cov = (int32_t *)dout; dout += a16(4 * cons_total); }
+    int32_t *d_len = (int32_t *)dout; dout += a16(4 * ns);
+    int32_t *d_status = (int32_t *)dout; dout += a16(4 * ns);
+    PoaTrace tr{};
+    tr.dump_read = -1;
+    if (trace) {
+        tr.best_score = (int32_t *)dout; dout += a16(4 * n_reads);
+        tr.node_n = (int32_t *)dout; dout += a16(4 * n_reads);
+        tr.n_ops = (int32_t *)dout; dout += a16(4 * n_reads);
+        tr.ops_hash = (uint64_t *)dout; dout += a16(8 * n_reads);
+        tr.cells = (long long *)dout; dout += a16(8 * n_reads);
+        CU(cudaMemsetAsync(tr.best_score, 0, tr_bytes, c->stream));
+    }
+    CU(cudaMemsetAsync(d_len, 0, a16(4 * ns) * 2, c->stream));
+
+    // control block: cells[2], then per launch one cursor, then the item lists
+    const size_t ctl_bytes = 64 + 4 * 64 + 4 * (size_t)ns;
+    if (int rc = c->poa_ctl.reserve(ctl_bytes)) return rc;
+    unsigned long long *d_cells = (unsigned long long *)c->poa_ctl.p;
+    int *d_cursors = (int *)((unsigned char *)c->poa_ctl.p + 64);
+    int *d_items = d_cursors + 64;
+    for (int i = 0; i < 2; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
+
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    const long long budget = (long long)(0.85 * (double)(free_b + c->poa_scratch.cap));
+
+    std::vector<int> todo;
+    for (int s = 0; s < ns; ++s) if (info[s].n > 0) todo.push_back(s);
+    std::vector<int32_t> h_status(ns, 0);
+    double scale = 1.0, kernel_ms = 0.0;
+    uint64_t relaunched = 0, max_workers = 0;
+    CU(cudaMemsetAsync(d_cells, 0, 64, c->stream));
+    int max_resident = 148 * 32;
+    {
+        int dev_sms = 0;
+        if (cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, c->device) == cudaSuccess && dev_sms > 0) max_resident = dev_sms * 32;
+    }
+    for (int attempt = 0; attempt < 4 && !todo.empty(); ++attempt) {
+        // classes, largest reads first; inside a class heaviest set first (the atomic queue then balances the tail)
+        std::sort(todo.begin(), todo.end(), [&](int x, int y) {
+            if (info[x].cls != info[y].cls) return info[x].cls > info[y].cls;
+            if (info[x].work != info[y].work) return info[x].work > info[y].work;
+            return x < y;
+        });
+        CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemsetAsync(d_cursors, 0, 4 * 64, c->stream));
+        CU(cudaStreamSynchronize(c->stream));      // todo is reused below; the copy above must have read it
+        size_t i0 = 0;
+        int launch_no = 0;
+        while (i0 < todo.size()) {
+            size_t i1 = i0;
+            PoaCaps caps = caps_for(info[todo[i0]], scale);
+            while (i1 < todo.size() && info[todo[i1]].cls == info[todo[i0]].cls) { caps = caps_max(caps, caps_for(info[todo[i1]], scale)); ++i1; }
+            const PoaLayout lay = poa_layout(caps);
+            long long workers = std::min<long long>((long long)(i1 - i0), max_resident);
+            if (lay.total > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", lay.total, budget);
+            workers = std::min(workers, budget / lay.total);
+            if (int rc = c->poa_scratch.reserve((size_t)(workers * lay.total))) return rc;
+            PoaLaunch L{};
+            L.n_items = (int)(i1 - i0); L.items = d_items + i0; L.next = d_cursors + (launch_no % 64);
+            L.set_off = d_set_off; L.seq_off = d_seq_off; L.bases = d_bases; L.cons = d_cons; L.cov = d_cov; L.cons_off = d_cons_off;
+            L.cons_len = d_len; L.status = d_status; L.cells = d_cells; L.scratch = (unsigned char *)c->poa_scratch.p; L.caps = caps;
+            L.trace = tr; L.have_trace = trace ? 1 : 0;
+            if (launch_no >= 64) { CU(cudaMemsetAsync(d_cursors + (launch_no % 64), 0, 4, c->stream)); }
+            CU(cudaEventRecord(c->poa_ev[0], c->stream));
+            k_poa_sets<<<(unsigned)workers, 32, 0, c->stream>>>(L);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(c->poa_ev[1], c->stream));
+            // the scratch buffer may be re-reserved (freed) by the next class: wait for this launch first
+            CU(cudaEventSynchronize(c->poa_ev[1]));
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
+            kernel_ms += ms;
+            c->launches += 1;
+            max_workers = std::max<uint64_t>(max_workers, (uint64_t)workers);
+            ++launch_no;
+            i0 = i1;
+        }
+        CU(cudaMemcpyAsync(h_status.data(), d_status, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        std::vector<int> again;
+        for (int s : todo) {
+            const int st = h_status[s];
+            if (st == POA_ERR_NODES || st == POA_ERR_EDGES || st == POA_ERR_CELLS || st == POA_ERR_CIGAR) again.push_back(s);
+        }
+        relaunched += again.size();
+        todo.swap(again);
+        scale *= 4.0;
+    }
+
+    // ---- results back
+    std::vector<int32_t> h_len(ns);
+    CU(cudaMemcpyAsync(h_len.data(), d_len, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(cons, d_cons, (size_t)cons_total, cudaMemcpyDeviceToHost, c->stream));
+    if (cons_cov) CU(cudaMemcpyAsync(cons_cov, d_cov, 4 * (size_t)cons_total, cudaMemcpyDeviceToHost, c->stream));
+    if (trace) {
+        CU(cudaMemcpyAsync(trace->best_score, tr.best_score, 4 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(trace->node_n, tr.node_n, 4 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(trace->n_ops, tr.n_ops, 4 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(trace->ops_hash, tr.ops_hash, 8 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(trace->cells, tr.cells, 8 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
+    }
+    unsigned long long h_cells[2] = {0, 0};
+    CU(cudaMemcpyAsync(h_cells, d_cells, 16, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->d2h_bytes += (uint64_t)cons_total * (cons_cov ? 5 : 1) + 8ull * ns;
+    int n_failed = 0, first_failed = -1, first_code = 0;
+    for (int s = 0; s < ns; ++s) {
+        const bool bad = h_status[s] != POA_OK;
+        cons_len[s] = bad ? 0 : h_len[s];
+        if (set_status) set_status[s] = bad ? SVTK_POA_FAILED : SVTK_POA_OK;
+        if (bad) { if (!n_failed) { first_failed = s; first_code = h_status[s]; } ++n_failed; }
+    }
+    if (stats) {
+        stats->n_sets = (uint64_t)ns; stats->n_reads = (uint64_t)n_reads; stats->n_bases = (uint64_t)n_bases;
+        stats->cells = h_cells[0]; stats->cells_full = h_cells[1]; stats->relaunched = relaunched; stats->workers = max_workers;
+        stats->kernel_ms = kernel_ms;
+    }
+    if (n_failed) return fail(SVTK_ERR_STATE, "poa: %d read set(s) failed, first set %d with internal code %d", n_failed, first_failed, first_code);
+    return 0;
+}

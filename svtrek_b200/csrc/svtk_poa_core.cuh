@@ -1,0 +1,635 @@
+// svtk_poa_core.cuh -- K3: insertion consensus by partial-order alignment, equivalent to abPOA's default
+// abpoa_msa() path (reference submodule abPOA/ v1.5.4):
+//     abpoa_msa                abpoa_align.c:401        -> abpoa_poa :312  (no seeding, reads in input order)
+//     alignment                abpoa_align_simd.c:1250  convex gap (4,2 / 24,1), match 2, mismatch 4, global,
+//                              adaptive band w = 10 + (int)(0.01f * qlen)        (:474, abpoa_align.h:34-35)
+//         first row            :669-688     row DP :935-1074     row arg-max -> band hints :1107-1130
+//         best end cell        :1092-1105   backtrack :309-458 (M -> E1 -> E2 -> F1 -> F2 -> M, cur_op machine)
+//     graph fusion             abpoa_graph.c:688-773    add node/edge :477-553, aligned groups :450-465
+//     topological sort         abpoa_graph.c:322        BFS index :221-266, exchange sort of edges :192-219,
+//                              max_remain reverse BFS :268-309
+//     consensus                abpoa_output.c:477-547   heaviest bundling, walk from SRC :375-391
+//
+// Execution model: ONE WARP OWNS ONE READ SET (a CTA of 32 threads per SV record).  The row DP is column
+// parallel across the 32 lanes -- 32 cells of the five-state convex recurrence per step, the two in-row gap
+// states (F1/F2) by a 5-step shuffle prefix-max, row arg-max by warp reductions -- and the pointer-chasing
+// phases (backtrack, graph fusion, the two BFS passes, bundling) run on lane 0 while many other warps of the
+// SM are in their DP phase.  abPOA's SIMD vectors are a storage detail of the CPU code: this file implements
+// the vector-width-1 semantics (cells outside a row's band read as inf_min), which is what every real-valued
+// cell of abPOA computes; SURVEY 7.3-6 measured the four CPU vector widths to agree on the same inputs.
+//
+// The same source compiles as plain C++ with POA_HOSTSIM defined (warp width 1): tests/ build that variant
+// to exercise the algorithm against the abPOA golden vectors on machines without a GPU.  It is a test build
+// of this file, not a product path: libsvtk_b200.so contains only the device instantiation.
+#pragma once
+#include <stdint.h>
+
+#ifdef POA_HOSTSIM
+#define PD static inline
+#define POA_NL 1
+static inline int poa_lane() { return 0; }
+static inline void poa_sync() {}
+static inline int poa_shfl(int v, int) { return v; }
+static inline long long poa_shfl_ll(long long v, int) { return v; }
+static inline int poa_shfl_up(int v, int) { return v; }
+static inline int poa_max_all(int v) { return v; }
+static inline int poa_min_all(int v) { return v; }
+#else
+#define PD __device__ __forceinline__
+#define POA_NL 32
+PD int poa_lane() { return threadIdx.x & 31; }
+PD void poa_sync() { __syncwarp(); }
+PD int poa_shfl(int v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+PD long long poa_shfl_ll(long long v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+PD int poa_shfl_up(int v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
+PD int poa_max_all(int v) { return __reduce_max_sync(0xffffffffu, v); }
+PD int poa_min_all(int v) { return __reduce_min_sync(0xffffffffu, v); }
+#endif
+
+namespace svtk_poa {
+
+// abPOA defaults: abpoa_align.h:9-14, abpoa.h:16-17, abpoa_align.c:100-157
+constexpr int MATCH = 2, MISMATCH = 4, GAP_O1 = 4, GAP_E1 = 2, GAP_O2 = 24, GAP_E2 = 1;
+constexpr int GAP_OE1 = GAP_O1 + GAP_E1, GAP_OE2 = GAP_O2 + GAP_E2;
+constexpr int EXTRA_B = 10;
+constexpr float EXTRA_F = 0.01f;
+constexpr int SRC = 0, SINK = 1;                              // abpoa.h:31-32
+constexpr int OP_M = 1, OP_E1 = 2, OP_E2 = 4, OP_E = 6, OP_F1 = 8, OP_F2 = 16, OP_F = 24, OP_ALL = 31;   // abpoa_align.h:20-27
+constexpr int CG_MATCH = 0, CG_INS = 1, CG_DEL = 2;           // abpoa.h:20-22
+constexpr int ALN_MAX = 4;                                    // an aligned group holds distinct bases: <= 5 nodes (m = 5)
+
+enum { POA_OK = 0, POA_ERR_NODES = 1, POA_ERR_EDGES = 2, POA_ERR_CELLS = 3, POA_ERR_CIGAR = 4, POA_ERR_BACKTRACK = 5,
+       POA_ERR_BAND = 6, POA_ERR_BFS = 7, POA_ERR_CONS = 8, POA_ERR_INPUT = 9 };
+
+// inf_min of the two score widths (abpoa_align_simd.c:1293-1299)
+constexpr int INF_MIN16 = -32768 + 25 + 512 * 2;
+constexpr int INF_MIN32 = (-2147483647 - 1) + 25 + 512 * 2;
+
+struct PoaState {
+    // capacities of this worker's scratch
+    int node_cap, edge_cap, cigar_cap;
+    long long cell_bytes;
+    // graph (abpoa_node_t / abpoa_graph_t, abpoa.h:89-110) as SoA
+    int node_n, edge_top;
+    uint8_t *base;
+    int *in_off, *in_n, *in_cap, *out_off, *out_n, *out_cap;   // edge lists live in the pool below
+    int *edge_id, *edge_w;
+    int *aln_n, *aln_id;                                       // aligned_node_id, ALN_MAX per node
+    int *n_read;
+    int *idx2id, *id2idx, *max_left, *max_right, *remain;      // index_to_node_id, node_id_to_index, max_pos_left/right, max_remain
+    int *deg, *queue;                                          // BFS scratch
+    // one alignment
+    int *dp_beg, *dp_end;
+    long long *row_off;                                        // first cell of each row's band (in cells)
+    unsigned char *cells;                                      // rows x band x {H, E1, E2, F1, F2}, int16 or int32
+    int2 *cigar;
+    int n_cigar;
+    int best_score, best_i, best_j;
+    long long cells_done, cells_full;                          // band cells / full-matrix-equivalent cells of this read set
+    int status;
+};
+
+PD int poa_score(int node_base, int q) { return (node_base > 3 || q > 3) ? 0 : (node_base == q ? MATCH : -MISMATCH); }   // gen_simple_mat, abpoa_align.c:12-25
+PD int imax(int a, int b) { return a > b ? a : b; }
+PD int imin(int a, int b) { return a < b ? a : b; }
+
+// ----------------------------------------------------------------------------------------------- graph (lane 0)
+PD int poa_add_node(PoaState &s, uint8_t b) {                 // abpoa_add_graph_node, abpoa_graph.c:468
+    if (s.node_n >= s.node_cap) { s.status = POA_ERR_NODES; return -1; }
+    const int id = s.node_n++;
+    s.base[id] = b;
+    s.in_n[id] = s.out_n[id] = s.in_cap[id] = s.out_cap[id] = s.in_off[id] = s.out_off[id] = 0;
+    s.aln_n[id] = 0; s.n_read[id] = 0;
+    return id;
+}
+
+PD bool poa_grow(PoaState &s, int *off, int *n, int *cap, int id) {
+    if (n[id] < cap[id]) return true;
+    const int nc = cap[id] ? cap[id] * 2 : 2;
+    if (s.edge_top + nc > s.edge_cap) { s.status = POA_ERR_EDGES; return false; }
+    const int no = s.edge_top;
+    s.edge_top += nc;
+    for (int k = 0; k < n[id]; ++k) { s.edge_id[no + k] = s.edge_id[off[id] + k]; s.edge_w[no + k] = s.edge_w[off[id] + k]; }
+    off[id] = no; cap[id] = nc;
+    return true;
+}
+
+PD void poa_add_edge(PoaState &s, int from, int to, int check, int w) {   // abpoa_add_graph_edge, abpoa_graph.c:477
+    bool exist = false;
+    if (check) {
+        for (int i = 0; i < s.in_n[to]; ++i)
+            if (s.edge_id[s.in_off[to] + i] == from) { s.edge_w[s.in_off[to] + i] += w; break; }
+        for (int i = 0; i < s.out_n[from]; ++i)
+            if (s.edge_id[s.out_off[from] + i] == to) { s.edge_w[s.out_off[from] + i] += w; exist = true; break; }
+    }
+    if (!exist) {
+        if (!poa_grow(s, s.in_off, s.in_n, s.in_cap, to)) return;
+        s.edge_id[s.in_off[to] + s.in_n[to]] = from; s.edge_w[s.in_off[to] + s.in_n[to]] = w; ++s.in_n[to];
+        if (!poa_grow(s, s.out_off, s.out_n, s.out_cap, from)) return;
+        s.edge_id[s.out_off[from] + s.out_n[from]] = to; s.edge_w[s.out_off[from] + s.out_n[from]] = w; ++s.out_n[from];
+    }
+    s.n_read[from] += 1;
+}
+
+PD void poa_aln_push(PoaState &s, int node, int other) {
+    if (s.aln_n[node] < ALN_MAX) s.aln_id[node * ALN_MAX + s.aln_n[node]++] = other;
+    else s.status = POA_ERR_NODES;
+}
+
+PD void poa_add_aligned(PoaState &s, int node_id, int new_id) {            // abpoa_add_graph_aligned_node, abpoa_graph.c:450
+    const int n = s.aln_n[node_id];
+    for (int i = 0; i < n; ++i) {
+        const int a = s.aln_id[node_id * ALN_MAX + i];
+        poa_aln_push(s, a, new_id);
+        poa_aln_push(s, new_id, a);
+    }
+    poa_aln_push(s, node_id, new_id);
+    poa_aln_push(s, new_id, node_id);
+}
+
+// BFS index (abpoa_BFS_set_node_index, abpoa_graph.c:221): FIFO Kahn order, a node enters the queue together with its
+// aligned group once every member has in-degree 0.  Uses the out-edge order BEFORE this round's edge sort.
+PD void poa_bfs_index(PoaState &s) {
+    int head = 0, tail = 0, index = 0;
+    s.queue[tail++] = SRC;
+    while (head < tail) {
+        const int cur = s.queue[head++];
+        s.idx2id[index] = cur; s.id2idx[cur] = index++;
+        if (cur == SINK) { if (index != s.node_n) s.status = POA_ERR_BFS; return; }
+        const int no = s.out_n[cur], oo = s.out_off[cur];
+        for (int i = 0; i < no; ++i) {
+            const int o = s.edge_id[oo + i];
+            if (--s.deg[o] == 0) {
+                bool ok = true;
+                const int na = s.aln_n[o];
+                for (int j = 0; j < na; ++j) if (s.deg[s.aln_id[o * ALN_MAX + j]] != 0) { ok = false; break; }
+                if (!ok) continue;
+                if (tail + 1 + na > s.node_cap) { s.status = POA_ERR_BFS; return; }
+                s.queue[tail++] = o;
+                for (int j = 0; j < na; ++j) s.queue[tail++] = s.aln_id[o * ALN_MAX + j];
+            }
+        }
+    }
+    s.status = POA_ERR_BFS;
+}
+
+// descending exchange sort of one edge list, swap sequence as in abpoa_sort_in_out_ids (abpoa_graph.c:192-219):
+// not stable, and applied to the order the previous rounds left behind -- tie order decides the backtrack's choices
+PD void poa_sort_edges(int *id, int *w, int n) {
+    for (int j = 0; j < n - 1; ++j)
+        for (int k = j + 1; k < n; ++k)
+            if (w[j] < w[k]) { int t = id[j]; id[j] = id[k]; id[k] = t; t = w[j]; w[j] = w[k]; w[k] = t; }
+}
+
+PD void poa_bfs_remain(PoaState &s) {                          // abpoa_BFS_set_node_remain, abpoa_graph.c:268
+    int head = 0, tail = 0;
+    s.queue[tail++] = SINK;
+    s.remain[SINK] = -1;
+    while (head < tail) {
+        const int cur = s.queue[head++];
+        if (cur != SINK) {
+            int max_w = -1, max_id = -1;
+            for (int i = 0; i < s.out_n[cur]; ++i)
+                if (s.edge_w[s.out_off[cur] + i] > max_w) { max_w = s.edge_w[s.out_off[cur] + i]; max_id = s.edge_id[s.out_off[cur] + i]; }
+            if (max_id < 0) { s.status = POA_ERR_BFS; return; }
+            s.remain[cur] = s.remain[max_id] + 1;
+        }
+        if (cur == SRC) return;
+        for (int i = 0; i < s.in_n[cur]; ++i) {
+            const int in = s.edge_id[s.in_off[cur] + i];
+            if (--s.deg[in] == 0) s.queue[tail++] = in;
+        }
+    }
+    s.status = POA_ERR_BFS;
+}
+
+// abpoa_topological_sort (abpoa_graph.c:322): all lanes enter
+PD void poa_topological_sort(PoaState &s) {
+    const int lane = poa_lane();
+    poa_sync();
+    const int n = s.node_n;
+    for (int i = lane; i < n; i += POA_NL) s.deg[i] = s.in_n[i];
+    poa_sync();
+    if (lane == 0) poa_bfs_index(s);
+    poa_sync();
+    if (s.status) return;
+    for (int i = lane; i < n; i += POA_NL) {                   // independent per node: lanes take nodes
+        poa_sort_edges(s.edge_id + s.in_off[i], s.edge_w + s.in_off[i], s.in_n[i]);
+        poa_sort_edges(s.edge_id + s.out_off[i], s.edge_w + s.out_off[i], s.out_n[i]);
+        s.max_right[i] = 0; s.max_left[i] = n;
+        s.deg[i] = s.out_n[i]; s.remain[i] = 0;
+    }
+    poa_sync();
+    if (lane == 0) poa_bfs_remain(s);
+    poa_sync();
+}
+
+// first read: abpoa_add_graph_sequence (abpoa_graph.c:555).  lane 0
+PD void poa_add_first(PoaState &s, const uint8_t *q, int qlen) {
+    int last = SRC;
+    for (int i = 0; i < qlen; ++i) {
+        const int cur = poa_add_node(s, q[i]);
+        if (cur < 0) return;
+        poa_add_edge(s, last, cur, 0, 1);
+        if (s.status) return;
+        last = cur;
+    }
+    poa_add_edge(s, last, SINK, 0, 1);
+}
+
+// abpoa_add_subgraph_alignment (abpoa_graph.c:688) with beg = SRC, end = SINK, inc_both_ends = 1, all weights 1.
+// The cigar is in backtrack order (last op first); ops are consumed from the back.  lane 0
+PD void poa_add_alignment(PoaState &s, const uint8_t *q, int qlen) {
+    if (s.n_cigar == 0) return;                                // abpoa_graph.c:706-709
+    int query_id = -1, last_new = 0, last_id = SRC;
+    for (int c = s.n_cigar - 1; c >= 0; --c) {
+        const int op = s.cigar[c].x, arg = s.cigar[c].y;
+        if (op == CG_MATCH) {
+            const int node_id = arg;
+            ++query_id;
+            const uint8_t b = q[query_id];
+            if (s.base[node_id] != b) {                        // mismatch: reuse an aligned node with this base, else a new one
+                int aligned = -1;
+                for (int i = 0; i < s.aln_n[node_id]; ++i) {
+                    const int a = s.aln_id[node_id * ALN_MAX + i];
+                    if (s.base[a] == b) { aligned = a; break; }
+                }
+                if (aligned != -1) {
+                    poa_add_edge(s, last_id, aligned, 1 - last_new, 1);
+                    last_id = aligned; last_new = 0;
+                } else {
+                    const int nid = poa_add_node(s, b);
+                    if (nid < 0) return;
+                    poa_add_edge(s, last_id, nid, 0, 1);
+                    last_id = nid; last_new = 1;
+                    poa_add_aligned(s, node_id, nid);
+                }
+            } else {
+                poa_add_edge(s, last_id, node_id, 1 - last_new, 1);
+                last_id = node_id; last_new = 0;
+            }
+        } else if (op == CG_INS) {
+            for (int l = 0; l < arg; ++l) {
+                ++query_id;
+                const int nid = poa_add_node(s, q[query_id]);
+                if (nid < 0) return;
+                poa_add_edge(s, last_id, nid, 0, 1);
+                last_id = nid; last_new = 1;
+                if (s.status) return;
+            }
+        }                                                      // CG_DEL: nothing
+        if (s.status) return;
+    }
+    (void)qlen;
+    poa_add_edge(s, last_id, SINK, 1 - last_new, 1);
+}
+
+// ----------------------------------------------------------------------------------------------- alignment
+template <typename SC>
+PD int poa_cell(const PoaState &s, int i, int plane, int j, int inf_min) {
+    const int b = s.dp_beg[i], e = s.dp_end[i];
+    if (j < b || j > e) return inf_min;
+    const int w = e - b + 1;
+    return (int)reinterpret_cast<const SC *>(s.cells)[s.row_off[i] * 5 + (long long)plane * w + (j - b)];
+}
+
+PD void poa_push_cigar(PoaState &s, int op, int arg) {
+    if (s.n_cigar >= s.cigar_cap) { s.status = POA_ERR_CIGAR; return; }
+    s.cigar[s.n_cigar].x = op; s.cigar[s.n_cigar].y = arg; ++s.n_cigar;
+}
+
+// simd_abpoa_cg_backtrack (abpoa_align_simd.c:309-458) with put_gap_on_right = put_gap_at_end = 0.  lane 0
+template <typename SC>
+PD void poa_backtrack(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
+    int i = s.best_i, j = s.best_j, cur_op = OP_ALL;
+    s.n_cigar = 0;
+    if (j < qlen) poa_push_cigar(s, CG_INS, qlen - j);
+    int guard = s.node_n + qlen + 8;
+    while (i > 0 && j > 0) {
+        if (--guard < 0 || s.status) { if (!s.status) s.status = POA_ERR_BACKTRACK; return; }
+        const int id = s.idx2id[i];
+        const int sc = poa_score(s.base[id], q[j - 1]);
+        const int pn = s.in_n[id], po = s.in_off[id];
+        const int Hij = poa_cell<SC>(s, i, 0, j, inf_min);
+        bool hit = false;
+        if (cur_op & OP_M) {
+            for (int k = 0; k < pn; ++k) {
+                const int p = s.id2idx[s.edge_id[po + k]];
+                if (j - 1 < s.dp_beg[p] || j - 1 > s.dp_end[p]) continue;
+                if (poa_cell<SC>(s, p, 0, j - 1, inf_min) + sc == Hij) {
+                    poa_push_cigar(s, CG_MATCH, id);
+                    i = p; --j; hit = true; cur_op = OP_ALL;
+                    break;
+                }
+            }
+        }
+        if (!hit && (cur_op & OP_E)) {
+            for (int k = 0; k < pn && !hit; ++k) {
+                const int p = s.id2idx[s.edge_id[po + k]];
+                if (j < s.dp_beg[p] || j > s.dp_end[p]) continue;
+                const int pH = poa_cell<SC>(s, p, 0, j, inf_min);
+                if (cur_op & OP_E1) {
+                    const int pe1 = poa_cell<SC>(s, p, 1, j, inf_min);
+                    const bool ok = (cur_op & OP_M) ? (Hij == pe1) : (poa_cell<SC>(s, i, 1, j, inf_min) == pe1 - GAP_E1);
+                    if (ok) {
+                        cur_op = (pH - GAP_OE1 == pe1) ? (OP_M | OP_F) : OP_E1;
+                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p;
+                        break;
+                    }
+                }
+                if (cur_op & OP_E2) {
+                    const int pe2 = poa_cell<SC>(s, p, 2, j, inf_min);
+                    const bool ok = (cur_op & OP_M) ? (Hij == pe2) : (poa_cell<SC>(s, i, 2, j, inf_min) == pe2 - GAP_E2);
+                    if (ok) {
+                        cur_op = (pH - GAP_OE2 == pe2) ? (OP_M | OP_F) : OP_E2;
+                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p;
+                        break;
+                    }
+                }
+            }
+        }
+        if (!hit && (cur_op & OP_F)) {
+            const int Hl = poa_cell<SC>(s, i, 0, j - 1, inf_min);
+            if (cur_op & OP_F1) {
+                const int f1 = poa_cell<SC>(s, i, 3, j, inf_min);
+                if (!(cur_op & OP_M) || Hij == f1) {
+                    if (Hl - GAP_OE1 == f1) { cur_op = OP_M | OP_E; hit = true; }
+                    else if (poa_cell<SC>(s, i, 3, j - 1, inf_min) - GAP_E1 == f1) { cur_op = OP_F1; hit = true; }
+                }
+            }
+            if (!hit && (cur_op & OP_F2)) {
+                const int f2 = poa_cell<SC>(s, i, 4, j, inf_min);
+                if (!(cur_op & OP_M) || Hij == f2) {
+                    if (Hl - GAP_OE2 == f2) { cur_op = OP_M | OP_E; hit = true; }
+                    else if (poa_cell<SC>(s, i, 4, j - 1, inf_min) - GAP_E2 == f2) { cur_op = OP_F2; hit = true; }
+                }
+            }
+            if (hit) { poa_push_cigar(s, CG_INS, 1); --j; }
+        }
+        if (!hit && (cur_op & OP_M)) {
+            for (int k = 0; k < pn; ++k) {
+                const int p = s.id2idx[s.edge_id[po + k]];
+                if (j - 1 < s.dp_beg[p] || j - 1 > s.dp_end[p]) continue;
+                if (poa_cell<SC>(s, p, 0, j - 1, inf_min) + sc == Hij) {
+                    poa_push_cigar(s, CG_MATCH, id);
+                    i = p; --j; hit = true; cur_op = OP_ALL;
+                    break;
+                }
+            }
+        }
+        if (!hit) { s.status = POA_ERR_BACKTRACK; return; }
+    }
+    if (j > 0) poa_push_cigar(s, CG_INS, j);
+}
+
+// One alignment of q against the sorted graph: first row, row DP in index order, best end cell.  All lanes.
+// Returns the number of band cells computed (uniform).  abpoa_align_simd.c:1200-1231
+template <typename SC>
+PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
+    const int lane = poa_lane();
+    const int n = s.node_n;
+    const int w = EXTRA_B + (int)(EXTRA_F * (float)qlen);      // abpoa_align_simd.c:474
+    SC *cells = reinterpret_cast<SC *>(s.cells);
+    const long long cell_cap = s.cell_bytes / (long long)(5 * sizeof(SC));
+    long long top = 0;
+
+    // ---- first row (simd_abpoa_cg_first_row / _first_dp, :669-688, :617-633)
+    if (lane == 0) {
+        s.max_left[SRC] = s.max_right[SRC] = 0;
+        for (int i = 0; i < s.out_n[SRC]; ++i) { const int o = s.edge_id[s.out_off[SRC] + i]; s.max_left[o] = s.max_right[o] = 1; }
+    }
+    poa_sync();
+    const int end0 = imin(qlen, imax(s.max_right[SRC], qlen - s.remain[SRC]) + w);
+    {
+        const int w0 = end0 + 1;
+        if (w0 > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return 0; }
+        if (lane == 0) { s.dp_beg[0] = 0; s.dp_end[0] = end0; s.row_off[0] = 0; }
+        for (int j = lane; j <= end0; j += POA_NL) {
+            int h, e1 = inf_min, e2 = inf_min, f1, f2;
+            if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
+            else { f1 = -GAP_O1 - GAP_E1 * j; f2 = -GAP_O2 - GAP_E2 * j; h = imax(f1, f2); }
+            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; cells[3 * w0 + j] = (SC)f1; cells[4 * w0 + j] = (SC)f2;
+        }
+        top = w0;
+    }
+    poa_sync();
+
+    // ---- rows 1 .. n-2 in topological index order (simd_abpoa_cg_dp, :935-1074)
+    for (int i = 1; i < n - 1; ++i) {
+        const int id = s.idx2id[i];
+        const int nb = s.base[id];
+        const int pn = s.in_n[id], po = s.in_off[id];
+        const int rt = qlen - s.remain[id];                    // remain[SINK] == -1 (abpoa_align.h:34-35)
+        int beg = imax(0, imin(s.max_left[id], rt) - w);
+        const int end = imin(qlen, imax(s.max_right[id], rt) + w);
+        int min_pre_beg = 0x7fffffff;
+        for (int k = 0; k < pn; ++k) min_pre_beg = imin(min_pre_beg, s.dp_beg[s.id2idx[s.edge_id[po + k]]]);
+        if (beg < min_pre_beg) beg = min_pre_beg;              // :957-959 at vector width 1
+        const int wd = end - beg + 1;
+        if (wd <= 0 || pn <= 0) { if (lane == 0) s.status = POA_ERR_BAND; poa_sync(); return top; }
+        if (top + wd > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return top; }
+        SC *row = cells + top * 5;
+        if (lane == 0) { s.dp_beg[i] = beg; s.dp_end[i] = end; s.row_off[i] = top; }
+
+        int carry_h = inf_min;                                 // Hme of the column left of the chunk
+        int carry_f1 = inf_min - GAP_OE1, carry_f2 = inf_min - GAP_OE2;
+        int bv = -2147483647 - 1, bl = -1, br = -1;            // this lane's row maximum, first and last column reaching it
+        for (int c0 = beg; c0 <= end; c0 += POA_NL) {
+            const int j = c0 + lane;
+            const bool valid = j <= end;
+            int m = inf_min, e1in = inf_min, e2in = inf_min;
+            if (valid) {
+                for (int k = 0; k < pn; ++k) {                 // predecessors in in-edge order; max is order independent
+                    const int p = s.id2idx[s.edge_id[po + k]];
+                    const int pb = s.dp_beg[p], pe = s.dp_end[p], pw = pe - pb + 1;
+                    const SC *pr = cells + s.row_off[p] * 5;
+                    if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
+                    if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+                }
+            }
+            const int sc = (valid && j > 0) ? poa_score(nb, q[j - 1]) : 0;   // query profile column 0 is 0 (:520)
+            const int hme = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
+            // F[j] = max(Hme[j-1] - oe, F[j-1] - e): prefix max of (Hme[k-1] - oe + k*e) across the lanes (:1052-1059)
+            int left = poa_shfl_up(hme, 1);
+            if (lane == 0) left = carry_h;
+            int g1 = left - GAP_OE1 + lane * GAP_E1, g2 = left - GAP_OE2 + lane * GAP_E2;
+#if POA_NL > 1
+#pragma unroll
+            for (int d = 1; d < POA_NL; d <<= 1) {
+                const int t1 = poa_shfl_up(g1, d), t2 = poa_shfl_up(g2, d);
+                if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
+            }
+#endif
+            const int f1 = imax(g1 - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
+            const int f2 = imax(g2 - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
+            const int h = imax(hme, imax(f1, f2));
+            if (valid) {
+                const int x = j - beg;
+                row[x] = (SC)h;
+                row[wd + x] = (SC)imax(e1in - GAP_E1, h - GAP_OE1);        // E for the next row (:1067-1071)
+                row[2 * wd + x] = (SC)imax(e2in - GAP_E2, h - GAP_OE2);
+                row[3 * wd + x] = (SC)f1;
+                row[4 * wd + x] = (SC)f2;
+                if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
+            }
+            carry_h = poa_shfl(hme, POA_NL - 1);
+            carry_f1 = poa_shfl(f1, POA_NL - 1);
+            carry_f2 = poa_shfl(f2, POA_NL - 1);
+        }
+        // row arg-max -> band hints of the successors (simd_abpoa_max_in_row :1107-1119, simd_abpoa_ada_max_i :1121-1130)
+        const int vmax = poa_max_all(bv);
+        int left_i = -1, right_i = -1;
+        if (vmax >= inf_min) {
+            right_i = poa_max_all(bv == vmax ? br : -1);
+            if (vmax > inf_min) left_i = poa_min_all(bv == vmax ? bl : 0x7fffffff);
+        }
+        for (int k = lane; k < s.out_n[id]; k += POA_NL) {
+            const int o = s.edge_id[s.out_off[id] + k];
+            if (right_i + 1 > s.max_right[o]) s.max_right[o] = right_i + 1;
+            if (left_i + 1 < s.max_left[o]) s.max_left[o] = left_i + 1;
+        }
+        top += wd;
+        poa_sync();
+    }
+    // ---- best end cell among SINK's predecessors (simd_abpoa_global_get_max, :1092-1105)
+    if (lane == 0) {
+        int best = inf_min, bi = 0, bj = 0;
+        for (int k = 0; k < s.in_n[SINK]; ++k) {
+            const int p = s.id2idx[s.edge_id[s.in_off[SINK] + k]];
+            const int e = qlen > s.dp_end[p] ? s.dp_end[p] : qlen;
+            const int v = poa_cell<SC>(s, p, 0, e, inf_min);
+            if (v > best) { best = v; bi = p; bj = e; }
+        }
+        s.best_score = best; s.best_i = bi; s.best_j = bj;
+    }
+    poa_sync();
+    return top;
+}
+
+PD uint64_t poa_fnv(uint64_t h, int32_t v) {
+    for (int k = 0; k < 4; ++k) { h ^= (uint64_t)(((uint32_t)v >> (8 * k)) & 0xffu); h *= 1099511628211ull; }
+    return h;
+}
+
+// per-read observations for the parity tests (all optional)
+struct PoaTrace {
+    int32_t *best_score, *node_n, *n_ops;
+    uint64_t *ops_hash;
+    long long *cells;
+    int32_t dump_read;          // global read index whose expanded ops go to dump (pairs op, node), or -1
+    int32_t *dump;
+    int32_t dump_cap;
+};
+
+// heaviest bundling (abpoa_heaviest_bundling, abpoa_output.c:477-547) + walk (abpoa_set_hb_cons :375-391).  lane 0.
+// score -> max_left, max_out_id -> max_right (free after the last alignment).  Returns the consensus length.
+PD int poa_consensus(PoaState &s, uint8_t *cons, int32_t *cov, int cap) {
+    int *score = s.max_left, *max_out = s.max_right;
+    for (int i = 0; i < s.node_n; ++i) s.deg[i] = s.out_n[i];
+    int head = 0, tail = 0;
+    s.queue[tail++] = SINK;
+    bool done = false;
+    while (head < tail && !done) {
+        const int cur = s.queue[head++];
+        if (cur == SINK) { max_out[cur] = -1; score[cur] = 0; }
+        else if (cur == SRC) {
+            int path_score = -1, path_max_w = -1, max_id = -1;
+            for (int i = 0; i < s.out_n[cur]; ++i) {
+                const int o = s.edge_id[s.out_off[cur] + i], ow = s.edge_w[s.out_off[cur] + i];
+                if (ow > path_max_w || (ow == path_max_w && score[o] > path_score)) { max_id = o; path_score = score[o]; path_max_w = ow; }
+            }
+            max_out[cur] = max_id;
+            done = true;
+            break;
+        } else {
+            int max_w = -2147483647 - 1, max_id = -1;
+            for (int i = 0; i < s.out_n[cur]; ++i) {
+                const int o = s.edge_id[s.out_off[cur] + i], ow = s.edge_w[s.out_off[cur] + i];
+                if (max_w < ow) { max_w = ow; max_id = o; }
+                else if (max_w == ow && score[max_id] <= score[o]) max_id = o;
+            }
+            if (max_id < 0) { s.status = POA_ERR_CONS; return 0; }
+            score[cur] = max_w + score[max_id];
+            max_out[cur] = max_id;
+        }
+        for (int i = 0; i < s.in_n[cur]; ++i) {
+            const int in = s.edge_id[s.in_off[cur] + i];
+            if (--s.deg[in] == 0) s.queue[tail++] = in;
+        }
+    }
+    if (!done) { s.status = POA_ERR_CONS; return 0; }
+    int len = 0, cur = max_out[SRC];
+    while (cur != SINK) {
+        if (cur < 0 || len > s.node_n) { s.status = POA_ERR_CONS; return 0; }
+        if (len < cap) { cons[len] = s.base[cur]; if (cov) cov[len] = s.n_read[cur]; }
+        ++len;
+        cur = max_out[cur];
+    }
+    return len;
+}
+
+// The whole read set: reads r0 .. r1 of the batch (bases[seq_off[r] .. seq_off[r+1])).  All lanes.  Returns the
+// consensus length (uniform), 0 on error (s.status says why).
+PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq_off, const uint8_t *bases, uint8_t *cons,
+                   int32_t *cov, int cons_cap, const PoaTrace *tr) {
+    const int lane = poa_lane();
+    if (lane == 0) {                                           // abpoa_reset (abpoa_graph.c:782): graph = {SRC, SINK}
+        s.node_n = 0; s.edge_top = 0; s.status = POA_OK; s.n_cigar = 0; s.cells_done = 0; s.cells_full = 0;
+        poa_add_node(s, 0); poa_add_node(s, 0);
+    }
+    poa_sync();
+    for (long long r = r0; r < r1 && !s.status; ++r) {
+        const uint8_t *q = bases + seq_off[r];
+        const int qlen = (int)(seq_off[r + 1] - seq_off[r]);
+        if (qlen <= 0) { if (lane == 0) s.status = POA_ERR_INPUT; poa_sync(); break; }
+        long long cells = 0;
+        const int rows = s.node_n;
+        if (rows <= 2) {                                       // abpoa_align_sequence_to_graph returns -1 (abpoa_align.c:201)
+            if (lane == 0) { s.n_cigar = 0; s.best_score = 0; poa_add_first(s, q, qlen); }
+        } else {
+            // score width (abpoa_align_simd.c:1291-1302)
+            const int len = qlen > rows ? qlen : rows;
+            const int max_score = imax(qlen * MATCH, len * GAP_E1 + GAP_O1);
+            const bool use16 = max_score <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2;
+            if (use16) cells = poa_align_dp<int16_t>(s, q, qlen, INF_MIN16);
+            else cells = poa_align_dp<int32_t>(s, q, qlen, INF_MIN32);
+            if (lane == 0 && !s.status) {
+                if (use16) poa_backtrack<int16_t>(s, q, qlen, INF_MIN16); else poa_backtrack<int32_t>(s, q, qlen, INF_MIN32);
+                s.cells_done += cells;
+                s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
+            }
+        }
+        poa_sync();
+        if (lane == 0 && !s.status) {
+            if (tr && tr->ops_hash) {                          // forward (query) order, as the reference's reversed cigar
+                uint64_t h = 1469598103934665603ull;
+                int nops = 0;
+                for (int c = s.n_cigar - 1; c >= 0; --c) {
+                    const int op = s.cigar[c].x, arg = s.cigar[c].y;
+                    const int rep = op == CG_INS ? arg : 1;
+                    for (int l = 0; l < rep; ++l) {
+                        const int node = op == CG_INS ? -1 : arg;
+                        h = poa_fnv(poa_fnv(h, op), node);
+                        if (tr->dump && r == tr->dump_read && 2 * nops + 1 < tr->dump_cap) { tr->dump[2 * nops] = op; tr->dump[2 * nops + 1] = node; }
+                        ++nops;
+                    }
+                }
+                tr->ops_hash[r] = h; tr->n_ops[r] = nops;
+            }
+            if (rows > 2) poa_add_alignment(s, q, qlen);
+            if (tr && tr->best_score) { tr->best_score[r] = rows > 2 ? s.best_score : 0; tr->cells[r] = cells; }
+        }
+        poa_sync();
+        if (s.status) break;
+        poa_topological_sort(s);
+        if (lane == 0 && tr && tr->node_n) tr->node_n[r] = s.node_n;
+        poa_sync();
+    }
+    int len = 0;
+    if (lane == 0 && !s.status && s.node_n > 2) len = poa_consensus(s, cons, cov, cons_cap);
+    poa_sync();
+    len = poa_shfl(len, 0);
+    return s.status ? 0 : len;
+}
+
+}  // namespace svtk_poa

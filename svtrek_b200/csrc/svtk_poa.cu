@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -236,6 +237,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     for (int s = 0; s < ns; ++s) if (info[s].n > 0) todo.push_back(s);
     std::vector<int32_t> h_status(ns, 0);
     double scale = 1.0, kernel_ms = 0.0;
+    if (const char *e = getenv("SVTK_POA_SCALE")) { const double v = atof(e); if (v > 0.0) scale = v; }   // tests: start from a too-small block
     uint64_t relaunched = 0, max_workers = 0;
     CU(cudaMemsetAsync(d_cells, 0, 64, c->stream));
     int max_resident = 148 * 32;
@@ -243,7 +245,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         int dev_sms = 0;
         if (cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, c->device) == cudaSuccess && dev_sms > 0) max_resident = dev_sms * 32;
     }
-    for (int attempt = 0; attempt < 4 && !todo.empty(); ++attempt) {
+    for (int attempt = 0; attempt < 6 && !todo.empty(); ++attempt) {
         // classes, largest reads first; inside a class heaviest set first (the atomic queue then balances the tail)
         std::sort(todo.begin(), todo.end(), [&](int x, int y) {
             if (info[x].cls != info[y].cls) return info[x].cls > info[y].cls;

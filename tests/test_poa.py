@@ -128,8 +128,8 @@ def test_gpu_matches_abpoa_live(auditor):
 
 @pytest.mark.gpu
 def test_gpu_32bit_scores_and_scratch_regrowth(auditor):
-    """A graph beyond 16 364 rows switches abPOA to int32 scores (abpoa_align_simd.c:1293); unrelated reads grow the graph
-    to the sum of their lengths, far past the first scratch estimate, so the set is rerun with a larger block."""
+    """A graph beyond 16 364 rows switches abPOA to int32 scores (abpoa_align_simd.c:1293).  SVTK_POA_SCALE starts the
+    workers from a scratch block 20x too small, so both sets run out of nodes / band cells and are rerun with larger blocks."""
     from oracle import binding as B
     if not B.have_abpoa():
         pytest.skip("oracle/_ref/libabpoa_ref.so did not travel")
@@ -139,7 +139,11 @@ def test_gpu_32bit_scores_and_scratch_regrowth(auditor):
     unrelated = [rng.integers(0, 4, 300).astype(np.uint8) for _ in range(30)]
     sets = [big, unrelated]
     so, qo, b = P.pack(sets)
-    cons, st, tr = auditor.poa_consensus(so, qo, b, want_trace=True)
+    os.environ["SVTK_POA_SCALE"] = "0.05"
+    try:
+        cons, st, tr = auditor.poa_consensus(so, qo, b, want_trace=True)
+    finally:
+        del os.environ["SVTK_POA_SCALE"]
     assert st["relaunched"] >= 1
     for s, seqs in enumerate(sets):
         r = B.ref_poa_steps(seqs)

@@ -48,10 +48,19 @@ __host__ __device__ inline PoaLayout poa_layout(const PoaCaps &c) {
     return L;
 }
 
+// One size class of a launch: its slice of the item list, its cursor, its workers and their scratch blocks.
+struct PoaClass {
+    int item_begin, item_end;          // slice of PoaLaunch::items (heaviest first)
+    int worker_begin, worker_end;      // CTAs that own a block of this class
+    long long scratch_off;             // byte offset of this class's first block
+    PoaCaps caps;                      // >= the caps of every smaller class: a worker can also take their sets
+};
+
 struct PoaLaunch {
-    int n_items;
-    const int *items;                  // read-set ids of this launch, heaviest first
-    int *next;                         // atomic cursor into items
+    int n_classes;
+    const PoaClass *classes;           // largest reads first
+    const int *items;                  // read-set ids
+    int *cursors;                      // one atomic cursor per class
     const long long *set_off, *seq_off;
     const uint8_t *bases;
     uint8_t *cons;
@@ -60,20 +69,23 @@ struct PoaLaunch {
     int32_t *cons_len, *status;
     unsigned long long *cells;         // [0] band cells, [1] full-matrix equivalent
     unsigned char *scratch;
-    PoaCaps caps;
     PoaTrace trace;
     int have_trace;
 };
 
 __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
     __shared__ PoaState s;
-    __shared__ int s_item;
+    __shared__ int s_item, s_cls;
     const int lane = threadIdx.x;
     if (lane == 0) {
-        const PoaLayout lay = poa_layout(L.caps);
-        unsigned char *blk = L.scratch + (long long)blockIdx.x * lay.total;
-        const int N = L.caps.node_cap;
-        s.node_cap = N; s.edge_cap = L.caps.edge_cap; s.cigar_cap = L.caps.cigar_cap; s.cell_bytes = L.caps.cell_bytes;
+        int k = 0;
+        while (k + 1 < L.n_classes && (int)blockIdx.x >= L.classes[k].worker_end) ++k;
+        s_cls = k;
+        const PoaClass cl = L.classes[k];
+        const PoaLayout lay = poa_layout(cl.caps);
+        unsigned char *blk = L.scratch + cl.scratch_off + (long long)((int)blockIdx.x - cl.worker_begin) * lay.total;
+        const int N = cl.caps.node_cap;
+        s.node_cap = N; s.edge_cap = cl.caps.edge_cap; s.cigar_cap = cl.caps.cigar_cap; s.cell_bytes = cl.caps.cell_bytes;
         s.base = blk + lay.base;
         int *p = reinterpret_cast<int *>(blk + lay.ints);
         s.in_off = p; p += N; s.in_n = p; p += N; s.in_cap = p; p += N; s.out_off = p; p += N; s.out_n = p; p += N; s.out_cap = p; p += N;
@@ -87,23 +99,27 @@ __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
         s.cells = blk + lay.cells;
     }
     __syncwarp();
-    while (true) {
-        if (lane == 0) s_item = atomicAdd(L.next, 1);
-        __syncwarp();
-        const int it = s_item;
-        __syncwarp();
-        if (it >= L.n_items) break;
-        const int sv = L.items[it];
-        const long long co = L.cons_off[sv];
-        const int cap = (int)(L.cons_off[sv + 1] - co);
-        const int len = poa_run_set(s, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
-                                    L.have_trace ? &L.trace : nullptr);
-        if (lane == 0) {
-            L.status[sv] = s.status;
-            L.cons_len[sv] = len;
-            if (!s.status) { atomicAdd(&L.cells[0], (unsigned long long)s.cells_done); atomicAdd(&L.cells[1], (unsigned long long)s.cells_full); }
+    // own class first, then every smaller one (their sets fit this worker's block): no CTA idles while sets remain
+    for (int k = s_cls; k < L.n_classes; ++k) {
+        const int i0 = L.classes[k].item_begin, n_items = L.classes[k].item_end - i0;
+        while (true) {
+            if (lane == 0) s_item = atomicAdd(L.cursors + k, 1);
+            __syncwarp();
+            const int it = s_item;
+            __syncwarp();
+            if (it >= n_items) break;
+            const int sv = L.items[i0 + it];
+            const long long co = L.cons_off[sv];
+            const int cap = (int)(L.cons_off[sv + 1] - co);
+            const int len = poa_run_set(s, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
+                                        L.have_trace ? &L.trace : nullptr);
+            if (lane == 0) {
+                L.status[sv] = s.status;
+                L.cons_len[sv] = len;
+                if (!s.status) { atomicAdd(&L.cells[0], (unsigned long long)s.cells_done); atomicAdd(&L.cells[1], (unsigned long long)s.cells_full); }
+            }
+            __syncwarp();
         }
-        __syncwarp();
     }
 }
 
@@ -221,12 +237,13 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     }
     CU(cudaMemsetAsync(d_len, 0, a16(4 * ns) * 2, c->stream));
 
-    // control block: cells[2], then per launch one cursor, then the item lists
-    const size_t ctl_bytes = 64 + 4 * 64 + 4 * (size_t)ns;
+    // control block: cells[2] | 64 class cursors | 64 class descriptors | item list
+    const size_t ctl_bytes = 64 + 4 * 64 + a16(sizeof(PoaClass) * 64) + 4 * (size_t)ns;
     if (int rc = c->poa_ctl.reserve(ctl_bytes)) return rc;
     unsigned long long *d_cells = (unsigned long long *)c->poa_ctl.p;
     int *d_cursors = (int *)((unsigned char *)c->poa_ctl.p + 64);
-    int *d_items = d_cursors + 64;
+    PoaClass *d_classes = (PoaClass *)((unsigned char *)c->poa_ctl.p + 64 + 4 * 64);
+    int *d_items = (int *)((unsigned char *)d_classes + a16(sizeof(PoaClass) * 64));
     for (int i = 0; i < 2; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
 
     size_t free_b = 0, total_b = 0;
@@ -252,42 +269,66 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             if (info[x].work != info[y].work) return info[x].work > info[y].work;
             return x < y;
         });
-        CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemsetAsync(d_cursors, 0, 4 * 64, c->stream));
-        CU(cudaStreamSynchronize(c->stream));      // todo is reused below; the copy above must have read it
-        size_t i0 = 0;
-        int launch_no = 0;
-        while (i0 < todo.size()) {
+        std::vector<PoaClass> cls;
+        std::vector<double> cwork;
+        for (size_t i0 = 0; i0 < todo.size();) {
             size_t i1 = i0;
             PoaCaps caps = caps_for(info[todo[i0]], scale);
-            while (i1 < todo.size() && info[todo[i1]].cls == info[todo[i0]].cls) { caps = caps_max(caps, caps_for(info[todo[i1]], scale)); ++i1; }
-            const PoaLayout lay = poa_layout(caps);
-            long long workers = std::min<long long>((long long)(i1 - i0), max_resident);
-            if (lay.total > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", lay.total, budget);
-            workers = std::min(workers, budget / lay.total);
-            if (int rc = c->poa_scratch.reserve((size_t)(workers * lay.total))) return rc;
-            PoaLaunch L{};
-            L.n_items = (int)(i1 - i0); L.items = d_items + i0; L.next = d_cursors + (launch_no % 64);
-            L.set_off = d_set_off; L.seq_off = d_seq_off; L.bases = d_bases; L.cons = d_cons; L.cov = d_cov; L.cons_off = d_cons_off;
-            L.cons_len = d_len; L.status = d_status; L.cells = d_cells; L.scratch = (unsigned char *)c->poa_scratch.p; L.caps = caps;
-            L.trace = tr; L.have_trace = trace ? 1 : 0;
-            if (launch_no >= 64) { CU(cudaMemsetAsync(d_cursors + (launch_no % 64), 0, 4, c->stream)); }
-            CU(cudaEventRecord(c->poa_ev[0], c->stream));
-            k_poa_sets<<<(unsigned)workers, 32, 0, c->stream>>>(L);
-            CU(cudaGetLastError());
-            CU(cudaEventRecord(c->poa_ev[1], c->stream));
-            // the scratch buffer may be re-reserved (freed) by the next class: wait for this launch first
-            CU(cudaEventSynchronize(c->poa_ev[1]));
-            float ms = 0.f;
-            CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
-            kernel_ms += ms;
-            c->launches += 1;
-            max_workers = std::max<uint64_t>(max_workers, (uint64_t)workers);
-            ++launch_no;
+            double wk = 0;
+            while (i1 < todo.size() && info[todo[i1]].cls == info[todo[i0]].cls) { caps = caps_max(caps, caps_for(info[todo[i1]], scale)); wk += info[todo[i1]].work; ++i1; }
+            PoaClass pc{};
+            pc.item_begin = (int)i0; pc.item_end = (int)i1; pc.caps = caps;
+            cls.push_back(pc); cwork.push_back(wk);
             i0 = i1;
         }
+        if (cls.size() > 64) return fail(SVTK_ERR_ARG, "poa: more than 64 size classes");
+        for (int k = (int)cls.size() - 2; k >= 0; --k) cls[k].caps = caps_max(cls[k].caps, cls[k + 1].caps);   // stealing downwards must fit
+        // workers per class: share of the resident CTAs proportional to the class's work, within the scratch budget
+        const int K = (int)cls.size();
+        const long long W = std::min<long long>((long long)todo.size(), max_resident);
+        double tot_work = 0;
+        for (double x : cwork) tot_work += x;
+        std::vector<long long> nw(K), bytes(K);
+        long long mem = 0;
+        for (int k = 0; k < K; ++k) {
+            bytes[k] = poa_layout(cls[k].caps).total;
+            if (bytes[k] > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", bytes[k], budget);
+            const long long nk = cls[k].item_end - cls[k].item_begin;
+            nw[k] = std::max<long long>(1, std::min<long long>(nk, (long long)std::llround((double)W * cwork[k] / std::max(tot_work, 1.0))));
+            mem += nw[k] * bytes[k];
+        }
+        while (mem > budget) {                                 // trim the class holding the most scratch
+            int big = -1;
+            for (int k = 0; k < K; ++k) if (nw[k] > 1 && (big < 0 || nw[k] * bytes[k] > nw[big] * bytes[big])) big = k;
+            if (big < 0) return fail(SVTK_ERR_ALLOC, "poa: scratch for one worker per size class (%lld bytes) exceeds the budget %lld", mem, budget);
+            const long long cut = std::max<long long>(1, nw[big] / 10);
+            nw[big] -= cut; mem -= cut * bytes[big];
+        }
+        long long workers = 0, off = 0;
+        for (int k = 0; k < K; ++k) {
+            cls[k].worker_begin = (int)workers; workers += nw[k]; cls[k].worker_end = (int)workers;
+            cls[k].scratch_off = off; off += nw[k] * bytes[k];
+        }
+        if (int rc = c->poa_scratch.reserve((size_t)off)) return rc;
+        CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(d_classes, cls.data(), sizeof(PoaClass) * cls.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemsetAsync(d_cursors, 0, 4 * 64, c->stream));
+        PoaLaunch L{};
+        L.n_classes = K; L.classes = d_classes; L.items = d_items; L.cursors = d_cursors;
+        L.set_off = d_set_off; L.seq_off = d_seq_off; L.bases = d_bases; L.cons = d_cons; L.cov = d_cov; L.cons_off = d_cons_off;
+        L.cons_len = d_len; L.status = d_status; L.cells = d_cells; L.scratch = (unsigned char *)c->poa_scratch.p;
+        L.trace = tr; L.have_trace = trace ? 1 : 0;
+        CU(cudaEventRecord(c->poa_ev[0], c->stream));
+        k_poa_sets<<<(unsigned)workers, 32, 0, c->stream>>>(L);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(c->poa_ev[1], c->stream));
         CU(cudaMemcpyAsync(h_status.data(), d_status, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaStreamSynchronize(c->stream));                  // also: todo / cls were read by the copies above
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
+        kernel_ms += ms;
+        c->launches += 1;
+        max_workers = std::max<uint64_t>(max_workers, (uint64_t)workers);
         std::vector<int> again;
         for (int s : todo) {
             const int st = h_status[s];

@@ -56,6 +56,8 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--ref-sample-mb", type=float, default=3.0, help="--impl reference: contig length of the bounded sample")
     ap.add_argument("--ref-threads", type=int, default=0)
+    ap.add_argument("--poa-sets", type=int, default=4000, help="INS read sets per GPU of the POA (K3) leg: a bounded sample of configs[3]'s 20k records; 0 skips the leg")
+    ap.add_argument("--poa-steps", type=int, default=2)
     return ap.parse_args()
 
 
@@ -242,6 +244,54 @@ def cpu_port_baseline(rs, w, n_records, budget_s=10.0):
 
 
 # ------------------------------------------------------------------------------------------------------------
+POA_DESC = "BASELINE.json configs[3] sample: INS read sets, inserted length log-uniform 50 bp - 10 kb, 60x depth x 0.8 carriers, 8 % ONT-like errors"
+
+
+def poa_workload(rank, n_sets):
+    from svtrek_b200 import simpoa as P
+    sets = P.ins_workload(SEED0 + 77 + 1000 * rank, n_sets, depth=60, carrier=0.8, err=0.08, len_lo=50, len_hi=10000)
+    return sets, P.pack(sets)
+
+
+def poa_leg(a, rank, n_sets, steps):
+    """K3: svtk_poa_consensus (host buffers in, consensus out) on this rank's read sets.  GCUPS = band cells the kernel
+    itself counted (5-state convex cell updates) / CUDA-event time of k_poa_sets; e2e = the same cells / wall
+    time of the C-ABI call (H2D of the reads, kernel, D2H of the consensus)."""
+    sets, (so, qo, b) = poa_workload(rank, n_sets)
+    a.poa_consensus(so, qo, b)                       # warm-up: scratch allocation, first-touch
+    kms, wall, st = 0.0, 0.0, None
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        cons, st = a.poa_consensus(so, qo, b)
+        wall += time.perf_counter() - t0
+        kms += st["kernel_ms"]
+    return sets, cons, dict(cells=st["cells"], cells_full=st["cells_full"], n_sets=n_sets, n_reads=int(len(qo) - 1), n_bases=int(len(b)),
+                            kernel_ms=kms / steps, wall_ms=wall * 1e3 / steps, workers=st["workers"], relaunched=st["relaunched"],
+                            phase_cycles=st["phase_cycles"])
+
+
+def poa_cpu_baseline(sets, cons, budget_s=10.0):
+    """abPOA 1.5.4 itself (oracle/_ref/libabpoa_ref.so, the reference's submodule compiled unmodified), 1 thread, on a
+    bounded sample of the same read sets; every sampled consensus is also compared with the GPU's."""
+    from oracle import binding as B
+    if not B.have_abpoa():
+        return None
+    rng = np.random.default_rng(1)
+    order = rng.permutation(len(sets))
+    t0 = time.perf_counter()
+    cells, n = 0, 0
+    for i in order:
+        r = B.ref_poa_steps(sets[i])
+        assert np.array_equal(r["cons"], cons[i]), f"POA consensus of set {i} differs from abPOA"
+        cells += int(r["cells"].sum()); n += 1
+        if time.perf_counter() - t0 >= budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": cells / dt / 1e9, "unit": "GCUPS", "cores": 1, "kind": "reference", "sets_per_s": n / dt,
+            "sample": f"abpoa_msa default path (abPOA 1.5.4 compiled from the reference's submodule, runtime SIMD dispatch), 1 thread, {n} randomly "
+                      f"chosen read sets of the GPU leg's batch in {dt:.1f} s; cells = abPOA's own dp_beg/dp_end; consensus compared with the GPU's: identical"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -347,6 +397,18 @@ def run_ours(args):
     clocks = sampler.stop()
     assert np.array_equal(h_res.numpy(), ref_res), "e2e result differs from the device-resident result"
 
+    # ---- K3: POA consensus leg (GCUPS half of the metric)
+    poa = None
+    if args.poa_sets > 0:
+        poa_sets_l, poa_cons, poa = poa_leg(a, rank, args.poa_sets, max(1, args.poa_steps))
+        pr = torch.tensor([poa["kernel_ms"], poa["wall_ms"]], dtype=torch.float64, device=dev)
+        pt = torch.tensor([float(poa["cells"]), float(poa["cells_full"]), float(poa["n_sets"])], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(pr, op=dist.ReduceOp.MAX)
+            dist.all_reduce(pt, op=dist.ReduceOp.SUM)
+        poa_kms, poa_wall = [float(x) for x in pr.cpu()]
+        poa_cells, poa_full, poa_nsets = [float(x) for x in pt.cpu()]
+
     # ---- max over ranks, whole-job aggregate
     red = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(n_records), float(launches), float(reads_bytes + win_bytes), float(4 * n_win)], dtype=torch.float64, device=dev)
@@ -395,6 +457,20 @@ def run_ours(args):
                                      "work": {k: walker[k] for k in ("n_windows", "n_pairs", "n_words_visited", "n_signatures", "n_overflow")}},
             "poa_gcups": None,
         }
+        if poa is not None:
+            cyc = [float(x) for x in poa["phase_cycles"]]
+            out["poa_gcups"] = {
+                "value": poa_cells / (poa_kms * 1e-3) / 1e9, "unit": "GCUPS (band cells: 5-state convex cell updates actually computed)",
+                "full_matrix_equivalent_gcups": poa_full / (poa_kms * 1e-3) / 1e9,
+                "e2e": {"value": poa_cells / (poa_wall * 1e-3) / 1e9, "unit": "GCUPS", "path": "svtk_poa_consensus: host read sets in, host consensus out, wall clock"},
+                "read_sets_per_s": poa_nsets / (poa_kms * 1e-3), "kernel_ms_per_step": poa_kms, "steps": max(1, args.poa_steps),
+                "workload": POA_DESC + f"; {poa['n_sets']} read sets / {poa['n_reads']} reads / {poa['n_bases'] / 1e6:.0f} Mbases per GPU",
+                "kernel": "k_poa_sets (one 32-thread CTA per read set, persistent workers)", "resident_workers": poa["workers"],
+                "relaunched_sets": poa["relaunched"],
+                "phase_share": dict(zip(("row_dp", "backtrack", "graph_fusion", "topological_sort"), [c / max(sum(cyc), 1.0) for c in cyc])),
+                "bound": "integer ALU / instruction latency (no tensor cores: not a contraction)"}
+            if world == 1 and not args.no_cpu:
+                out["poa_gcups"]["cpu_baseline"] = poa_cpu_baseline(poa_sets_l, poa_cons)
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_port_baseline(rs, w, n_records)
         print(json.dumps(out), flush=True)

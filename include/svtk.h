@@ -221,6 +221,7 @@ typedef struct {
     uint64_t relaunched;     /* read sets that outgrew their first scratch estimate and were rerun with a larger one */
     uint64_t workers;        /* resident warps (= CTAs) of the largest launch */
     double kernel_ms;        /* CUDA-event time of the k_poa_sets launches on the ctx stream */
+    uint64_t phase_cycles[4];/* SM cycles summed over read sets: row DP, backtrack, graph fusion, topological sort */
 } svtk_poa_stats;
 
 enum { SVTK_POA_OK = 0, SVTK_POA_FAILED = 1 };

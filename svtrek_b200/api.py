@@ -64,7 +64,7 @@ class PoaTrace(C.Structure):
 
 
 class PoaStats(C.Structure):
-    _fields_ = [(k, C.c_uint64) for k in ("n_sets", "n_reads", "n_bases", "cells", "cells_full", "relaunched", "workers")] + [("kernel_ms", C.c_double)]
+    _fields_ = [(k, C.c_uint64) for k in ("n_sets", "n_reads", "n_bases", "cells", "cells_full", "relaunched", "workers")] + [("kernel_ms", C.c_double), ("phase_cycles", C.c_uint64 * 4)]
 
 
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
@@ -318,7 +318,7 @@ class Auditor:
         if ns and (clen[:ns] > np.diff(cons_off)).any():       # a consensus longer than its room: rerun with the reported lengths
             return self.poa_consensus(set_off, seq_off, bases, cons_cap=np.maximum(clen[:ns], 1) + 8, want_cov=want_cov, want_trace=want_trace)
         out = [cons[cons_off[s]:cons_off[s] + clen[s]].copy() for s in range(ns)]
-        res = [out, {k: (getattr(st, k)) for k, _ in PoaStats._fields_}]
+        res = [out, {k: (list(getattr(st, k)) if k == "phase_cycles" else getattr(st, k)) for k, _ in PoaStats._fields_}]
         if want_cov:
             res.append([cov[cons_off[s]:cons_off[s] + clen[s]].copy() for s in range(ns)])
         if want_trace:

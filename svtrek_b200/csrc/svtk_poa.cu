@@ -29,7 +29,7 @@ struct PoaCaps {
 
 // layout of one worker's scratch block (byte offsets, 16-byte aligned sections)
 struct PoaLayout {
-    long long base, ints, row_off, edge_id, edge_w, cigar, cells, total;
+    long long base, ints, row_off, edge_id, edge_w, edge_idx, rowmeta, cigar, cells, total;
 };
 constexpr int POA_INT_ARRAYS = 17 + ALN_MAX;
 
@@ -42,6 +42,8 @@ __host__ __device__ inline PoaLayout poa_layout(const PoaCaps &c) {
     L.row_off = o; o = a16(o + 8ll * c.node_cap);
     L.edge_id = o; o = a16(o + 4ll * c.edge_cap);
     L.edge_w = o; o = a16(o + 4ll * c.edge_cap);
+    L.edge_idx = o; o = a16(o + 4ll * c.edge_cap);
+    L.rowmeta = o; o = a16(o + 16ll * c.node_cap);
     L.cigar = o; o = a16(o + 8ll * c.cigar_cap);
     L.cells = o; o = a16(o + c.cell_bytes);
     L.total = (o + 255) & ~255ll;
@@ -67,7 +69,7 @@ struct PoaLaunch {
     int32_t *cov;                      // may be null
     const long long *cons_off;
     int32_t *cons_len, *status;
-    unsigned long long *cells;         // [0] band cells, [1] full-matrix equivalent
+    unsigned long long *cells;         // [0] band cells, [1] full-matrix equivalent, [2..5] SM cycles per phase
     unsigned char *scratch;
     PoaTrace trace;
     int have_trace;
@@ -95,6 +97,8 @@ __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
         s.row_off = reinterpret_cast<long long *>(blk + lay.row_off);
         s.edge_id = reinterpret_cast<int *>(blk + lay.edge_id);
         s.edge_w = reinterpret_cast<int *>(blk + lay.edge_w);
+        s.edge_idx = reinterpret_cast<int *>(blk + lay.edge_idx);
+        s.rowmeta = reinterpret_cast<int4 *>(blk + lay.rowmeta);
         s.cigar = reinterpret_cast<int2 *>(blk + lay.cigar);
         s.cells = blk + lay.cells;
     }
@@ -116,7 +120,10 @@ __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
             if (lane == 0) {
                 L.status[sv] = s.status;
                 L.cons_len[sv] = len;
-                if (!s.status) { atomicAdd(&L.cells[0], (unsigned long long)s.cells_done); atomicAdd(&L.cells[1], (unsigned long long)s.cells_full); }
+                if (!s.status) {
+                    atomicAdd(&L.cells[0], (unsigned long long)s.cells_done); atomicAdd(&L.cells[1], (unsigned long long)s.cells_full);
+                    for (int k = 0; k < 4; ++k) atomicAdd(&L.cells[2 + k], (unsigned long long)s.t_phase[k]);
+                }
             }
             __syncwarp();
         }
@@ -145,11 +152,14 @@ static PoaCaps caps_for(const SetInfo &si, double scale) {
     c.edge_cap = (int)std::min<long long>(8 * nodes + 4ll * si.n + 1024, 0x7fffffffll);
     c.cigar_cap = (int)std::min<long long>(nodes + si.maxlen + 16, 0x7fffffffll);
     const int w = EXTRA_B + (int)(EXTRA_F * (float)si.maxlen);
-    long long width = (long long)(scale * (2 * w + 64 + (si.maxlen - si.minlen)));
+    // band cells of one alignment: rows (graph nodes; ~3.4x the template at 10 % error) x band width
+    // (2w + 1 + arg-max spread + how far qlen - remain drifts from the diagonal, bounded by the length spread)
+    long long width = (long long)(scale * (2 * w + 48 + (si.maxlen - si.minlen)));
     if (width > si.maxlen + 1) width = si.maxlen + 1;
+    const long long dp_rows = std::min<long long>(nodes, (long long)(scale * 4.0 * si.maxlen) + 256);
     const long long len = std::max<long long>(si.maxlen, nodes);
     const int sc_bytes = (std::max<long long>(si.maxlen * MATCH, len * GAP_E1 + GAP_O1) <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2) ? 2 : 4;
-    c.cell_bytes = a16(nodes * width * 5 * sc_bytes);
+    c.cell_bytes = a16(dp_rows * width * 5 * sc_bytes);
     return c;
 }
 
@@ -297,6 +307,16 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             nw[k] = std::max<long long>(1, std::min<long long>(nk, (long long)std::llround((double)W * cwork[k] / std::max(tot_work, 1.0))));
             mem += nw[k] * bytes[k];
         }
+        {   // CTA slots the proportional split left unused (a class cannot use more workers than it has sets) go to the
+            // classes that still have sets without a worker, largest reads first
+            long long used = 0;
+            for (int k = 0; k < K; ++k) used += nw[k];
+            for (int k = 0; k < K && used < W; ++k) {
+                const long long nk = cls[k].item_end - cls[k].item_begin;
+                const long long add = std::min<long long>(nk - nw[k], W - used);
+                nw[k] += add; used += add; mem += add * bytes[k];
+            }
+        }
         while (mem > budget) {                                 // trim the class holding the most scratch
             int big = -1;
             for (int k = 0; k < K; ++k) if (nw[k] > 1 && (big < 0 || nw[k] * bytes[k] > nw[big] * bytes[big])) big = k;
@@ -351,8 +371,8 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         CU(cudaMemcpyAsync(trace->ops_hash, tr.ops_hash, 8 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaMemcpyAsync(trace->cells, tr.cells, 8 * (size_t)n_reads, cudaMemcpyDeviceToHost, c->stream));
     }
-    unsigned long long h_cells[2] = {0, 0};
-    CU(cudaMemcpyAsync(h_cells, d_cells, 16, cudaMemcpyDeviceToHost, c->stream));
+    unsigned long long h_cells[6] = {0, 0, 0, 0, 0, 0};
+    CU(cudaMemcpyAsync(h_cells, d_cells, 48, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->d2h_bytes += (uint64_t)cons_total * (cons_cov ? 5 : 1) + 8ull * ns;
     int n_failed = 0, first_failed = -1, first_code = 0;
@@ -366,6 +386,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         stats->n_sets = (uint64_t)ns; stats->n_reads = (uint64_t)n_reads; stats->n_bases = (uint64_t)n_bases;
         stats->cells = h_cells[0]; stats->cells_full = h_cells[1]; stats->relaunched = relaunched; stats->workers = max_workers;
         stats->kernel_ms = kernel_ms;
+        for (int k = 0; k < 4; ++k) stats->phase_cycles[k] = h_cells[2 + k];
     }
     if (n_failed) return fail(SVTK_ERR_STATE, "poa: %d read set(s) failed, first set %d with internal code %d", n_failed, first_failed, first_code);
     return 0;

@@ -45,6 +45,11 @@ PD int poa_shfl_up(int v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
 PD int poa_max_all(int v) { return __reduce_max_sync(0xffffffffu, v); }
 PD int poa_min_all(int v) { return __reduce_min_sync(0xffffffffu, v); }
 #endif
+#if defined(POA_HOSTSIM)
+static inline long long poa_clock() { return 0; }
+#else
+PD long long poa_clock() { return clock64(); }
+#endif
 
 namespace svtk_poa {
 
@@ -56,6 +61,11 @@ constexpr float EXTRA_F = 0.01f;
 constexpr int SRC = 0, SINK = 1;                              // abpoa.h:31-32
 constexpr int OP_M = 1, OP_E1 = 2, OP_E2 = 4, OP_E = 6, OP_F1 = 8, OP_F2 = 16, OP_F = 24, OP_ALL = 31;   // abpoa_align.h:20-27
 constexpr int CG_MATCH = 0, CG_INS = 1, CG_DEL = 2;           // abpoa.h:20-22
+#ifndef POA_ROW_CB
+#define POA_ROW_CB 2
+#endif
+constexpr int ROW_CB = POA_ROW_CB;                                     // 32-column chunks of a row whose loads are issued together
+constexpr int PRED_REG = 3;                                   // predecessors of a row held in registers (most nodes have 1-2 in-edges)
 constexpr int ALN_MAX = 4;                                    // an aligned group holds distinct bases: <= 5 nodes (m = 5)
 
 enum { POA_OK = 0, POA_ERR_NODES = 1, POA_ERR_EDGES = 2, POA_ERR_CELLS = 3, POA_ERR_CIGAR = 4, POA_ERR_BACKTRACK = 5,
@@ -78,6 +88,10 @@ struct PoaState {
     int *n_read;
     int *idx2id, *id2idx, *max_left, *max_right, *remain;      // index_to_node_id, node_id_to_index, max_pos_left/right, max_remain
     int *deg, *queue;                                          // BFS scratch
+    // what the row DP streams, rebuilt by every topological sort: per INDEX {node id, base | in-degree << 8, first
+    // in-edge slot, max_remain}, and per in-edge slot the predecessor's index
+    int4 *rowmeta;
+    int *edge_idx;
     // one alignment
     int *dp_beg, *dp_end;
     long long *row_off;                                        // first cell of each row's band (in cells)
@@ -86,6 +100,7 @@ struct PoaState {
     int n_cigar;
     int best_score, best_i, best_j;
     long long cells_done, cells_full;                          // band cells / full-matrix-equivalent cells of this read set
+    long long t_phase[4];                                      // SM cycles of this read set in: row DP, backtrack, graph fusion, topological sort
     int status;
 };
 
@@ -221,6 +236,16 @@ PD void poa_topological_sort(PoaState &s) {
     }
     poa_sync();
     if (lane == 0) poa_bfs_remain(s);
+    poa_sync();
+    if (s.status) return;
+    for (int i = lane; i < n; i += POA_NL) {                   // the DP's streaming view of the sorted graph
+        const int id = s.idx2id[i];
+        const int pn = s.in_n[id], po = s.in_off[id];
+        int4 m;
+        m.x = id; m.y = (int)s.base[id] | (pn << 8); m.z = po; m.w = s.remain[id];
+        s.rowmeta[i] = m;
+        for (int k = 0; k < pn; ++k) s.edge_idx[po + k] = s.id2idx[s.edge_id[po + k]];
+    }
     poa_sync();
 }
 
@@ -414,16 +439,42 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     }
     poa_sync();
 
-    // ---- rows 1 .. n-2 in topological index order (simd_abpoa_cg_dp, :935-1074)
+    // ---- rows 1 .. n-2 in topological index order (simd_abpoa_cg_dp, :935-1074).
+    // Latency plan: a row's static description (rowmeta, predecessor indices) is fetched one and two rows ahead; the
+    // previous row's band sits in registers (it is the predecessor of most rows); and a row is computed in blocks of
+    // ROW_CB x 32 columns whose predecessor cells are all requested before the first scan starts, so a block pays one
+    // memory round trip, not one per 32 columns.
+    int lb = 0, le = end0;                                     // band of row i-1
+    long long lo = 0;                                          // its first cell
+    int4 meta = s.rowmeta[1], meta_n = s.rowmeta[imin(2, n - 1)];
+    int pi[PRED_REG];
+#pragma unroll
+    for (int k = 0; k < PRED_REG; ++k) pi[k] = k < (meta.y >> 8) ? s.edge_idx[meta.z + k] : -1;
     for (int i = 1; i < n - 1; ++i) {
-        const int id = s.idx2id[i];
-        const int nb = s.base[id];
-        const int pn = s.in_n[id], po = s.in_off[id];
-        const int rt = qlen - s.remain[id];                    // remain[SINK] == -1 (abpoa_align.h:34-35)
-        int beg = imax(0, imin(s.max_left[id], rt) - w);
-        const int end = imin(qlen, imax(s.max_right[id], rt) + w);
+        const int id = meta.x, nb = meta.y & 0xff, pn = meta.y >> 8, po = meta.z;
+        const int rt = qlen - meta.w;                          // remain[SINK] == -1 (abpoa_align.h:34-35)
+        const int4 meta_nn = s.rowmeta[imin(i + 2, n - 1)];    // in flight during this row
+        int pi_n[PRED_REG];
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) pi_n[k] = k < (meta_n.y >> 8) ? s.edge_idx[meta_n.z + k] : -1;
+        const int ml = s.max_left[id], mr = s.max_right[id];
+        // the first PRED_REG predecessors' bands and row pointers stay in registers for the whole row (an empty slot
+        // has an empty band, so it never contributes); nodes with more in-edges take the generic loop for the rest
+        int pbv[PRED_REG], pev[PRED_REG];
+        const SC *prv[PRED_REG];
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) {
+            pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
+            const int p = pi[k];
+            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
+            else if (p >= 0) { pbv[k] = s.dp_beg[p]; pev[k] = s.dp_end[p]; prv[k] = cells + s.row_off[p] * 5; }
+        }
+        int beg = imax(0, imin(ml, rt) - w);
+        const int end = imin(qlen, imax(mr, rt) + w);
         int min_pre_beg = 0x7fffffff;
-        for (int k = 0; k < pn; ++k) min_pre_beg = imin(min_pre_beg, s.dp_beg[s.id2idx[s.edge_id[po + k]]]);
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) min_pre_beg = imin(min_pre_beg, pbv[k]);
+        for (int k = PRED_REG; k < pn; ++k) min_pre_beg = imin(min_pre_beg, s.dp_beg[s.edge_idx[po + k]]);
         if (beg < min_pre_beg) beg = min_pre_beg;              // :957-959 at vector width 1
         const int wd = end - beg + 1;
         if (wd <= 0 || pn <= 0) { if (lane == 0) s.status = POA_ERR_BAND; poa_sync(); return top; }
@@ -434,47 +485,68 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
         int carry_h = inf_min;                                 // Hme of the column left of the chunk
         int carry_f1 = inf_min - GAP_OE1, carry_f2 = inf_min - GAP_OE2;
         int bv = -2147483647 - 1, bl = -1, br = -1;            // this lane's row maximum, first and last column reaching it
-        for (int c0 = beg; c0 <= end; c0 += POA_NL) {
-            const int j = c0 + lane;
-            const bool valid = j <= end;
-            int m = inf_min, e1in = inf_min, e2in = inf_min;
-            if (valid) {
-                for (int k = 0; k < pn; ++k) {                 // predecessors in in-edge order; max is order independent
-                    const int p = s.id2idx[s.edge_id[po + k]];
-                    const int pb = s.dp_beg[p], pe = s.dp_end[p], pw = pe - pb + 1;
-                    const SC *pr = cells + s.row_off[p] * 5;
-                    if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
-                    if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+        for (int cb = beg; cb <= end; cb += ROW_CB * POA_NL) {
+            int hmev[ROW_CB], e1v[ROW_CB], e2v[ROW_CB];
+            // pass 1: every predecessor cell of the block is requested here (independent loads)
+#pragma unroll
+            for (int u = 0; u < ROW_CB; ++u) {
+                const int j = cb + u * POA_NL + lane;
+                const bool valid = j <= end;
+                int m = inf_min, e1in = inf_min, e2in = inf_min, sc = 0;
+                if (valid) {
+#pragma unroll
+                    for (int k = 0; k < PRED_REG; ++k) {       // max over predecessors is order independent
+                        const int pb = pbv[k], pe = pev[k], pw = pe - pb + 1;
+                        const SC *pr = prv[k];
+                        if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
+                        if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+                    }
+                    for (int k = PRED_REG; k < pn; ++k) {
+                        const int p = s.edge_idx[po + k];
+                        const int pb = s.dp_beg[p], pe = s.dp_end[p], pw = pe - pb + 1;
+                        const SC *pr = cells + s.row_off[p] * 5;
+                        if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
+                        if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+                    }
+                    if (j > 0) sc = poa_score(nb, q[j - 1]);   // query profile column 0 is 0 (:520)
                 }
+                hmev[u] = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
+                e1v[u] = e1in; e2v[u] = e2in;
             }
-            const int sc = (valid && j > 0) ? poa_score(nb, q[j - 1]) : 0;   // query profile column 0 is 0 (:520)
-            const int hme = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
-            // F[j] = max(Hme[j-1] - oe, F[j-1] - e): prefix max of (Hme[k-1] - oe + k*e) across the lanes (:1052-1059)
-            int left = poa_shfl_up(hme, 1);
-            if (lane == 0) left = carry_h;
-            int g1 = left - GAP_OE1 + lane * GAP_E1, g2 = left - GAP_OE2 + lane * GAP_E2;
+            // pass 2: F[j] = max(Hme[j-1] - oe, F[j-1] - e) as a prefix max of (Hme[k-1] - oe + k*e) across the lanes (:1052-1059)
+#pragma unroll
+            for (int u = 0; u < ROW_CB; ++u) {
+                const int c0 = cb + u * POA_NL;
+                if (c0 > end) break;
+                const int j = c0 + lane;
+                const bool valid = j <= end;
+                const int hme = hmev[u];
+                int left = poa_shfl_up(hme, 1);
+                if (lane == 0) left = carry_h;
+                int g1 = left - GAP_OE1 + lane * GAP_E1, g2 = left - GAP_OE2 + lane * GAP_E2;
 #if POA_NL > 1
 #pragma unroll
-            for (int d = 1; d < POA_NL; d <<= 1) {
-                const int t1 = poa_shfl_up(g1, d), t2 = poa_shfl_up(g2, d);
-                if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
-            }
+                for (int d = 1; d < POA_NL; d <<= 1) {
+                    const int t1 = poa_shfl_up(g1, d), t2 = poa_shfl_up(g2, d);
+                    if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
+                }
 #endif
-            const int f1 = imax(g1 - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
-            const int f2 = imax(g2 - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
-            const int h = imax(hme, imax(f1, f2));
-            if (valid) {
-                const int x = j - beg;
-                row[x] = (SC)h;
-                row[wd + x] = (SC)imax(e1in - GAP_E1, h - GAP_OE1);        // E for the next row (:1067-1071)
-                row[2 * wd + x] = (SC)imax(e2in - GAP_E2, h - GAP_OE2);
-                row[3 * wd + x] = (SC)f1;
-                row[4 * wd + x] = (SC)f2;
-                if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
+                const int f1 = imax(g1 - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
+                const int f2 = imax(g2 - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
+                const int h = imax(hme, imax(f1, f2));
+                if (valid) {
+                    const int x = j - beg;
+                    row[x] = (SC)h;
+                    row[wd + x] = (SC)imax(e1v[u] - GAP_E1, h - GAP_OE1);      // E for the next row (:1067-1071)
+                    row[2 * wd + x] = (SC)imax(e2v[u] - GAP_E2, h - GAP_OE2);
+                    row[3 * wd + x] = (SC)f1;
+                    row[4 * wd + x] = (SC)f2;
+                    if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
+                }
+                carry_h = poa_shfl(hme, POA_NL - 1);
+                carry_f1 = poa_shfl(f1, POA_NL - 1);
+                carry_f2 = poa_shfl(f2, POA_NL - 1);
             }
-            carry_h = poa_shfl(hme, POA_NL - 1);
-            carry_f1 = poa_shfl(f1, POA_NL - 1);
-            carry_f2 = poa_shfl(f2, POA_NL - 1);
         }
         // row arg-max -> band hints of the successors (simd_abpoa_max_in_row :1107-1119, simd_abpoa_ada_max_i :1121-1130)
         const int vmax = poa_max_all(bv);
@@ -488,7 +560,11 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             if (right_i + 1 > s.max_right[o]) s.max_right[o] = right_i + 1;
             if (left_i + 1 < s.max_left[o]) s.max_left[o] = left_i + 1;
         }
+        lb = beg; le = end; lo = top;
         top += wd;
+        meta = meta_n; meta_n = meta_nn;
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) pi[k] = pi_n[k];
         poa_sync();
     }
     // ---- best end cell among SINK's predecessors (simd_abpoa_global_get_max, :1092-1105)
@@ -575,6 +651,7 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
     const int lane = poa_lane();
     if (lane == 0) {                                           // abpoa_reset (abpoa_graph.c:782): graph = {SRC, SINK}
         s.node_n = 0; s.edge_top = 0; s.status = POA_OK; s.n_cigar = 0; s.cells_done = 0; s.cells_full = 0;
+        s.t_phase[0] = s.t_phase[1] = s.t_phase[2] = s.t_phase[3] = 0;
         poa_add_node(s, 0); poa_add_node(s, 0);
     }
     poa_sync();
@@ -591,10 +668,13 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
             const int len = qlen > rows ? qlen : rows;
             const int max_score = imax(qlen * MATCH, len * GAP_E1 + GAP_O1);
             const bool use16 = max_score <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2;
+            const long long t0 = poa_clock();
             if (use16) cells = poa_align_dp<int16_t>(s, q, qlen, INF_MIN16);
             else cells = poa_align_dp<int32_t>(s, q, qlen, INF_MIN32);
             if (lane == 0 && !s.status) {
+                const long long t1 = poa_clock();
                 if (use16) poa_backtrack<int16_t>(s, q, qlen, INF_MIN16); else poa_backtrack<int32_t>(s, q, qlen, INF_MIN32);
+                s.t_phase[0] += t1 - t0; s.t_phase[1] += poa_clock() - t1;
                 s.cells_done += cells;
                 s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
             }
@@ -616,12 +696,16 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
                 }
                 tr->ops_hash[r] = h; tr->n_ops[r] = nops;
             }
+            const long long t2 = poa_clock();
             if (rows > 2) poa_add_alignment(s, q, qlen);
+            s.t_phase[2] += poa_clock() - t2;
             if (tr && tr->best_score) { tr->best_score[r] = rows > 2 ? s.best_score : 0; tr->cells[r] = cells; }
         }
         poa_sync();
         if (s.status) break;
+        const long long t3 = poa_clock();
         poa_topological_sort(s);
+        if (lane == 0) s.t_phase[3] += poa_clock() - t3;
         if (lane == 0 && tr && tr->node_n) tr->node_n[r] = s.node_n;
         poa_sync();
     }

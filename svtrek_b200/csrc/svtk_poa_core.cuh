@@ -219,15 +219,16 @@ PD void poa_bfs_remain(PoaState &s) {                          // abpoa_BFS_set_
 }
 
 // abpoa_topological_sort (abpoa_graph.c:322): all lanes enter
-PD void poa_topological_sort(PoaState &s) {
+PD void poa_topological_sort(PoaState &sh) {
     const int lane = poa_lane();
     poa_sync();
+    PoaState s = sh;                                           // register copy: the shared struct would be re-read after every store
     const int n = s.node_n;
     for (int i = lane; i < n; i += POA_NL) s.deg[i] = s.in_n[i];
     poa_sync();
-    if (lane == 0) poa_bfs_index(s);
+    if (lane == 0) { poa_bfs_index(s); sh.status = s.status; }
     poa_sync();
-    if (s.status) return;
+    if (sh.status) return;
     for (int i = lane; i < n; i += POA_NL) {                   // independent per node: lanes take nodes
         poa_sort_edges(s.edge_id + s.in_off[i], s.edge_w + s.in_off[i], s.in_n[i]);
         poa_sort_edges(s.edge_id + s.out_off[i], s.edge_w + s.out_off[i], s.out_n[i]);
@@ -235,9 +236,9 @@ PD void poa_topological_sort(PoaState &s) {
         s.deg[i] = s.out_n[i]; s.remain[i] = 0;
     }
     poa_sync();
-    if (lane == 0) poa_bfs_remain(s);
+    if (lane == 0) { poa_bfs_remain(s); sh.status = s.status; }
     poa_sync();
-    if (s.status) return;
+    if (sh.status) return;
     for (int i = lane; i < n; i += POA_NL) {                   // the DP's streaming view of the sorted graph
         const int id = s.idx2id[i];
         const int pn = s.in_n[id], po = s.in_off[id];
@@ -412,23 +413,24 @@ PD void poa_backtrack(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
 template <typename SC>
 PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
     const int lane = poa_lane();
-    const int n = s.node_n;
+    const PoaState g = s;                                      // register copy of the pointer block (s lives in shared memory)
+    const int n = g.node_n;
     const int w = EXTRA_B + (int)(EXTRA_F * (float)qlen);      // abpoa_align_simd.c:474
-    SC *cells = reinterpret_cast<SC *>(s.cells);
-    const long long cell_cap = s.cell_bytes / (long long)(5 * sizeof(SC));
+    SC *cells = reinterpret_cast<SC *>(g.cells);
+    const long long cell_cap = g.cell_bytes / (long long)(5 * sizeof(SC));
     long long top = 0;
 
     // ---- first row (simd_abpoa_cg_first_row / _first_dp, :669-688, :617-633)
     if (lane == 0) {
-        s.max_left[SRC] = s.max_right[SRC] = 0;
-        for (int i = 0; i < s.out_n[SRC]; ++i) { const int o = s.edge_id[s.out_off[SRC] + i]; s.max_left[o] = s.max_right[o] = 1; }
+        g.max_left[SRC] = g.max_right[SRC] = 0;
+        for (int i = 0; i < g.out_n[SRC]; ++i) { const int o = g.edge_id[g.out_off[SRC] + i]; g.max_left[o] = g.max_right[o] = 1; }
     }
     poa_sync();
-    const int end0 = imin(qlen, imax(s.max_right[SRC], qlen - s.remain[SRC]) + w);
+    const int end0 = imin(qlen, imax(g.max_right[SRC], qlen - g.remain[SRC]) + w);
     {
         const int w0 = end0 + 1;
         if (w0 > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return 0; }
-        if (lane == 0) { s.dp_beg[0] = 0; s.dp_end[0] = end0; s.row_off[0] = 0; }
+        if (lane == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; }
         for (int j = lane; j <= end0; j += POA_NL) {
             int h, e1 = inf_min, e2 = inf_min, f1, f2;
             if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
@@ -446,18 +448,18 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     // memory round trip, not one per 32 columns.
     int lb = 0, le = end0;                                     // band of row i-1
     long long lo = 0;                                          // its first cell
-    int4 meta = s.rowmeta[1], meta_n = s.rowmeta[imin(2, n - 1)];
+    int4 meta = g.rowmeta[1], meta_n = g.rowmeta[imin(2, n - 1)];
     int pi[PRED_REG];
 #pragma unroll
-    for (int k = 0; k < PRED_REG; ++k) pi[k] = k < (meta.y >> 8) ? s.edge_idx[meta.z + k] : -1;
+    for (int k = 0; k < PRED_REG; ++k) pi[k] = k < (meta.y >> 8) ? g.edge_idx[meta.z + k] : -1;
     for (int i = 1; i < n - 1; ++i) {
         const int id = meta.x, nb = meta.y & 0xff, pn = meta.y >> 8, po = meta.z;
         const int rt = qlen - meta.w;                          // remain[SINK] == -1 (abpoa_align.h:34-35)
-        const int4 meta_nn = s.rowmeta[imin(i + 2, n - 1)];    // in flight during this row
+        const int4 meta_nn = g.rowmeta[imin(i + 2, n - 1)];    // in flight during this row
         int pi_n[PRED_REG];
 #pragma unroll
-        for (int k = 0; k < PRED_REG; ++k) pi_n[k] = k < (meta_n.y >> 8) ? s.edge_idx[meta_n.z + k] : -1;
-        const int ml = s.max_left[id], mr = s.max_right[id];
+        for (int k = 0; k < PRED_REG; ++k) pi_n[k] = k < (meta_n.y >> 8) ? g.edge_idx[meta_n.z + k] : -1;
+        const int ml = g.max_left[id], mr = g.max_right[id];
         // the first PRED_REG predecessors' bands and row pointers stay in registers for the whole row (an empty slot
         // has an empty band, so it never contributes); nodes with more in-edges take the generic loop for the rest
         int pbv[PRED_REG], pev[PRED_REG];
@@ -467,20 +469,20 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
             const int p = pi[k];
             if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
-            else if (p >= 0) { pbv[k] = s.dp_beg[p]; pev[k] = s.dp_end[p]; prv[k] = cells + s.row_off[p] * 5; }
+            else if (p >= 0) { pbv[k] = g.dp_beg[p]; pev[k] = g.dp_end[p]; prv[k] = cells + g.row_off[p] * 5; }
         }
         int beg = imax(0, imin(ml, rt) - w);
         const int end = imin(qlen, imax(mr, rt) + w);
         int min_pre_beg = 0x7fffffff;
 #pragma unroll
         for (int k = 0; k < PRED_REG; ++k) min_pre_beg = imin(min_pre_beg, pbv[k]);
-        for (int k = PRED_REG; k < pn; ++k) min_pre_beg = imin(min_pre_beg, s.dp_beg[s.edge_idx[po + k]]);
+        for (int k = PRED_REG; k < pn; ++k) min_pre_beg = imin(min_pre_beg, g.dp_beg[g.edge_idx[po + k]]);
         if (beg < min_pre_beg) beg = min_pre_beg;              // :957-959 at vector width 1
         const int wd = end - beg + 1;
         if (wd <= 0 || pn <= 0) { if (lane == 0) s.status = POA_ERR_BAND; poa_sync(); return top; }
         if (top + wd > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return top; }
         SC *row = cells + top * 5;
-        if (lane == 0) { s.dp_beg[i] = beg; s.dp_end[i] = end; s.row_off[i] = top; }
+        if (lane == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; }
 
         int carry_h = inf_min;                                 // Hme of the column left of the chunk
         int carry_f1 = inf_min - GAP_OE1, carry_f2 = inf_min - GAP_OE2;
@@ -502,9 +504,9 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                         if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
                     }
                     for (int k = PRED_REG; k < pn; ++k) {
-                        const int p = s.edge_idx[po + k];
-                        const int pb = s.dp_beg[p], pe = s.dp_end[p], pw = pe - pb + 1;
-                        const SC *pr = cells + s.row_off[p] * 5;
+                        const int p = g.edge_idx[po + k];
+                        const int pb = g.dp_beg[p], pe = g.dp_end[p], pw = pe - pb + 1;
+                        const SC *pr = cells + g.row_off[p] * 5;
                         if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
                         if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
                     }
@@ -555,10 +557,10 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             right_i = poa_max_all(bv == vmax ? br : -1);
             if (vmax > inf_min) left_i = poa_min_all(bv == vmax ? bl : 0x7fffffff);
         }
-        for (int k = lane; k < s.out_n[id]; k += POA_NL) {
-            const int o = s.edge_id[s.out_off[id] + k];
-            if (right_i + 1 > s.max_right[o]) s.max_right[o] = right_i + 1;
-            if (left_i + 1 < s.max_left[o]) s.max_left[o] = left_i + 1;
+        for (int k = lane; k < g.out_n[id]; k += POA_NL) {
+            const int o = g.edge_id[g.out_off[id] + k];
+            if (right_i + 1 > g.max_right[o]) g.max_right[o] = right_i + 1;
+            if (left_i + 1 < g.max_left[o]) g.max_left[o] = left_i + 1;
         }
         lb = beg; le = end; lo = top;
         top += wd;
@@ -570,10 +572,10 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     // ---- best end cell among SINK's predecessors (simd_abpoa_global_get_max, :1092-1105)
     if (lane == 0) {
         int best = inf_min, bi = 0, bj = 0;
-        for (int k = 0; k < s.in_n[SINK]; ++k) {
-            const int p = s.id2idx[s.edge_id[s.in_off[SINK] + k]];
-            const int e = qlen > s.dp_end[p] ? s.dp_end[p] : qlen;
-            const int v = poa_cell<SC>(s, p, 0, e, inf_min);
+        for (int k = 0; k < g.in_n[SINK]; ++k) {
+            const int p = g.id2idx[g.edge_id[g.in_off[SINK] + k]];
+            const int e = qlen > g.dp_end[p] ? g.dp_end[p] : qlen;
+            const int v = poa_cell<SC>(g, p, 0, e, inf_min);
             if (v > best) { best = v; bi = p; bj = e; }
         }
         s.best_score = best; s.best_i = bi; s.best_j = bj;
@@ -662,7 +664,12 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
         long long cells = 0;
         const int rows = s.node_n;
         if (rows <= 2) {                                       // abpoa_align_sequence_to_graph returns -1 (abpoa_align.c:201)
-            if (lane == 0) { s.n_cigar = 0; s.best_score = 0; poa_add_first(s, q, qlen); }
+            if (lane == 0) {
+                PoaState g = s;
+                g.n_cigar = 0; g.best_score = 0;
+                poa_add_first(g, q, qlen);
+                s = g;
+            }
         } else {
             // score width (abpoa_align_simd.c:1291-1302)
             const int len = qlen > rows ? qlen : rows;
@@ -673,7 +680,9 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
             else cells = poa_align_dp<int32_t>(s, q, qlen, INF_MIN32);
             if (lane == 0 && !s.status) {
                 const long long t1 = poa_clock();
-                if (use16) poa_backtrack<int16_t>(s, q, qlen, INF_MIN16); else poa_backtrack<int32_t>(s, q, qlen, INF_MIN32);
+                PoaState g = s;
+                if (use16) poa_backtrack<int16_t>(g, q, qlen, INF_MIN16); else poa_backtrack<int32_t>(g, q, qlen, INF_MIN32);
+                s.n_cigar = g.n_cigar; s.status = g.status;
                 s.t_phase[0] += t1 - t0; s.t_phase[1] += poa_clock() - t1;
                 s.cells_done += cells;
                 s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
@@ -697,7 +706,11 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
                 tr->ops_hash[r] = h; tr->n_ops[r] = nops;
             }
             const long long t2 = poa_clock();
-            if (rows > 2) poa_add_alignment(s, q, qlen);
+            if (rows > 2) {
+                PoaState g = s;
+                poa_add_alignment(g, q, qlen);
+                s.node_n = g.node_n; s.edge_top = g.edge_top; s.status = g.status;
+            }
             s.t_phase[2] += poa_clock() - t2;
             if (tr && tr->best_score) { tr->best_score[r] = rows > 2 ? s.best_score : 0; tr->cells[r] = cells; }
         }
@@ -710,7 +723,11 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
         poa_sync();
     }
     int len = 0;
-    if (lane == 0 && !s.status && s.node_n > 2) len = poa_consensus(s, cons, cov, cons_cap);
+    if (lane == 0 && !s.status && s.node_n > 2) {
+        PoaState g = s;
+        len = poa_consensus(g, cons, cov, cons_cap);
+        s.status = g.status;
+    }
     poa_sync();
     len = poa_shfl(len, 0);
     return s.status ? 0 : len;

@@ -336,7 +336,8 @@ void svtk_destroy(svtk_ctx *ctx) {
                       &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
-    for (int i = 0; i < 2; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
+    for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
+    if (c->poa_side) cudaStreamDestroy(c->poa_side);
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);

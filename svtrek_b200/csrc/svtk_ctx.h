@@ -71,7 +71,8 @@ struct Ctx {
     // K3 (svtk_poa.cu): device copies of one batch of read sets, per-worker scratch, events
     DevBuf poa_in, poa_out, poa_scratch, poa_ctl;
     PinBuf poa_h;
-    cudaEvent_t poa_ev[2] = {nullptr, nullptr};
+    cudaEvent_t poa_ev[3] = {nullptr, nullptr, nullptr};
+    cudaStream_t poa_side = nullptr;      // the CTA-wide launch of the heaviest read sets runs beside the warp-per-set launch
 
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;

@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -75,8 +76,12 @@ struct PoaLaunch {
     int have_trace;
 };
 
-__global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
+// NW = 1: one warp per read set (the throughput shape).  NW = 8: the whole 256-thread CTA shares each DP row and the
+// parallel parts of the sort -- used for the few heaviest sets, whose single-warp latency would be the batch's tail.
+template <int NW>
+__global__ void __launch_bounds__(32 * NW) k_poa_sets(PoaLaunch L) {
     __shared__ PoaState s;
+    __shared__ PoaXchg xch;
     __shared__ int s_item, s_cls;
     const int lane = threadIdx.x;
     if (lane == 0) {
@@ -102,20 +107,20 @@ __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
         s.cigar = reinterpret_cast<int2 *>(blk + lay.cigar);
         s.cells = blk + lay.cells;
     }
-    __syncwarp();
+    __syncthreads();
     // own class first, then every smaller one (their sets fit this worker's block): no CTA idles while sets remain
     for (int k = s_cls; k < L.n_classes; ++k) {
         const int i0 = L.classes[k].item_begin, n_items = L.classes[k].item_end - i0;
         while (true) {
             if (lane == 0) s_item = atomicAdd(L.cursors + k, 1);
-            __syncwarp();
+            __syncthreads();
             const int it = s_item;
-            __syncwarp();
+            __syncthreads();
             if (it >= n_items) break;
             const int sv = L.items[i0 + it];
             const long long co = L.cons_off[sv];
             const int cap = (int)(L.cons_off[sv + 1] - co);
-            const int len = poa_run_set(s, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
+            const int len = poa_run_set<NW>(s, xch, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
                                         L.have_trace ? &L.trace : nullptr);
             if (lane == 0) {
                 L.status[sv] = s.status;
@@ -125,7 +130,7 @@ __global__ void __launch_bounds__(32) k_poa_sets(PoaLaunch L) {
                     for (int k = 0; k < 4; ++k) atomicAdd(&L.cells[2 + k], (unsigned long long)s.t_phase[k]);
                 }
             }
-            __syncwarp();
+            __syncthreads();
         }
     }
 }
@@ -168,6 +173,58 @@ static PoaCaps caps_max(const PoaCaps &a, const PoaCaps &b) {
     c.node_cap = std::max(a.node_cap, b.node_cap); c.edge_cap = std::max(a.edge_cap, b.edge_cap);
     c.cigar_cap = std::max(a.cigar_cap, b.cigar_cap); c.cell_bytes = std::max(a.cell_bytes, b.cell_bytes);
     return c;
+}
+
+// Size classes, workers and scratch of one launch over items[0 .. n) (sorted: class descending, work descending).
+// W = CTAs wanted at most.  Fills cls (item ranges relative to item_base, workers and scratch offsets relative to 0).
+static int plan_group(const std::vector<SetInfo> &info, const int *items, size_t n, int item_base, double scale, long long W,
+                      long long budget, std::vector<PoaClass> &cls, long long &workers, long long &bytes_total) {
+    cls.clear(); workers = 0; bytes_total = 0;
+    if (n == 0) return 0;
+    std::vector<double> cwork;
+    for (size_t i0 = 0; i0 < n;) {
+        size_t i1 = i0;
+        PoaCaps caps = caps_for(info[items[i0]], scale);
+        double wk = 0;
+        while (i1 < n && info[items[i1]].cls == info[items[i0]].cls) { caps = caps_max(caps, caps_for(info[items[i1]], scale)); wk += info[items[i1]].work; ++i1; }
+        PoaClass pc{};
+        pc.item_begin = item_base + (int)i0; pc.item_end = item_base + (int)i1; pc.caps = caps;
+        cls.push_back(pc); cwork.push_back(wk);
+        i0 = i1;
+    }
+    const int K = (int)cls.size();
+    for (int k = K - 2; k >= 0; --k) cls[k].caps = caps_max(cls[k].caps, cls[k + 1].caps);   // stealing downwards must fit
+    W = std::min<long long>(W, (long long)n);
+    double tot_work = 0;
+    for (double x : cwork) tot_work += x;
+    std::vector<long long> nw(K), bytes(K);
+    long long mem = 0, used = 0;
+    for (int k = 0; k < K; ++k) {                              // share of the CTAs proportional to the class's work
+        bytes[k] = poa_layout(cls[k].caps).total;
+        if (bytes[k] > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", bytes[k], budget);
+        const long long nk = cls[k].item_end - cls[k].item_begin;
+        nw[k] = std::max<long long>(1, std::min<long long>(nk, (long long)std::llround((double)W * cwork[k] / std::max(tot_work, 1.0))));
+        mem += nw[k] * bytes[k]; used += nw[k];
+    }
+    for (int k = 0; k < K && used < W; ++k) {                  // slots the split left unused: largest reads first
+        const long long nk = cls[k].item_end - cls[k].item_begin;
+        const long long add = std::min<long long>(nk - nw[k], W - used);
+        nw[k] += add; used += add; mem += add * bytes[k];
+    }
+    while (mem > budget) {                                     // trim the class holding the most scratch
+        int big = -1;
+        for (int k = 0; k < K; ++k) if (nw[k] > 1 && (big < 0 || nw[k] * bytes[k] > nw[big] * bytes[big])) big = k;
+        if (big < 0) return fail(SVTK_ERR_ALLOC, "poa: scratch for one worker per size class (%lld bytes) exceeds the budget %lld", mem, budget);
+        const long long cut = std::max<long long>(1, nw[big] / 10);
+        nw[big] -= cut; mem -= cut * bytes[big];
+    }
+    long long off = 0;
+    for (int k = 0; k < K; ++k) {
+        cls[k].worker_begin = (int)workers; workers += nw[k]; cls[k].worker_end = (int)workers;
+        cls[k].scratch_off = off; off += nw[k] * bytes[k];
+    }
+    bytes_total = off;
+    return 0;
 }
 
 }  // namespace svtk
@@ -247,14 +304,28 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     }
     CU(cudaMemsetAsync(d_len, 0, a16(4 * ns) * 2, c->stream));
 
-    // control block: cells[2] | 64 class cursors | 64 class descriptors | item list
-    const size_t ctl_bytes = 64 + 4 * 64 + a16(sizeof(PoaClass) * 64) + 4 * (size_t)ns;
+    // control block: cells[6] | 128 class cursors | 128 class descriptors | item list
+    constexpr int MAXC = 128;
+    const size_t ctl_bytes = 64 + 4 * MAXC + a16(sizeof(PoaClass) * MAXC) + 4 * (size_t)ns;
     if (int rc = c->poa_ctl.reserve(ctl_bytes)) return rc;
     unsigned long long *d_cells = (unsigned long long *)c->poa_ctl.p;
     int *d_cursors = (int *)((unsigned char *)c->poa_ctl.p + 64);
-    PoaClass *d_classes = (PoaClass *)((unsigned char *)c->poa_ctl.p + 64 + 4 * 64);
-    int *d_items = (int *)((unsigned char *)d_classes + a16(sizeof(PoaClass) * 64));
-    for (int i = 0; i < 2; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
+    PoaClass *d_classes = (PoaClass *)((unsigned char *)c->poa_ctl.p + 64 + 4 * MAXC);
+    int *d_items = (int *)((unsigned char *)d_classes + a16(sizeof(PoaClass) * MAXC));
+    for (int i = 0; i < 3; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
+    if (!c->poa_side) {
+        CU(cudaStreamCreateWithFlags(&c->poa_side, cudaStreamNonBlocking));
+        // First use: run both instantiations once with no work.  k_poa_sets<1> needs a larger local-memory pool than
+        // k_poa_sets<8>; growing that pool is a device-wide synchronisation, which would otherwise serialise the first
+        // pair of launches (measured: 12.1 s instead of 6.7 s for the first batch).
+        CU(cudaMemsetAsync(d_classes, 0, sizeof(PoaClass) * MAXC, c->stream));
+        PoaLaunch L0{};
+        L0.classes = d_classes; L0.cursors = d_cursors; L0.scratch = (unsigned char *)c->poa_ctl.p;
+        k_poa_sets<1><<<1, 32, 0, c->stream>>>(L0);
+        k_poa_sets<8><<<1, 256, 0, c->stream>>>(L0);
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(c->stream));
+    }
 
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
@@ -265,12 +336,14 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     std::vector<int32_t> h_status(ns, 0);
     double scale = 1.0, kernel_ms = 0.0;
     if (const char *e = getenv("SVTK_POA_SCALE")) { const double v = atof(e); if (v > 0.0) scale = v; }   // tests: start from a too-small block
+    int wide_on = 1;
+    if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere
     uint64_t relaunched = 0, max_workers = 0;
     CU(cudaMemsetAsync(d_cells, 0, 64, c->stream));
-    int max_resident = 148 * 32;
+    int sms = 148;
     {
         int dev_sms = 0;
-        if (cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, c->device) == cudaSuccess && dev_sms > 0) max_resident = dev_sms * 32;
+        if (cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, c->device) == cudaSuccess && dev_sms > 0) sms = dev_sms;
     }
     for (int attempt = 0; attempt < 6 && !todo.empty(); ++attempt) {
         // classes, largest reads first; inside a class heaviest set first (the atomic queue then balances the tail)
@@ -279,76 +352,79 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             if (info[x].work != info[y].work) return info[x].work > info[y].work;
             return x < y;
         });
-        std::vector<PoaClass> cls;
-        std::vector<double> cwork;
-        for (size_t i0 = 0; i0 < todo.size();) {
-            size_t i1 = i0;
-            PoaCaps caps = caps_for(info[todo[i0]], scale);
-            double wk = 0;
-            while (i1 < todo.size() && info[todo[i1]].cls == info[todo[i0]].cls) { caps = caps_max(caps, caps_for(info[todo[i1]], scale)); wk += info[todo[i1]].work; ++i1; }
-            PoaClass pc{};
-            pc.item_begin = (int)i0; pc.item_end = (int)i1; pc.caps = caps;
-            cls.push_back(pc); cwork.push_back(wk);
-            i0 = i1;
-        }
-        if (cls.size() > 64) return fail(SVTK_ERR_ARG, "poa: more than 64 size classes");
-        for (int k = (int)cls.size() - 2; k >= 0; --k) cls[k].caps = caps_max(cls[k].caps, cls[k + 1].caps);   // stealing downwards must fit
-        // workers per class: share of the resident CTAs proportional to the class's work, within the scratch budget
-        const int K = (int)cls.size();
-        const long long W = std::min<long long>((long long)todo.size(), max_resident);
-        double tot_work = 0;
-        for (double x : cwork) tot_work += x;
-        std::vector<long long> nw(K), bytes(K);
-        long long mem = 0;
-        for (int k = 0; k < K; ++k) {
-            bytes[k] = poa_layout(cls[k].caps).total;
-            if (bytes[k] > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", bytes[k], budget);
-            const long long nk = cls[k].item_end - cls[k].item_begin;
-            nw[k] = std::max<long long>(1, std::min<long long>(nk, (long long)std::llround((double)W * cwork[k] / std::max(tot_work, 1.0))));
-            mem += nw[k] * bytes[k];
-        }
-        {   // CTA slots the proportional split left unused (a class cannot use more workers than it has sets) go to the
-            // classes that still have sets without a worker, largest reads first
-            long long used = 0;
-            for (int k = 0; k < K; ++k) used += nw[k];
-            for (int k = 0; k < K && used < W; ++k) {
-                const long long nk = cls[k].item_end - cls[k].item_begin;
-                const long long add = std::min<long long>(nk - nw[k], W - used);
-                nw[k] += add; used += add; mem += add * bytes[k];
+        // A set alone on a warp can outlast the rest of the batch.  The sets within 1/WIDE_GAIN of the heaviest one's work (reads
+        // beyond 2 kb, at most one per SM: a 256-thread CTA holds half an SM's registers) get a whole CTA each (k_poa_sets<8>),
+        // which finishes them ~WIDE_GAIN x sooner; everything else runs one warp per set, the shape that fills the SMs.
+        constexpr double WIDE_GAIN = 1.5;
+        std::vector<int> wide, rest;
+        {
+            double wmax = 0;
+            for (int x : todo) wmax = std::max(wmax, info[x].work);
+            std::vector<int> by_work(todo);
+            std::sort(by_work.begin(), by_work.end(), [&](int x, int y) { return info[x].work != info[y].work ? info[x].work > info[y].work : x < y; });
+            std::vector<char> is_wide(ns, 0);
+            for (int x : by_work) {
+                if (!wide_on || (int)wide.size() >= sms || info[x].maxlen <= 2048 || info[x].work * WIDE_GAIN < wmax) break;
+                wide.push_back(x); is_wide[x] = 1;
             }
+            for (int x : todo) if (!is_wide[x]) rest.push_back(x);
+            std::sort(wide.begin(), wide.end(), [&](int x, int y) {
+                if (info[x].cls != info[y].cls) return info[x].cls > info[y].cls;
+                if (info[x].work != info[y].work) return info[x].work > info[y].work;
+                return x < y;
+            });
+            todo = wide;
+            todo.insert(todo.end(), rest.begin(), rest.end());
         }
-        while (mem > budget) {                                 // trim the class holding the most scratch
-            int big = -1;
-            for (int k = 0; k < K; ++k) if (nw[k] > 1 && (big < 0 || nw[k] * bytes[k] > nw[big] * bytes[big])) big = k;
-            if (big < 0) return fail(SVTK_ERR_ALLOC, "poa: scratch for one worker per size class (%lld bytes) exceeds the budget %lld", mem, budget);
-            const long long cut = std::max<long long>(1, nw[big] / 10);
-            nw[big] -= cut; mem -= cut * bytes[big];
-        }
-        long long workers = 0, off = 0;
-        for (int k = 0; k < K; ++k) {
-            cls[k].worker_begin = (int)workers; workers += nw[k]; cls[k].worker_end = (int)workers;
-            cls[k].scratch_off = off; off += nw[k] * bytes[k];
-        }
-        if (int rc = c->poa_scratch.reserve((size_t)off)) return rc;
+        const size_t nA = wide.size();
+        std::vector<PoaClass> clsA, clsB;
+        long long wA = 0, wB = 0, memA = 0, memB = 0;
+        if (int rc = plan_group(info, todo.data(), nA, 0, scale, (long long)nA, (long long)(0.6 * (double)budget), clsA, wA, memA)) return rc;
+        if (int rc = plan_group(info, todo.data() + nA, todo.size() - nA, (int)nA, scale, (long long)sms * 32, budget - memA, clsB, wB, memB)) return rc;
+        if (clsA.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
+        for (PoaClass &pc : clsB) pc.scratch_off += memA;
+        std::vector<PoaClass> cls(clsA);
+        cls.insert(cls.end(), clsB.begin(), clsB.end());
+        if (int rc = c->poa_scratch.reserve((size_t)(memA + memB))) return rc;
         CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(d_classes, cls.data(), sizeof(PoaClass) * cls.size(), cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemsetAsync(d_cursors, 0, 4 * 64, c->stream));
+        CU(cudaMemsetAsync(d_cursors, 0, 4 * MAXC, c->stream));
         PoaLaunch L{};
-        L.n_classes = K; L.classes = d_classes; L.items = d_items; L.cursors = d_cursors;
+        L.items = d_items;
         L.set_off = d_set_off; L.seq_off = d_seq_off; L.bases = d_bases; L.cons = d_cons; L.cov = d_cov; L.cons_off = d_cons_off;
         L.cons_len = d_len; L.status = d_status; L.cells = d_cells; L.scratch = (unsigned char *)c->poa_scratch.p;
         L.trace = tr; L.have_trace = trace ? 1 : 0;
         CU(cudaEventRecord(c->poa_ev[0], c->stream));
-        k_poa_sets<<<(unsigned)workers, 32, 0, c->stream>>>(L);
-        CU(cudaGetLastError());
+        if (wA > 0) {                                          // side stream: both launches are resident together
+            CU(cudaStreamWaitEvent(c->poa_side, c->poa_ev[0], 0));
+            PoaLaunch LA = L;
+            LA.n_classes = (int)clsA.size(); LA.classes = d_classes; LA.cursors = d_cursors;
+            k_poa_sets<8><<<(unsigned)wA, 256, 0, c->poa_side>>>(LA);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(c->poa_ev[2], c->poa_side));
+            c->launches += 1;
+        }
+        if (wB > 0) {
+            PoaLaunch LB = L;
+            LB.n_classes = (int)clsB.size(); LB.classes = d_classes + clsA.size(); LB.cursors = d_cursors + clsA.size();
+            k_poa_sets<1><<<(unsigned)wB, 32, 0, c->stream>>>(LB);
+            CU(cudaGetLastError());
+            c->launches += 1;
+        }
+        if (wA > 0) CU(cudaStreamWaitEvent(c->stream, c->poa_ev[2], 0));
         CU(cudaEventRecord(c->poa_ev[1], c->stream));
         CU(cudaMemcpyAsync(h_status.data(), d_status, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));                  // also: todo / cls were read by the copies above
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
         kernel_ms += ms;
-        c->launches += 1;
-        max_workers = std::max<uint64_t>(max_workers, (uint64_t)workers);
+        if (getenv("SVTK_POA_DEBUG")) {
+            float msA = 0.f;
+            if (wA > 0) cudaEventElapsedTime(&msA, c->poa_ev[0], c->poa_ev[2]);
+            fprintf(stderr, "[poa] attempt %d: wide %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
+                    attempt, (long long)nA, wA, memA / 1e6, msA, todo.size() - nA, wB, memB / 1e6, ms);
+        }
+        max_workers = std::max<uint64_t>(max_workers, (uint64_t)(wA + wB));
         std::vector<int> again;
         for (int s : todo) {
             const int st = h_status[s];

@@ -10,11 +10,13 @@
 //                              max_remain reverse BFS :268-309
 //     consensus                abpoa_output.c:477-547   heaviest bundling, walk from SRC :375-391
 //
-// Execution model: ONE WARP OWNS ONE READ SET (a CTA of 32 threads per SV record).  The row DP is column
-// parallel across the 32 lanes -- 32 cells of the five-state convex recurrence per step, the two in-row gap
-// states (F1/F2) by a 5-step shuffle prefix-max, row arg-max by warp reductions -- and the pointer-chasing
-// phases (backtrack, graph fusion, the two BFS passes, bundling) run on lane 0 while many other warps of the
-// SM are in their DP phase.  abPOA's SIMD vectors are a storage detail of the CPU code: this file implements
+// Execution model: one CTA owns one read set -- a single warp (NW = 1, the throughput shape: up to 16 sets per SM
+// in flight) or, for the few heaviest sets of a batch, 8 warps (NW = 8, poa_align_dp_cta).  The row DP is column
+// parallel across the threads -- one cell of the five-state convex recurrence per thread and step, the two
+// in-row gap states (F1/F2) by a shuffle prefix-max (plus a shared-memory exchange of warp totals at NW = 8), row
+// arg-max by warp reductions; edge sorting, max_remain (pointer jumping) and the DP's row descriptions are thread
+// parallel; the pointer-chasing phases (backtrack, graph fusion, the BFS index, bundling) run on thread 0 while
+// the other warps of the SM are in their DP phase.  abPOA's SIMD vectors are a storage detail of the CPU code: this file implements
 // the vector-width-1 semantics (cells outside a row's band read as inf_min), which is what every real-valued
 // cell of abPOA computes; SURVEY 7.3-6 measured the four CPU vector widths to agree on the same inputs.
 //
@@ -47,8 +49,13 @@ PD int poa_min_all(int v) { return __reduce_min_sync(0xffffffffu, v); }
 #endif
 #if defined(POA_HOSTSIM)
 static inline long long poa_clock() { return 0; }
+template <int NW> static inline int poa_tid() { return 0; }
+template <int NW> static inline void poa_bar() {}
 #else
 PD long long poa_clock() { return clock64(); }
+// a read set is owned by NW warps (NW = 1: one warp, warp-level sync; NW > 1: the whole CTA, block barriers)
+template <int NW> PD int poa_tid() { return NW == 1 ? (int)(threadIdx.x & 31) : (int)threadIdx.x; }
+template <int NW> PD void poa_bar() { if (NW == 1) __syncwarp(); else __syncthreads(); }
 #endif
 
 namespace svtk_poa {
@@ -98,7 +105,7 @@ struct PoaState {
     unsigned char *cells;                                      // rows x band x {H, E1, E2, F1, F2}, int16 or int32
     int2 *cigar;
     int n_cigar;
-    int best_score, best_i, best_j;
+    int best_score, best_i, best_j, ret_len;
     long long cells_done, cells_full;                          // band cells / full-matrix-equivalent cells of this read set
     long long t_phase[4];                                      // SM cycles of this read set in: row DP, backtrack, graph fusion, topological sort
     int status;
@@ -196,50 +203,59 @@ PD void poa_sort_edges(int *id, int *w, int n) {
             if (w[j] < w[k]) { int t = id[j]; id[j] = id[k]; id[k] = t; t = w[j]; w[j] = w[k]; w[k] = t; }
 }
 
-PD void poa_bfs_remain(PoaState &s) {                          // abpoa_BFS_set_node_remain, abpoa_graph.c:268
-    int head = 0, tail = 0;
-    s.queue[tail++] = SINK;
-    s.remain[SINK] = -1;
-    while (head < tail) {
-        const int cur = s.queue[head++];
-        if (cur != SINK) {
-            int max_w = -1, max_id = -1;
-            for (int i = 0; i < s.out_n[cur]; ++i)
-                if (s.edge_w[s.out_off[cur] + i] > max_w) { max_w = s.edge_w[s.out_off[cur] + i]; max_id = s.edge_id[s.out_off[cur] + i]; }
-            if (max_id < 0) { s.status = POA_ERR_BFS; return; }
-            s.remain[cur] = s.remain[max_id] + 1;
-        }
-        if (cur == SRC) return;
-        for (int i = 0; i < s.in_n[cur]; ++i) {
-            const int in = s.edge_id[s.in_off[cur] + i];
-            if (--s.deg[in] == 0) s.queue[tail++] = in;
-        }
-    }
-    s.status = POA_ERR_BFS;
-}
-
 // abpoa_topological_sort (abpoa_graph.c:322): all lanes enter
+template <int NW>
 PD void poa_topological_sort(PoaState &sh) {
-    const int lane = poa_lane();
-    poa_sync();
+    const int lane = poa_tid<NW>();
+    poa_bar<NW>();
     PoaState s = sh;                                           // register copy: the shared struct would be re-read after every store
     const int n = s.node_n;
-    for (int i = lane; i < n; i += POA_NL) s.deg[i] = s.in_n[i];
-    poa_sync();
+    for (int i = lane; i < n; i += (NW * POA_NL)) s.deg[i] = s.in_n[i];
+    poa_bar<NW>();
     if (lane == 0) { poa_bfs_index(s); sh.status = s.status; }
-    poa_sync();
+    poa_bar<NW>();
     if (sh.status) return;
-    for (int i = lane; i < n; i += POA_NL) {                   // independent per node: lanes take nodes
+    constexpr int NT = NW * POA_NL;
+    // max_remain (abpoa_BFS_set_node_remain, abpoa_graph.c:268): remain[v] = remain[heaviest successor of v] + 1 with
+    // remain[SINK] = -1, the heaviest successor being the FIRST out-edge once the list is sorted by weight (the
+    // reference takes the first strict maximum).  The reference walks a reverse BFS; the values only depend on the
+    // successor chain, so they are computed here by pointer jumping (ceil(log2 n) rounds, all threads) instead of
+    // one thread chasing n pointers.  Buffers: (deg, remain) <-> (queue, max_left).
+    for (int i = lane; i < n; i += NT) {                       // independent per node: threads take nodes
         poa_sort_edges(s.edge_id + s.in_off[i], s.edge_w + s.in_off[i], s.in_n[i]);
         poa_sort_edges(s.edge_id + s.out_off[i], s.edge_w + s.out_off[i], s.out_n[i]);
-        s.max_right[i] = 0; s.max_left[i] = n;
-        s.deg[i] = s.out_n[i]; s.remain[i] = 0;
+        int nx = SINK, d = 0;
+        if (i != SINK) {
+            if (s.out_n[i] <= 0) sh.status = POA_ERR_BFS;      // every node reaches SINK in a well-formed graph
+            else { nx = s.edge_id[s.out_off[i]]; d = 1; }
+        }
+        s.deg[i] = nx; s.remain[i] = d;
     }
-    poa_sync();
-    if (lane == 0) { poa_bfs_remain(s); sh.status = s.status; }
-    poa_sync();
+    poa_bar<NW>();
     if (sh.status) return;
-    for (int i = lane; i < n; i += POA_NL) {                   // the DP's streaming view of the sorted graph
+    {
+        int *nxa = s.deg, *da = s.remain, *nxb = s.queue, *db = s.max_left;
+        for (int span = 1; span < n; span <<= 1) {
+            for (int i = lane; i < n; i += NT) {
+                const int nx = nxa[i];
+                db[i] = da[i] + da[nx];
+                nxb[i] = nxa[nx];
+            }
+            poa_bar<NW>();
+            int *t = nxa; nxa = nxb; nxb = t;
+            t = da; da = db; db = t;
+        }
+        if (da != s.remain) {
+            for (int i = lane; i < n; i += NT) s.remain[i] = da[i];
+            poa_bar<NW>();
+        }
+    }
+    for (int i = lane; i < n; i += NT) {
+        s.remain[i] -= 1;
+        s.max_right[i] = 0; s.max_left[i] = n;                 // abpoa_graph.c:344-347
+    }
+    poa_bar<NW>();
+    for (int i = lane; i < n; i += (NW * POA_NL)) {                   // the DP's streaming view of the sorted graph
         const int id = s.idx2id[i];
         const int pn = s.in_n[id], po = s.in_off[id];
         int4 m;
@@ -247,7 +263,7 @@ PD void poa_topological_sort(PoaState &sh) {
         s.rowmeta[i] = m;
         for (int k = 0; k < pn; ++k) s.edge_idx[po + k] = s.id2idx[s.edge_id[po + k]];
     }
-    poa_sync();
+    poa_bar<NW>();
 }
 
 // first read: abpoa_add_graph_sequence (abpoa_graph.c:555).  lane 0
@@ -584,6 +600,195 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     return top;
 }
 
+// cross-warp exchange of one CTA-wide row (shared memory): lane 31's Hme and scan totals, per-warp row maxima
+struct PoaXchg {
+    int h[8], g1[8], g2[8];
+    int bv[8], bl[8], br[8];
+};
+
+#ifndef POA_HOSTSIM
+// CTA-wide row DP for the large read sets: NW warps share a row, thread t owns column cb + t.  Same recurrences as
+// poa_align_dp; F1/F2 are written as one prefix max over the whole row of g(k) = Hme[k-1] - oe + k*e
+// (F[j] = max_{k<=j} g(k) - j*e, identical in exact integer arithmetic to F[j] = max(Hme[j-1] - oe, F[j-1] - e)):
+// warp shuffle scan, lane-31 totals through shared memory, running maximum carried across 32*NW-column blocks.
+template <typename SC, int NW>
+__device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, const uint8_t *q, int qlen, int inf_min) {
+    constexpr int NT = 32 * NW;
+    constexpr int IMIN = -2147483647 - 1;
+    const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+    const PoaState g = s;
+    const int n = g.node_n;
+    const int w = EXTRA_B + (int)(EXTRA_F * (float)qlen);
+    SC *cells = reinterpret_cast<SC *>(g.cells);
+    const long long cell_cap = g.cell_bytes / (long long)(5 * sizeof(SC));
+    long long top = 0;
+
+    if (t == 0) {
+        g.max_left[SRC] = g.max_right[SRC] = 0;
+        for (int i = 0; i < g.out_n[SRC]; ++i) { const int o = g.edge_id[g.out_off[SRC] + i]; g.max_left[o] = g.max_right[o] = 1; }
+    }
+    __syncthreads();
+    const int end0 = imin(qlen, imax(g.max_right[SRC], qlen - g.remain[SRC]) + w);
+    {
+        const int w0 = end0 + 1;
+        if (w0 > cell_cap) { if (t == 0) s.status = POA_ERR_CELLS; __syncthreads(); return 0; }
+        if (t == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; }
+        for (int j = t; j <= end0; j += NT) {
+            int h, e1 = inf_min, e2 = inf_min, f1, f2;
+            if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
+            else { f1 = -GAP_O1 - GAP_E1 * j; f2 = -GAP_O2 - GAP_E2 * j; h = imax(f1, f2); }
+            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; cells[3 * w0 + j] = (SC)f1; cells[4 * w0 + j] = (SC)f2;
+        }
+        top = w0;
+    }
+    __syncthreads();
+
+    int lb = 0, le = end0;
+    long long lo = 0;
+    int4 meta = g.rowmeta[1], meta_n = g.rowmeta[imin(2, n - 1)];
+    int pi[PRED_REG];
+#pragma unroll
+    for (int k = 0; k < PRED_REG; ++k) pi[k] = k < (meta.y >> 8) ? g.edge_idx[meta.z + k] : -1;
+    for (int i = 1; i < n - 1; ++i) {
+        const int id = meta.x, nb = meta.y & 0xff, pn = meta.y >> 8, po = meta.z;
+        const int rt = qlen - meta.w;
+        const int4 meta_nn = g.rowmeta[imin(i + 2, n - 1)];
+        int pi_n[PRED_REG];
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) pi_n[k] = k < (meta_n.y >> 8) ? g.edge_idx[meta_n.z + k] : -1;
+        const int ml = g.max_left[id], mr = g.max_right[id];
+        int pbv[PRED_REG], pev[PRED_REG];
+        const SC *prv[PRED_REG];
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) {
+            pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
+            const int p = pi[k];
+            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
+            else if (p >= 0) { pbv[k] = g.dp_beg[p]; pev[k] = g.dp_end[p]; prv[k] = cells + g.row_off[p] * 5; }
+        }
+        int beg = imax(0, imin(ml, rt) - w);
+        const int end = imin(qlen, imax(mr, rt) + w);
+        int min_pre_beg = 0x7fffffff;
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) min_pre_beg = imin(min_pre_beg, pbv[k]);
+        for (int k = PRED_REG; k < pn; ++k) min_pre_beg = imin(min_pre_beg, g.dp_beg[g.edge_idx[po + k]]);
+        if (beg < min_pre_beg) beg = min_pre_beg;
+        const int wd = end - beg + 1;
+        if (wd <= 0 || pn <= 0) { if (t == 0) s.status = POA_ERR_BAND; __syncthreads(); return top; }
+        if (top + wd > cell_cap) { if (t == 0) s.status = POA_ERR_CELLS; __syncthreads(); return top; }
+        SC *row = cells + top * 5;
+        if (t == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; }
+
+        int carry_h = inf_min;                                 // Hme of the column left of the block
+        int run1 = IMIN, run2 = IMIN;                          // max of g1 / g2 over all columns left of the block
+        int bv = IMIN, bl = -1, br = -1;
+        for (int cb = beg; cb <= end; cb += NT) {
+            const int j = cb + t;
+            const bool valid = j <= end;
+            int m = inf_min, e1in = inf_min, e2in = inf_min, sc = 0;
+            if (valid) {
+#pragma unroll
+                for (int k = 0; k < PRED_REG; ++k) {
+                    const int pb = pbv[k], pe = pev[k], pw = pe - pb + 1;
+                    const SC *pr = prv[k];
+                    if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
+                    if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+                }
+                for (int k = PRED_REG; k < pn; ++k) {
+                    const int p = g.edge_idx[po + k];
+                    const int pb = g.dp_beg[p], pe = g.dp_end[p], pw = pe - pb + 1;
+                    const SC *pr = cells + g.row_off[p] * 5;
+                    if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
+                    if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
+                }
+                if (j > 0) sc = poa_score(nb, q[j - 1]);
+            }
+            const int hme = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
+            int left = __shfl_up_sync(0xffffffffu, hme, 1);
+            if (lane == 31) x.h[wp] = hme;
+            __syncthreads();                                   // (A) lane-31 Hme of every warp visible
+            if (lane == 0) left = wp == 0 ? carry_h : x.h[wp - 1];
+            carry_h = x.h[NW - 1];
+            int g1 = left - GAP_OE1 + j * GAP_E1, g2 = left - GAP_OE2 + j * GAP_E2;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t1 = __shfl_up_sync(0xffffffffu, g1, d), t2 = __shfl_up_sync(0xffffffffu, g2, d);
+                if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
+            }
+            if (lane == 31) { x.g1[wp] = g1; x.g2[wp] = g2; }
+            __syncthreads();                                   // (B) warp totals visible
+            int pre1 = run1, pre2 = run2;
+#pragma unroll
+            for (int v = 0; v < NW; ++v) {
+                const int a1 = x.g1[v], a2 = x.g2[v];
+                if (v < wp) { pre1 = imax(pre1, a1); pre2 = imax(pre2, a2); }
+                run1 = imax(run1, a1); run2 = imax(run2, a2);
+            }
+            const int f1 = imax(g1, pre1) - j * GAP_E1;
+            const int f2 = imax(g2, pre2) - j * GAP_E2;
+            const int h = imax(hme, imax(f1, f2));
+            if (valid) {
+                const int xo = j - beg;
+                row[xo] = (SC)h;
+                row[wd + xo] = (SC)imax(e1in - GAP_E1, h - GAP_OE1);
+                row[2 * wd + xo] = (SC)imax(e2in - GAP_E2, h - GAP_OE2);
+                row[3 * wd + xo] = (SC)f1;
+                row[4 * wd + xo] = (SC)f2;
+                if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
+            }
+        }
+        // row arg-max across the CTA
+        {
+            const int wv = __reduce_max_sync(0xffffffffu, bv);
+            const int wl = __reduce_min_sync(0xffffffffu, bv == wv ? bl : 0x7fffffff);
+            const int wr = __reduce_max_sync(0xffffffffu, bv == wv ? br : -1);
+            if (lane == 0) { x.bv[wp] = wv; x.bl[wp] = wl; x.br[wp] = wr; }
+        }
+        __syncthreads();                                       // (C)
+        int vmax = IMIN;
+#pragma unroll
+        for (int v = 0; v < NW; ++v) vmax = imax(vmax, x.bv[v]);
+        int left_i = 0x7fffffff, right_i = -1;
+#pragma unroll
+        for (int v = 0; v < NW; ++v) if (x.bv[v] == vmax) { left_i = imin(left_i, x.bl[v]); right_i = imax(right_i, x.br[v]); }
+        if (vmax < inf_min) { left_i = -1; right_i = -1; }
+        else if (vmax == inf_min || left_i == 0x7fffffff) left_i = -1;
+        for (int k = t; k < g.out_n[id]; k += NT) {
+            const int o = g.edge_id[g.out_off[id] + k];
+            if (right_i + 1 > g.max_right[o]) g.max_right[o] = right_i + 1;
+            if (left_i + 1 < g.max_left[o]) g.max_left[o] = left_i + 1;
+        }
+        lb = beg; le = end; lo = top;
+        top += wd;
+        meta = meta_n; meta_n = meta_nn;
+#pragma unroll
+        for (int k = 0; k < PRED_REG; ++k) pi[k] = pi_n[k];
+        __syncthreads();                                       // (D) row visible to the next one; exchange slots free
+    }
+    if (t == 0) {
+        int best = inf_min, bi = 0, bj = 0;
+        for (int k = 0; k < g.in_n[SINK]; ++k) {
+            const int p = g.id2idx[g.edge_id[g.in_off[SINK] + k]];
+            const int e = qlen > g.dp_end[p] ? g.dp_end[p] : qlen;
+            const int v = poa_cell<SC>(g, p, 0, e, inf_min);
+            if (v > best) { best = v; bi = p; bj = e; }
+        }
+        s.best_score = best; s.best_i = bi; s.best_j = bj;
+    }
+    __syncthreads();
+    return top;
+}
+#endif
+
+template <typename SC, int NW>
+PD long long poa_align_any(PoaState &s, PoaXchg &x, const uint8_t *q, int qlen, int inf_min) {
+#ifndef POA_HOSTSIM
+    if (NW > 1) return poa_align_dp_cta<SC, NW>(s, x, q, qlen, inf_min);
+#endif
+    (void)x;
+    return poa_align_dp<SC>(s, q, qlen, inf_min);
+}
+
 PD uint64_t poa_fnv(uint64_t h, int32_t v) {
     for (int k = 0; k < 4; ++k) { h ^= (uint64_t)(((uint32_t)v >> (8 * k)) & 0xffu); h *= 1099511628211ull; }
     return h;
@@ -648,19 +853,20 @@ PD int poa_consensus(PoaState &s, uint8_t *cons, int32_t *cov, int cap) {
 
 // The whole read set: reads r0 .. r1 of the batch (bases[seq_off[r] .. seq_off[r+1])).  All lanes.  Returns the
 // consensus length (uniform), 0 on error (s.status says why).
-PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq_off, const uint8_t *bases, uint8_t *cons,
+template <int NW, typename XCH>
+PD int poa_run_set(PoaState &s, XCH &xch, long long r0, long long r1, const long long *seq_off, const uint8_t *bases, uint8_t *cons,
                    int32_t *cov, int cons_cap, const PoaTrace *tr) {
-    const int lane = poa_lane();
+    const int lane = poa_tid<NW>();
     if (lane == 0) {                                           // abpoa_reset (abpoa_graph.c:782): graph = {SRC, SINK}
         s.node_n = 0; s.edge_top = 0; s.status = POA_OK; s.n_cigar = 0; s.cells_done = 0; s.cells_full = 0;
         s.t_phase[0] = s.t_phase[1] = s.t_phase[2] = s.t_phase[3] = 0;
         poa_add_node(s, 0); poa_add_node(s, 0);
     }
-    poa_sync();
+    poa_bar<NW>();
     for (long long r = r0; r < r1 && !s.status; ++r) {
         const uint8_t *q = bases + seq_off[r];
         const int qlen = (int)(seq_off[r + 1] - seq_off[r]);
-        if (qlen <= 0) { if (lane == 0) s.status = POA_ERR_INPUT; poa_sync(); break; }
+        if (qlen <= 0) { if (lane == 0) s.status = POA_ERR_INPUT; poa_bar<NW>(); break; }
         long long cells = 0;
         const int rows = s.node_n;
         if (rows <= 2) {                                       // abpoa_align_sequence_to_graph returns -1 (abpoa_align.c:201)
@@ -676,8 +882,8 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
             const int max_score = imax(qlen * MATCH, len * GAP_E1 + GAP_O1);
             const bool use16 = max_score <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2;
             const long long t0 = poa_clock();
-            if (use16) cells = poa_align_dp<int16_t>(s, q, qlen, INF_MIN16);
-            else cells = poa_align_dp<int32_t>(s, q, qlen, INF_MIN32);
+            if (use16) cells = poa_align_any<int16_t, NW>(s, xch, q, qlen, INF_MIN16);
+            else cells = poa_align_any<int32_t, NW>(s, xch, q, qlen, INF_MIN32);
             if (lane == 0 && !s.status) {
                 const long long t1 = poa_clock();
                 PoaState g = s;
@@ -688,7 +894,7 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
                 s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
             }
         }
-        poa_sync();
+        poa_bar<NW>();
         if (lane == 0 && !s.status) {
             if (tr && tr->ops_hash) {                          // forward (query) order, as the reference's reversed cigar
                 uint64_t h = 1469598103934665603ull;
@@ -714,13 +920,13 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
             s.t_phase[2] += poa_clock() - t2;
             if (tr && tr->best_score) { tr->best_score[r] = rows > 2 ? s.best_score : 0; tr->cells[r] = cells; }
         }
-        poa_sync();
+        poa_bar<NW>();
         if (s.status) break;
         const long long t3 = poa_clock();
-        poa_topological_sort(s);
+        poa_topological_sort<NW>(s);
         if (lane == 0) s.t_phase[3] += poa_clock() - t3;
         if (lane == 0 && tr && tr->node_n) tr->node_n[r] = s.node_n;
-        poa_sync();
+        poa_bar<NW>();
     }
     int len = 0;
     if (lane == 0 && !s.status && s.node_n > 2) {
@@ -728,8 +934,10 @@ PD int poa_run_set(PoaState &s, long long r0, long long r1, const long long *seq
         len = poa_consensus(g, cons, cov, cons_cap);
         s.status = g.status;
     }
-    poa_sync();
-    len = poa_shfl(len, 0);
+    if (lane == 0) s.ret_len = len;
+    poa_bar<NW>();
+    len = s.ret_len;
+    poa_bar<NW>();
     return s.status ? 0 : len;
 }
 

@@ -44,7 +44,8 @@ extern "C" int hostsim_poa(int n, const long long *off, const uint8_t *bases, ui
     PoaTrace tr;
     tr.best_score = best_score; tr.node_n = node_n; tr.n_ops = n_ops; tr.ops_hash = ops_hash; tr.cells = cells;
     tr.dump_read = dump_read; tr.dump = dump; tr.dump_cap = dump_cap;
-    int len = poa_run_set(s, 0, n, off, bases, cons, cov, cons_cap, best_score ? &tr : nullptr);
+    PoaXchg xch;
+    int len = poa_run_set<1>(s, xch, 0, n, off, bases, cons, cov, cons_cap, best_score ? &tr : nullptr);
     *status = s.status;
     if (cells_total) *cells_total = s.cells_done;
     return len;

@@ -1,0 +1,92 @@
+"""Region sharding of one audt job across GPUs (BASELINE north star: "VCF records are sharded by genomic region across
+the 8 GPUs ... no NCCL collective is needed and per-GPU results are merged in order on the host").
+
+The reference's unit of fan-out is one VCF line per pool thread (audit.c:289-338, tpool.c); here it is one contiguous
+run of VCF records per GPU.  A shard is closed under its reads: it takes every read an iterator of one of its windows
+could yield -- pos < max(end) - 1 and endpos > min(start) - 1 (hts.c:3913-3916), found with the same look-back bound the
+device search uses (the longest reference span of any read) -- so a rank needs nothing from its neighbours and the only
+exchange is the gather of 4-byte results in shard order == VCF order.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .simreads import ReadSet
+
+
+def plan_shards(windows: dict, n_shards: int):
+    """Cut the window list (VCF order) into n_shards contiguous pieces of roughly equal work, never splitting a record's
+    windows (a DEL owns two).  Work estimate = window width (reads seen ~ width x depth).  Returns
+    [(win_lo, win_hi)] of length n_shards (possibly empty ranges)."""
+    n = int(len(windows["chrom"]))
+    if n == 0:
+        return [(0, 0)] * n_shards
+    width = (windows["end"].astype(np.int64) - windows["start"].astype(np.int64)) & 0xFFFFFFFF
+    width = np.where(width > (1 << 31), 0, width) + 1          # a uint32-wrapped window sees no reads
+    cum = np.cumsum(width)
+    rec = np.asarray(windows["record"])
+    cuts = [0]
+    for s in range(1, n_shards):
+        i = int(np.searchsorted(cum, cum[-1] * s / n_shards))
+        i = min(max(i, cuts[-1]), n)
+        while 0 < i < n and rec[i] == rec[i - 1]:               # keep a record's windows together
+            i += 1
+        cuts.append(i)
+    cuts.append(n)
+    return [(cuts[i], cuts[i + 1]) for i in range(n_shards)]
+
+
+def shard_reads(rs: ReadSet, windows: dict, lo: int, hi: int) -> ReadSet:
+    """The sub read set windows[lo:hi] can see (all contigs kept, so chrom numbers stay valid)."""
+    span = int((rs.end.astype(np.int64) - rs.pos.astype(np.int64)).max(initial=1))
+    n_tid = rs.n_tid
+    keep_lo = np.zeros(n_tid, np.int64); keep_hi = np.zeros(n_tid, np.int64)
+    for t in range(n_tid):
+        keep_lo[t] = keep_hi[t] = rs.tid_off[t]
+    chrom = np.asarray(windows["chrom"][lo:hi]).astype(np.int64)
+    ws = np.asarray(windows["start"][lo:hi]).astype(np.int64)
+    we = np.asarray(windows["end"][lo:hi]).astype(np.int64)
+    for t in np.unique(chrom - 1):
+        if t < 0 or t >= n_tid:
+            continue
+        m = chrom - 1 == t
+        beg = ws[m] - 1; end = we[m] - 1                        # sam_itr_queryi(idx, tid, start - 1, end - 1), refinement.c:114
+        ok = (end >= beg) & (beg >= 0)
+        if not ok.any():
+            continue
+        t0, t1 = int(rs.tid_off[t]), int(rs.tid_off[t + 1])
+        p = rs.pos[t0:t1].astype(np.int64)
+        keep_lo[t] = t0 + int(np.searchsorted(p, beg[ok].min() - span + 1, side="left"))
+        keep_hi[t] = t0 + int(np.searchsorted(p, end[ok].max(), side="left"))
+        keep_hi[t] = max(keep_hi[t], keep_lo[t])
+    idx = np.concatenate([np.arange(keep_lo[t], keep_hi[t]) for t in range(n_tid)]) if n_tid else np.zeros(0, np.int64)
+    tid_off = np.zeros(n_tid + 1, np.int64)
+    tid_off[1:] = np.cumsum(keep_hi - keep_lo)
+    ncig = rs.n_cigar[idx].astype(np.uint32)
+    coff = np.zeros(len(idx) + 1, np.uint64)
+    coff[1:] = np.cumsum(ncig.astype(np.uint64))
+    words = [rs.cigar[int(rs.cigar_off[keep_lo[t]]):int(rs.cigar_off[keep_hi[t]])] for t in range(n_tid) if keep_hi[t] > keep_lo[t]]
+    cigar = np.concatenate(words).astype(np.uint32) if words else np.zeros(0, np.uint32)
+    return ReadSet(tid_off, rs.pos[idx], rs.end[idx], ncig, coff, cigar, list(rs.contig_len))
+
+
+def audit_sharded(refine_fn, rs: ReadSet, windows: dict, rank: int, world: int, group=None):
+    """Run this rank's shard through refine_fn(sub_reads, chrom, start, end, pos, kind) -> int32 results and return the
+    whole job's results in VCF order on every rank.  With world > 1 the only communication is the gather of results
+    (torch.distributed, backend nccl on GPUs / gloo in the CPU tests): no data-path collective."""
+    shards = plan_shards(windows, world)
+    lo, hi = shards[rank]
+    sub = shard_reads(rs, windows, lo, hi)
+    mine = np.asarray(refine_fn(sub, *[windows[k][lo:hi] for k in ("chrom", "start", "end", "pos", "kind")]), dtype=np.int32)
+    if world == 1:
+        return mine
+    import torch
+    import torch.distributed as dist
+    sizes = [h - l for l, h in shards]
+    cap = max(max(sizes), 1)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    buf = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+    buf[:len(mine)] = torch.from_numpy(mine).to(dev)
+    out = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(out, buf, group=group)
+    return np.concatenate([o[:n].cpu().numpy() for o, n in zip(out, sizes)])

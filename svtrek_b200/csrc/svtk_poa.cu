@@ -78,8 +78,11 @@ struct PoaLaunch {
 
 // NW = 1: one warp per read set (the throughput shape).  NW = 8: the whole 256-thread CTA shares each DP row and the
 // parallel parts of the sort -- used for the few heaviest sets, whose single-warp latency would be the batch's tail.
+#ifndef SVTK_POA_MINB
+#define SVTK_POA_MINB 16
+#endif
 template <int NW>
-__global__ void __launch_bounds__(32 * NW) k_poa_sets(PoaLaunch L) {
+__global__ void __launch_bounds__(32 * NW, NW == 1 ? SVTK_POA_MINB : 1) k_poa_sets(PoaLaunch L) {
     __shared__ PoaState s;
     __shared__ PoaXchg xch;
     __shared__ int s_item, s_cls;

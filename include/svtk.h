@@ -143,6 +143,30 @@ int svtk_load_reads(svtk_ctx *ctx, const svtk_reads *host_reads);
  * HOST pointer).  The ctx does not take ownership.  Used when the packer itself runs on the GPU. */
 int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *dev_reads);
 
+/* ---- BAM in: the whole coordinate-sorted, BAI-indexed BAM -> resident read set, decoded on the GPU.
+ * Replaces hts_open + sam_index_load (audit.c:270-272) and everything sam_itr_queryi / sam_itr_next do per window
+ * (refinement.c:109-117; bgzf.c:988 bgzf_read_block -> bgzf.c:746 inflate; sam.c:754-795 bam_read1 incl. the CG-tag CIGAR
+ * fix-up sam.c:645; sam.c:638 bam_endpos): the file is copied to HBM compressed, every BGZF block is inflated there, the
+ * record chain is cut at the record-aligned offsets the .bai holds, and pos / endpos / CIGAR are extracted into the same
+ * arrays svtk_load_reads fills.  Every record with refID >= 0 becomes a read (no FLAG / MAPQ filter, like the reference).
+ * bai_path NULL: "<bam_path>.bai", else "<bam_path minus .bam>.bai".  Errors (SVTK_ERR_IO): unreadable / corrupt file,
+ * stale index, records out of coordinate order.  BGZF CRC32 footers are not verified. */
+typedef struct {
+    uint64_t file_bytes, n_blocks, inflated_bytes;
+    uint64_t n_reads, n_words;
+    int32_t n_ref;
+    uint32_t n_pieces;               /* pieces the record chain was cut into */
+    float host_scan_ms;              /* mmap + BGZF block table + header + .bai */
+    float upload_ms, inflate_ms, parse_ms, total_ms;
+} svtk_bam_stats;
+int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats);
+/* the BAM header's reference dictionary (bam_hdr_t target_name / target_len) after svtk_load_bam */
+int svtk_bam_n_ref(const svtk_ctx *ctx);
+int svtk_bam_ref(const svtk_ctx *ctx, int tid, const char **name, uint32_t *len);
+/* the resident read set copied back to host arrays (any array may be NULL; call once for the sizes).  Parity aid. */
+int svtk_copy_reads(svtk_ctx *ctx, int64_t *n_tid, int64_t *n_reads, int64_t *n_words, int64_t *tid_off, uint32_t *pos, uint32_t *end,
+                    uint32_t *n_cigar, uint64_t *cigar_off, uint32_t *cigar);
+
 /* ---- batch seam: N refine_* calls in one go.  result[i] == the reference's return value (-1 == NA). */
 /* host buffers in, host buffer out; H2D + kernels + D2H, synchronous */
 int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *host_windows, int32_t *host_result);

@@ -67,10 +67,17 @@ class PoaStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("n_sets", "n_reads", "n_bases", "cells", "cells_full", "relaunched", "workers")] + [("kernel_ms", C.c_double), ("phase_cycles", C.c_uint64 * 4)]
 
 
+class BamStats(C.Structure):
+    _fields_ = [("file_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("inflated_bytes", C.c_uint64), ("n_reads", C.c_uint64), ("n_words", C.c_uint64),
+                ("n_ref", C.c_int32), ("n_pieces", C.c_uint32), ("host_scan_ms", C.c_float), ("upload_ms", C.c_float), ("inflate_ms", C.c_float),
+                ("parse_ms", C.c_float), ("total_ms", C.c_float)]
+
+
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
-           "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus"]
+           "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads"]
 
 _lib = None
 
@@ -110,6 +117,10 @@ def load_library():
     L.svtk_process_vcf.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
     L.svtk_poa_consensus.argtypes = [C.c_void_p, C.POINTER(PoaBatch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.POINTER(PoaTrace), C.POINTER(PoaStats)]
+    L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
+    L.svtk_bam_n_ref.argtypes = [C.c_void_p]
+    L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
+    L.svtk_copy_reads.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)] + [C.c_void_p] * 6
     _lib = L
     return L
 
@@ -227,6 +238,31 @@ class Auditor:
         t = Timing()
         _check(self.lib.svtk_get_timing(self.ctx, C.byref(t)))
         return {k: getattr(t, k) for k, _ in Timing._fields_}
+
+    # ---- BAM in (svtk_load_bam): what hts_open + sam_index_load + the per-window iterators give the reference
+    def load_bam(self, bam_path, bai_path=None):
+        """BGZF inflate + BAM record extraction on the GPU; returns the loader's counters / timings."""
+        st = BamStats()
+        _check(self.lib.svtk_load_bam(self.ctx, os.fsencode(bam_path), os.fsencode(bai_path) if bai_path else None, C.byref(st)))
+        return {k: getattr(st, k) for k, _ in BamStats._fields_}
+
+    def bam_refs(self):
+        """[(name, length)] of the BAM header's reference dictionary."""
+        out = []
+        for t in range(self.lib.svtk_bam_n_ref(self.ctx)):
+            nm, ln = C.c_char_p(), C.c_uint32()
+            _check(self.lib.svtk_bam_ref(self.ctx, t, C.byref(nm), C.byref(ln)))
+            out.append((nm.value.decode(), int(ln.value)))
+        return out
+
+    def copy_reads(self):
+        """The resident read set as host arrays (dict with the svtk_reads field names)."""
+        nt, nr, nw = C.c_int64(), C.c_int64(), C.c_int64()
+        _check(self.lib.svtk_copy_reads(self.ctx, C.byref(nt), C.byref(nr), C.byref(nw), None, None, None, None, None, None))
+        a = dict(tid_off=np.zeros(nt.value + 1, np.int64), pos=np.zeros(nr.value, np.uint32), end=np.zeros(nr.value, np.uint32),
+                 n_cigar=np.zeros(nr.value, np.uint32), cigar_off=np.zeros(nr.value, np.uint64), cigar=np.zeros(nw.value, np.uint32))
+        _check(self.lib.svtk_copy_reads(self.ctx, None, None, None, *[a[k].ctypes.data for k in ("tid_off", "pos", "end", "n_cigar", "cigar_off", "cigar")]))
+        return a
 
     def load_reads_ptr(self, n_tid, n_reads, n_words, tid_off_ptr, pos_ptr, end_ptr, n_cigar_ptr, cigar_off_ptr, cigar_ptr):
         """svtk_load_reads on raw HOST pointers (e.g. pinned torch tensors): no numpy conversion on the timed path."""

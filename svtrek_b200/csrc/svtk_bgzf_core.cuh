@@ -1,0 +1,256 @@
+// svtk_bgzf_core.cuh -- RFC 1951 (DEFLATE) decoder for one BGZF block, written so that ONE GPU LANE decodes ONE block
+// (32 independent blocks per warp) and so that the same source compiles as plain C++ for the CPU unit tests
+// (tests/hostsim/bgzf_hostsim.cpp).
+//
+// Where it sits: the reference reaches every read through HTSlib, which inflates each 64 KiB BGZF block with zlib on the
+// host every time an iterator touches it (bgzf.c:746 bgzf_uncompress -> inflate, called from bgzf_read_block bgzf.c:988);
+// >= 99 % of `svtrek audt` wall time is spent there.  BGZF blocks are independent gzip members
+// (SAMv1 4.1), so svtk_load_bam (svtk_bam.cu) ships the raw file to HBM and inflates all blocks at once.
+//
+// Decoder shape (per lane, state in registers, tables in shared memory):
+//   - 64-bit LSB-first bit buffer refilled 32 bits at a time from the (word aligned) compressed buffer;
+//   - canonical Huffman codes: a primary lookup table (9 bits literal/length, 8 bits distance; entry = symbol << 4 | code
+//     length) filled per DEFLATE block, and for the rare longer codes the count/first-code walk over the code lengths;
+//   - length / distance bases computed arithmetically (no constant-memory tables: lanes index them divergently);
+//   - every output byte is bounds-checked against the block's ISIZE, every match distance against the bytes produced so far
+//     (a BGZF block has no preset dictionary), so corrupt input yields an error code, never a stray store.
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+
+#if defined(__CUDACC__)
+#define BZ_HD __host__ __device__ __forceinline__
+#else
+#define BZ_HD inline
+#endif
+
+namespace svtk {
+
+constexpr int BZ_LBITS = 9, BZ_DBITS = 8;
+enum { BZ_OK = 0, BZ_ERR_BTYPE = 1, BZ_ERR_STORED = 2, BZ_ERR_LENS = 3, BZ_ERR_CODE = 4, BZ_ERR_DIST = 5, BZ_ERR_OUT = 6,
+       BZ_ERR_IN = 7, BZ_ERR_SIZE = 8, BZ_ERR_HEADER = 9 };
+
+struct BzTables {                         // one per lane; all members 16-bit so that a lane's copy can start at any 4-byte boundary
+    uint16_t lit[1 << BZ_LBITS];          // primary literal/length table: sym << 4 | len, 0 = code longer than BZ_LBITS
+    uint16_t dist[1 << BZ_DBITS];
+    uint16_t lsym[288], dsym[32];         // symbols in canonical order (for the long-code walk)
+    uint16_t lcnt[16], dcnt[16];          // codes per length
+};
+constexpr int BZ_TABLE_WORDS = (int)((sizeof(BzTables) + 3) / 4) | 1;   // odd stride: 32 lanes' copies start in 32 different banks
+
+struct BzBits {
+    const uint32_t *w;                    // compressed buffer, 4-byte aligned, readable 8 bytes past the last block
+    unsigned long long ip, end;           // byte offsets: next unread byte, end of this block's DEFLATE payload
+    unsigned long long buf;
+    int cnt;
+};
+
+BZ_HD uint32_t bz_load32(const uint32_t *w, unsigned long long off) {
+    const unsigned long long i = off >> 2;
+    const uint32_t sh = (uint32_t)(off & 3) * 8u, lo = w[i], hi = w[i + 1];
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
+#endif
+}
+BZ_HD uint32_t bz_byte(const uint32_t *w, unsigned long long off) { return (w[off >> 2] >> ((uint32_t)(off & 3) * 8u)) & 255u; }
+
+BZ_HD void bz_refill(BzBits &b) {         // afterwards cnt >= 32
+    if (b.cnt < 32) { b.buf |= (unsigned long long)bz_load32(b.w, b.ip) << b.cnt; b.ip += 4; b.cnt += 32; }
+}
+BZ_HD uint32_t bz_take(BzBits &b, int n) {   // n <= 16, cnt >= n
+    const uint32_t v = (uint32_t)b.buf & ((1u << n) - 1u);
+    b.buf >>= n; b.cnt -= n;
+    return v;
+}
+
+BZ_HD uint32_t bz_rev(uint32_t code, int len) {
+#if defined(__CUDA_ARCH__)
+    return __brev(code) >> (32 - len);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < len; ++i) r |= ((code >> i) & 1u) << (len - 1 - i);
+    return r;
+#endif
+}
+
+// canonical code from lens[0..n): counts, symbols in code order, primary table of `bits` bits.  Over-subscribed -> error.
+BZ_HD int bz_build(const uint8_t *lens, int n, uint16_t *cnt, uint16_t *sym, uint16_t *tab, int bits) {
+    for (int l = 0; l < 16; ++l) cnt[l] = 0;
+    for (int s = 0; s < n; ++s) cnt[lens[s]]++;
+    int left = 1;
+    for (int l = 1; l < 16; ++l) { left = (left << 1) - (int)cnt[l]; if (left < 0) return BZ_ERR_LENS; }
+    uint16_t offs[16];
+    offs[0] = 0; offs[1] = 0;
+    for (int l = 1; l < 15; ++l) offs[l + 1] = (uint16_t)(offs[l] + cnt[l]);
+    for (int s = 0; s < n; ++s) if (lens[s]) sym[offs[lens[s]]++] = (uint16_t)s;
+    for (int i = 0; i < (1 << bits); ++i) tab[i] = 0;
+    uint32_t code = 0;
+    int idx = 0;
+    for (int l = 1; l <= bits; ++l) {
+        for (int k = 0; k < (int)cnt[l]; ++k, ++idx, ++code) {
+            const uint16_t e = (uint16_t)(sym[idx] << 4 | l);
+            for (uint32_t r = bz_rev(code, l); r < (1u << bits); r += 1u << l) tab[r] = e;
+        }
+        code <<= 1;
+    }
+    return BZ_OK;
+}
+
+// one symbol: primary table, else the bit-by-bit walk (codes longer than `bits`).  cnt >= 15 bits available.  -1 = invalid code
+BZ_HD int bz_symbol(BzBits &b, const uint16_t *tab, int bits, const uint16_t *cnt, const uint16_t *sym) {
+    const uint32_t e = tab[(uint32_t)b.buf & ((1u << bits) - 1u)];
+    if (e) { const int l = (int)(e & 15u); b.buf >>= l; b.cnt -= l; return (int)(e >> 4); }
+    int code = 0, first = 0, index = 0;
+    unsigned long long v = b.buf;
+    for (int l = 1; l < 16; ++l) {
+        code |= (int)(v & 1ull); v >>= 1;
+        const int c = (int)cnt[l];
+        if (code - c < first) { b.buf >>= l; b.cnt -= l; return (int)sym[index + (code - first)]; }
+        index += c; first += c; first <<= 1; code <<= 1;
+    }
+    return -1;
+}
+
+BZ_HD uint32_t bz_clen_order(int i) {    // RFC 1951 3.2.7: 16,17,18,0,8,7,9,6,10,5,11,4 | 12,3,13,2,14,1,15 (5 bits each)
+    const unsigned long long a = 16ull | 17ull << 5 | 18ull << 10 | 0ull << 15 | 8ull << 20 | 7ull << 25 | 9ull << 30 | 6ull << 35 |
+                                 10ull << 40 | 5ull << 45 | 11ull << 50 | 4ull << 55;
+    const unsigned long long c = 12ull | 3ull << 5 | 13ull << 10 | 2ull << 15 | 14ull << 20 | 1ull << 25 | 15ull << 30;
+    return (uint32_t)((i < 12 ? a >> (5 * i) : c >> (5 * (i - 12))) & 31ull);
+}
+
+// ---- resumable per-lane decoder.  On the GPU the 32 lanes of a warp run bz_header / bz_symbols from ONE warp-level loop
+// (svtk_bam.cu k_bgzf_inflate) so that lanes working on different blocks stay converged on the symbol step; a lane that
+// finished its block must not drift into a private copy of the loop.  On the host, bz_inflate below drives one lane.
+enum { BZ_S_IDLE = 0, BZ_S_HEADER = 1, BZ_S_SYMBOLS = 2 };
+
+struct BzLane {
+    BzBits b;
+    uint8_t *out;
+    uint32_t op, out_len;
+    int state, last, err;
+};
+
+BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len) {
+    z.b.w = words; z.b.ip = in_beg; z.b.end = in_end; z.b.buf = 0; z.b.cnt = 0;
+    z.out = out; z.op = 0; z.out_len = out_len; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
+}
+
+BZ_HD void bz_fail(BzLane &z, int e) { z.err = e; z.state = BZ_S_IDLE; }
+
+BZ_HD void bz_finish(BzLane &z) {        // after the final block
+    if (z.b.ip - (unsigned long long)(z.b.cnt >> 3) > z.b.end) z.err = BZ_ERR_IN;
+    else if (z.op != z.out_len) z.err = BZ_ERR_SIZE;
+    z.state = BZ_S_IDLE;
+}
+
+// one DEFLATE block header: stored blocks are copied here; for Huffman blocks the lane's tables are (re)built
+BZ_HD void bz_header(BzLane &z, BzTables &T) {
+    BzBits &b = z.b;
+    if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
+    bz_refill(b);
+    z.last = (int)bz_take(b, 1);
+    const uint32_t type = bz_take(b, 2);
+    if (type == 3) return bz_fail(z, BZ_ERR_BTYPE);
+    if (type == 0) {                                                       // stored: byte align, LEN, ~LEN, bytes
+        bz_take(b, b.cnt & 7);
+        b.ip -= (unsigned long long)(b.cnt >> 3); b.buf = 0; b.cnt = 0;    // hand the whole bytes back
+        if (b.ip + 4 > b.end) return bz_fail(z, BZ_ERR_STORED);
+        const uint32_t len = bz_byte(b.w, b.ip) | bz_byte(b.w, b.ip + 1) << 8;
+        const uint32_t nlen = bz_byte(b.w, b.ip + 2) | bz_byte(b.w, b.ip + 3) << 8;
+        b.ip += 4;
+        if ((len ^ nlen) != 0xffffu || b.ip + len > b.end) return bz_fail(z, BZ_ERR_STORED);
+        if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
+        for (uint32_t k = 0; k < len; ++k) z.out[z.op + k] = (uint8_t)bz_byte(b.w, b.ip + k);
+        z.op += len; b.ip += len;
+        if (z.last) bz_finish(z);
+        return;
+    }
+    uint8_t lens[320];
+    int hlit, hdist;
+    if (type == 1) {                                                       // fixed code, RFC 1951 3.2.6
+        hlit = 288; hdist = 30;
+        for (int s = 0; s < 144; ++s) lens[s] = 8;
+        for (int s = 144; s < 256; ++s) lens[s] = 9;
+        for (int s = 256; s < 280; ++s) lens[s] = 7;
+        for (int s = 280; s < 288; ++s) lens[s] = 8;
+        for (int s = 0; s < 30; ++s) lens[288 + s] = 5;
+    } else {
+        hlit = (int)bz_take(b, 5) + 257; hdist = (int)bz_take(b, 5) + 1;
+        const int hclen = (int)bz_take(b, 4) + 4;
+        if (hlit > 286 || hdist > 30) return bz_fail(z, BZ_ERR_HEADER);
+        for (int i = 0; i < 19; ++i) lens[i] = 0;
+        for (int i = 0; i < hclen; ++i) { bz_refill(b); lens[bz_clen_order(i)] = (uint8_t)bz_take(b, 3); }
+        // the code-length code borrows the distance table's storage (its 7-bit primary table covers every code)
+        if (bz_build(lens, 19, T.dcnt, T.dsym, T.dist, 7)) return bz_fail(z, BZ_ERR_LENS);
+        int n = 0, prev = 0;
+        while (n < hlit + hdist) {
+            bz_refill(b);
+            const int s = bz_symbol(b, T.dist, 7, T.dcnt, T.dsym);
+            if (s < 0) return bz_fail(z, BZ_ERR_CODE);
+            if (s < 16) { lens[n++] = (uint8_t)s; prev = s; continue; }
+            int rep, val = 0;
+            if (s == 16) { if (n == 0) return bz_fail(z, BZ_ERR_LENS); val = prev; rep = 3 + (int)bz_take(b, 2); }
+            else if (s == 17) { rep = 3 + (int)bz_take(b, 3); prev = 0; }
+            else { rep = 11 + (int)bz_take(b, 7); prev = 0; }
+            if (n + rep > hlit + hdist) return bz_fail(z, BZ_ERR_LENS);
+            while (rep--) lens[n++] = (uint8_t)val;
+        }
+        if (lens[256] == 0) return bz_fail(z, BZ_ERR_LENS);                // no end-of-block code
+        if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
+    }
+    if (bz_build(lens, hlit, T.lcnt, T.lsym, T.lit, BZ_LBITS)) return bz_fail(z, BZ_ERR_LENS);
+    if (bz_build(lens + hlit, hdist, T.dcnt, T.dsym, T.dist, BZ_DBITS)) return bz_fail(z, BZ_ERR_LENS);
+    z.state = BZ_S_SYMBOLS;
+}
+
+// one literal/length symbol (and its distance + copy).  Only called in state BZ_S_SYMBOLS.
+BZ_HD void bz_step(BzLane &z, const BzTables &T) {
+    BzBits &b = z.b;
+    bz_refill(b);
+    const int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym);
+    if (s < 256) {
+        if (s < 0) return bz_fail(z, BZ_ERR_CODE);
+        if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
+        z.out[z.op++] = (uint8_t)s;
+        return;
+    }
+    if (s == 256) {
+        if (z.last) bz_finish(z); else z.state = BZ_S_HEADER;
+        return;
+    }
+    if (s > 285) return bz_fail(z, BZ_ERR_CODE);
+    uint32_t len;
+    if (s < 265) len = (uint32_t)(s - 254);
+    else if (s == 285) len = 258;
+    else { const int k = s - 261, eb = k >> 2; len = 3u + ((4u + (uint32_t)(k & 3)) << eb) + bz_take(b, eb); }
+    bz_refill(b);
+    const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym);
+    if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
+    uint32_t dist;
+    if (d < 4) dist = (uint32_t)d + 1u;
+    else { const int eb = (d >> 1) - 1; dist = 1u + ((2u + (uint32_t)(d & 1)) << eb) + bz_take(b, eb); }
+    if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
+    if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
+    if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
+    uint8_t *o = z.out + z.op;
+    for (uint32_t k = 0; k < len; ++k) o[k] = o[(long long)k - (long long)dist];
+    z.op += len;
+}
+
+// Inflate one raw DEFLATE stream (the payload of one BGZF block): words/in_beg/in_end locate it inside the compressed
+// buffer, out/out_len is the block's slice of the inflated buffer (out_len == the block's ISIZE footer).  Returns BZ_OK
+// when the final block ended with exactly out_len bytes written.  (Single-lane driver; the kernel has its own.)
+BZ_HD int bz_inflate(const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len,
+                     BzTables &T) {
+    BzLane z;
+    bz_begin(z, words, in_beg, in_end, out, out_len);
+    while (z.state != BZ_S_IDLE) {
+        if (z.state == BZ_S_HEADER) bz_header(z, T);
+        else bz_step(z, T);
+    }
+    return z.err;
+}
+
+}  // namespace svtk

@@ -287,6 +287,31 @@ static int resolve_overflow(Ctx *c) {
     return 0;
 }
 
+static int check_reads(const svtk_reads *r) {
+    if (!r || r->n_tid < 0 || r->n_reads < 0 || r->n_words < 0) return fail(SVTK_ERR_ARG, "bad svtk_reads");
+    if (r->n_reads >= (1ll << 31) - 1024) return fail(SVTK_ERR_ARG, "more than 2^31 reads per device: shard the read set");
+    if (r->n_tid > 0 && !r->tid_off) return fail(SVTK_ERR_ARG, "tid_off is NULL");
+    if (r->n_reads > 0 && (!r->pos || !r->end || !r->n_cigar || !r->cigar_off)) return fail(SVTK_ERR_ARG, "read arrays are NULL");
+    if (r->n_words > 0 && !r->cigar) return fail(SVTK_ERR_ARG, "cigar is NULL");
+    return 0;
+}
+
+int adopt_device_reads(Ctx *c, const svtk_reads *d) {
+    if (int rc = check_reads(d)) return rc;
+    if (((uintptr_t)d->cigar & 15) != 0) return fail(SVTK_ERR_ARG, "device cigar array must be 16-byte aligned");
+    if (int rc = set_device(c)) return rc;
+    c->have_reads = false;
+    if (int rc = c->r_tid_off.reserve(sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
+    c->h_tid_off.assign(d->n_tid + 1, 0);
+    if (d->n_tid > 0) memcpy(c->h_tid_off.data(), d->tid_off, sizeof(int64_t) * (size_t)(d->n_tid + 1));
+    if (c->h_tid_off.back() != d->n_reads) return fail(SVTK_ERR_ARG, "tid_off[n_tid] != n_reads");
+    if (int rc = upload(c, c->r_tid_off.p, c->h_tid_off.data(), sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
+    c->reads = LaunchReads{d->n_tid, d->n_reads, (const long long *)c->r_tid_off.p, d->pos, d->end, d->n_cigar,
+                           (const unsigned long long *)d->cigar_off, d->cigar, 1};
+    c->n_words = d->n_words;
+    return finish_reads(c);
+}
+
 }  // namespace svtk
 
 using namespace svtk;
@@ -333,10 +358,13 @@ void svtk_destroy(svtk_ctx *ctx) {
     cudaStreamSynchronize(c->stream);
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items, &c->ov_count,
                       &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
-                      &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl})
+                      &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl, &c->bam_comp, &c->bam_infl, &c->bam_blocks,
+                      &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
     for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
+    for (int i = 0; i < 4; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
+    c->bam_h.release();
     if (c->poa_side) cudaStreamDestroy(c->poa_side);
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
@@ -352,15 +380,6 @@ int svtk_set_params(svtk_ctx *ctx, const svtk_params *p) {
 int svtk_get_params(const svtk_ctx *ctx, svtk_params *p) {
     if (!ctx || !p) return fail(SVTK_ERR_ARG, "null argument");
     *p = reinterpret_cast<const Ctx *>(ctx)->params;
-    return 0;
-}
-
-static int check_reads(const svtk_reads *r) {
-    if (!r || r->n_tid < 0 || r->n_reads < 0 || r->n_words < 0) return fail(SVTK_ERR_ARG, "bad svtk_reads");
-    if (r->n_reads >= (1ll << 31) - 1024) return fail(SVTK_ERR_ARG, "more than 2^31 reads per device: shard the read set");
-    if (r->n_tid > 0 && !r->tid_off) return fail(SVTK_ERR_ARG, "tid_off is NULL");
-    if (r->n_reads > 0 && (!r->pos || !r->end || !r->n_cigar || !r->cigar_off)) return fail(SVTK_ERR_ARG, "read arrays are NULL");
-    if (r->n_words > 0 && !r->cigar) return fail(SVTK_ERR_ARG, "cigar is NULL");
     return 0;
 }
 
@@ -397,19 +416,7 @@ int svtk_load_reads(svtk_ctx *ctx, const svtk_reads *h) {
 int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *d) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c) return fail(SVTK_ERR_ARG, "null ctx");
-    if (int rc = check_reads(d)) return rc;
-    if (((uintptr_t)d->cigar & 15) != 0) return fail(SVTK_ERR_ARG, "device cigar array must be 16-byte aligned");
-    if (int rc = set_device(c)) return rc;
-    c->have_reads = false;
-    if (int rc = c->r_tid_off.reserve(sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
-    c->h_tid_off.assign(d->n_tid + 1, 0);
-    if (d->n_tid > 0) memcpy(c->h_tid_off.data(), d->tid_off, sizeof(int64_t) * (size_t)(d->n_tid + 1));
-    if (c->h_tid_off.back() != d->n_reads) return fail(SVTK_ERR_ARG, "tid_off[n_tid] != n_reads");
-    if (int rc = upload(c, c->r_tid_off.p, c->h_tid_off.data(), sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
-    c->reads = LaunchReads{d->n_tid, d->n_reads, (const long long *)c->r_tid_off.p, d->pos, d->end, d->n_cigar,
-                           (const unsigned long long *)d->cigar_off, d->cigar, 1};
-    c->n_words = d->n_words;
-    return finish_reads(c);
+    return adopt_device_reads(c, d);
 }
 
 static LaunchWindows as_launch(const svtk_windows *w) {

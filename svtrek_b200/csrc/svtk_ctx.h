@@ -5,6 +5,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <string>
 #include <vector>
 
 namespace svtk {
@@ -74,6 +75,16 @@ struct Ctx {
     cudaEvent_t poa_ev[3] = {nullptr, nullptr, nullptr};
     cudaStream_t poa_side = nullptr;      // the CTA-wide launch of the heaviest read sets runs beside the warp-per-set launch
 
+    // svtk_load_bam (svtk_bam.cu): the raw file, its inflated image and the record table stay resident (INS-sequence extraction
+    // reads SEQ from them); reference names / lengths of the BAM header for the host front end
+    DevBuf bam_comp, bam_infl, bam_blocks, bam_splits, bam_seg, bam_rec, bam_ctl;
+    PinBuf bam_h;
+    cudaEvent_t bam_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::vector<std::string> bam_ref_names;
+    std::vector<uint32_t> bam_ref_lens;
+    unsigned long long bam_infl_bytes = 0;
+    long long bam_n_rec = 0;
+
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;
     cudaEvent_t prof_ev[4] = {nullptr, nullptr, nullptr, nullptr};     // [0,1] refine kernel, [2,3] index kernel
@@ -83,5 +94,6 @@ struct Ctx {
 
 int upload(Ctx *c, void *dst, const void *src, size_t bytes);   // host -> device on the ctx stream (pinned staging)
 int set_device(Ctx *c);
+int adopt_device_reads(Ctx *c, const svtk_reads *d);   // what svtk_attach_reads_device does, for loaders that fill c->r_* themselves
 
 }  // namespace svtk

@@ -1,0 +1,215 @@
+"""svtk_load_bam: BGZF inflate + BAM record extraction on the GPU.
+
+The reference reads BAM through HTSlib (hts_open / sam_index_load / sam_itr_queryi, audit.c:270-272, refinement.c:109-117),
+which inflates BGZF blocks with zlib (bgzf.c:746).  Inflate output is fully determined by the input, so the bar is bit-exact:
+
+  not gpu : the DEFLATE decoder source (svtk_bgzf_core.cuh) compiled as plain C++ equals zlib on stored / fixed / dynamic
+            blocks of several data kinds and rejects corrupt streams; the host-side BGZF / BAI parsers agree with the Python
+            restatement in tests/util_bam.py
+  gpu     : svtk_load_bam on BAM files written by the reference's own HTSlib (oracle/_ref) yields exactly the reads that were
+            written, and refinement results equal the oracle's on the same windows
+"""
+import ctypes as C
+import os
+import subprocess
+import tempfile
+import zlib
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def hostsim():
+    d = tempfile.mkdtemp(prefix="svtk_hostsim_")
+    so = os.path.join(d, "libbgzf_hostsim.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, os.path.join(ROOT, "tests", "hostsim", "bgzf_hostsim.cpp")])
+    L = C.CDLL(so)
+    L.hostsim_inflate.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_longlong, C.c_void_p, C.c_uint]
+    return L
+
+
+def raw_deflate(data, level, strategy=zlib.Z_DEFAULT_STRATEGY):
+    c = zlib.compressobj(level, zlib.DEFLATED, -15, 9, strategy)
+    return c.compress(data) + c.flush()
+
+
+def payloads(rng, n):
+    for t in range(n):
+        ln = int(rng.integers(0, 65280)) if t else 0
+        kind = t % 6
+        if kind == 0:
+            yield rng.integers(0, 256, ln, dtype=np.uint8).tobytes()
+        elif kind == 1:
+            yield bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), ln))
+        elif kind == 2:
+            yield (b"chr1\t12345\tACGTTTGA" * (ln // 19 + 1))[:ln]
+        elif kind == 3:
+            yield bytes(rng.integers(33, 74, ln, dtype=np.uint8))
+        elif kind == 4:
+            yield bytes(ln)
+        else:
+            a = rng.integers(0, 256, ln, dtype=np.uint8)
+            a[rng.random(ln) < 0.7] = 65
+            yield a.tobytes()
+
+
+def run_inflate(L, comp, out_len, pad=0):
+    buf = np.frombuffer(b"\xAA" * pad + bytes(comp) + b"\x55" * 5, np.uint8).copy()
+    out = np.zeros(max(out_len, 1), np.uint8)
+    rc = L.hostsim_inflate(buf.ctypes.data, len(buf), pad, pad + len(comp), out.ctypes.data, out_len)
+    return rc, out[:out_len].tobytes()
+
+
+def test_decoder_equals_zlib(hostsim):
+    rng = np.random.default_rng(20261104)
+    modes = ((6, zlib.Z_DEFAULT_STRATEGY), (1, zlib.Z_DEFAULT_STRATEGY), (9, zlib.Z_DEFAULT_STRATEGY), (0, zlib.Z_DEFAULT_STRATEGY),
+             (6, zlib.Z_FIXED), (6, zlib.Z_HUFFMAN_ONLY), (6, zlib.Z_RLE), (6, zlib.Z_FILTERED))
+    for t, data in enumerate(payloads(rng, 60)):
+        for level, strat in modes:
+            rc, out = run_inflate(hostsim, raw_deflate(data, level, strat), len(data), pad=t % 4)
+            assert rc == 0, (t, level, strat, rc)
+            assert out == data, (t, level, strat)
+
+
+def test_decoder_rejects_or_matches_zlib_on_corrupt_streams(hostsim):
+    rng = np.random.default_rng(7)
+    data = rng.integers(0, 64, 30000, dtype=np.uint8).tobytes()
+    comp = raw_deflate(data, 6)
+    rejected = 0
+    for _ in range(200):
+        c2 = bytearray(comp)
+        c2[int(rng.integers(0, len(c2)))] ^= 1 << int(rng.integers(0, 8))
+        rc, out = run_inflate(hostsim, c2, len(data))
+        try:
+            d = zlib.decompressobj(-15)
+            ref = d.decompress(bytes(c2))
+            ref_ok = d.eof and len(ref) == len(data)
+        except zlib.error:
+            ref, ref_ok = None, False
+        if rc == 0:
+            assert ref_ok and out == ref          # a flip zlib also accepts (raw DEFLATE carries no checksum): same bytes
+        else:
+            rejected += 1
+    assert rejected >= 1
+    # wrong ISIZE, truncated payload
+    assert run_inflate(hostsim, comp, len(data) - 1)[0] != 0
+    assert run_inflate(hostsim, comp, len(data) + 1)[0] != 0
+    assert run_inflate(hostsim, comp[:len(comp) // 2], len(data))[0] != 0
+
+
+# ---- golden BAM written by the reference's HTSlib (tools/make_bam_golden.py)
+GOLD_BAM = os.path.join(ROOT, "tests", "golden", "bam_small.bam")
+GOLD_NPZ = os.path.join(ROOT, "tests", "golden", "bam_small.npz")
+FIELDS = ("tid_off", "pos", "end", "n_cigar", "cigar_off", "cigar")
+
+
+def test_python_reader_matches_golden():
+    from tests import util_bam as U
+    z = np.load(GOLD_NPZ)
+    got = U.read_bam(GOLD_BAM)
+    for k in FIELDS:
+        assert np.array_equal(got[k], z[k]), k
+    assert [n for n, _ in got["refs"]] == list(z["ref_names"])
+    assert int(z["n_cigar"].max()) == 70001 and int((z["n_cigar"] == 0).sum()) >= 2      # CG-tag read, `*` CIGARs
+
+
+def test_decoder_inflates_every_block_of_the_golden_bam(hostsim):
+    from tests import util_bam as U
+    buf = open(GOLD_BAM, "rb").read()
+    blocks = U.bgzf_blocks(buf)
+    assert len(blocks) > 10 and blocks[-1][3] == 0                                     # ends with the empty EOF block
+    for off, p, n, isize in blocks:
+        rc, out = run_inflate(hostsim, buf[p:p + n], isize, pad=off % 4)
+        assert rc == 0 and out == zlib.decompress(buf[p:p + n], -15), off
+
+
+# ---- GPU
+def _same_reads(got, want):
+    for k in FIELDS:
+        assert np.array_equal(np.asarray(got[k]).astype(np.int64), np.asarray(want[k]).astype(np.int64)[:len(got[k])]), k
+
+
+@pytest.mark.gpu
+def test_load_bam_golden():
+    from svtrek_b200 import api
+    z = np.load(GOLD_NPZ)
+    a = api.Auditor(0)
+    st = a.load_bam(GOLD_BAM)
+    got = a.copy_reads()
+    for k in FIELDS:
+        assert np.array_equal(got[k].astype(np.int64), z[k].astype(np.int64)), k
+    assert a.bam_refs() == list(zip([str(x) for x in z["ref_names"]], [int(x) for x in z["ref_lens"]]))
+    assert st["n_reads"] == len(z["pos"]) and st["n_words"] == len(z["cigar"]) and st["n_blocks"] == 19 and st["n_ref"] == 3
+    assert st["inflated_bytes"] > st["file_bytes"]
+    # loading again (buffers reused) gives the same thing
+    a.load_bam(GOLD_BAM, GOLD_BAM + ".bai")
+    got2 = a.copy_reads()
+    for k in FIELDS:
+        assert np.array_equal(got2[k], got[k]), k
+
+
+@pytest.mark.gpu
+def test_load_bam_errors(tmp_path):
+    from svtrek_b200 import api
+    a = api.Auditor(0)
+    buf = bytearray(open(GOLD_BAM, "rb").read())
+    bai = open(GOLD_BAM + ".bai", "rb").read()
+
+    def attempt(name, data, index=bai):
+        p = tmp_path / name
+        p.write_bytes(bytes(data))
+        if index is not None:
+            (tmp_path / (name + ".bai")).write_bytes(index)
+        with pytest.raises(api.SvtkError):
+            a.load_bam(str(p))
+
+    attempt("noindex.bam", buf, index=None)
+    attempt("trunc.bam", buf[:len(buf) // 2])
+    attempt("magic.bam", b"\0" + bytes(buf[1:]))
+    from tests import util_bam as U
+    off, p, n, isize = U.bgzf_blocks(bytes(buf))[3]
+    bad = bytearray(buf)
+    bad[p + 2:p + 40] = bytes(38)                      # wipe the start of a DEFLATE payload: dynamic-block header becomes garbage
+    attempt("payload.bam", bad)
+    import struct
+    attempt("nref.bam", buf, index=bai[:4] + struct.pack("<i", 2) + bai[8:])                       # index of another file: reference count differs
+    assert struct.unpack_from("<i", bai, 8)[0] > 0 and struct.unpack_from("<i", bai, 16)[0] > 0       # ref 0 has a bin with a chunk at byte 20
+    attempt("stale1.bam", buf, index=bai[:20] + struct.pack("<Q", 12345 << 16) + bai[28:])          # chunk start inside no block
+    attempt("stale2.bam", buf, index=bai[:20] + struct.pack("<Q", off << 16 | 7) + bai[28:])        # a real block, but not a record boundary
+    with pytest.raises(api.SvtkError):
+        a.load_bam(str(tmp_path / "does_not_exist.bam"))
+    # the ctx is still usable afterwards
+    a.load_bam(GOLD_BAM)
+    assert a.copy_reads()["pos"].shape[0] == 256
+
+
+@pytest.mark.gpu
+def test_load_bam_live_equals_written_reads_and_refines_like_the_oracle(tmp_path):
+    """HTSlib-written BAM of a C1-like read set: loader output == the reads that were written; windows refined on the loaded
+    reads == the oracle on the original arrays."""
+    from oracle import binding as B
+    from svtrek_b200 import api, simreads as S
+    from tests import util_bam as U
+    if not os.path.exists(os.path.join(B.REF_DIR, "test_view")):
+        pytest.skip("oracle/_ref HTSlib tools not built here")
+    rs, truth = S.make_config("c1", scale=0.25)
+    sam, bam = str(tmp_path / "c1.sam"), str(tmp_path / "c1.bam")
+    S.write_sam(sam, rs)
+    B.make_bam(sam, bam)
+    a = api.Auditor(0)
+    st = a.load_bam(bam)
+    got = a.copy_reads()
+    assert st["n_reads"] == rs.n_reads and st["n_pieces"] >= 2
+    want = dict(tid_off=rs.tid_off, pos=rs.pos, end=rs.end, n_cigar=rs.n_cigar, cigar_off=rs.cigar_off[:-1], cigar=rs.cigar)
+    for k in FIELDS:
+        assert np.array_equal(got[k].astype(np.int64), np.asarray(want[k]).astype(np.int64)), k
+    py = U.read_bam(bam)
+    for k in FIELDS:
+        assert np.array_equal(got[k].astype(np.int64), py[k].astype(np.int64)), k
+    w = S.windows_from_truth(truth)
+    res = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    want = B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    assert np.array_equal(res, want) and int((want >= 0).sum()) > 10

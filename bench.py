@@ -56,6 +56,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--ref-sample-mb", type=float, default=3.0, help="--impl reference: contig length of the bounded sample")
     ap.add_argument("--ref-threads", type=int, default=0)
+    ap.add_argument("--no-bam", action="store_true", help="skip the file-to-file leg (svtk_load_bam + svtk_process_vcf on the reference arm's sample)")
     ap.add_argument("--poa-sets", type=int, default=4000, help="INS read sets per GPU of the POA (K3) leg: a bounded sample of configs[3]'s 20k records; 0 skips the leg")
     ap.add_argument("--poa-steps", type=int, default=2)
     return ap.parse_args()
@@ -471,6 +472,8 @@ def run_ours(args):
                 "bound": "integer ALU / instruction latency (no tensor cores: not a contraction)"}
             if world == 1 and not args.no_cpu:
                 out["poa_gcups"]["cpu_baseline"] = poa_cpu_baseline(poa_sets_l, poa_cons)
+        if world == 1 and not args.no_bam:
+            out["bam_e2e"] = bam_e2e_leg(a, args)
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_port_baseline(rs, w, n_records)
         print(json.dumps(out), flush=True)
@@ -478,6 +481,56 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def reference_sample(args):
+    """The bounded sample both arms' file-level legs run on: a contig of --ref-sample-mb Mb with the workload's coverage,
+    read length, error rate and SV density (same seed => the same BAM + VCF on both arms)."""
+    from svtrek_b200 import simreads as S
+    cfg = dict(S.CONFIGS[args.workload])
+    L = int(args.ref_sample_mb * 1e6)
+    full_L = float(sum(cfg["contig_lens"]))
+    cfg["n_sv"] = max(10, int(round(cfg["n_sv"] * L / full_L)))
+    cfg["contig_lens"] = [L]
+    seed = SEED0 + sorted(S.CONFIGS).index(args.workload)
+    if args.workload == "c5":
+        return S._make_c5(seed, cfg)
+    return S.simulate(seed, **cfg)
+
+
+def bam_e2e_leg(a, args, steps=5):
+    """File to file, like the reference CLI: svtk_load_bam (BGZF inflate + record extraction on the GPU) + svtk_process_vcf
+    (VCF in, the reference's stdout lines out) on the sample the reference arm times: same reads, same VCF; the BAM + BAI are
+    written by svtrek_b200.simreads.write_bam (HTSlib's block layout, zlib level 6; the reference CLI prints the same lines
+    from it as from the HTSlib-written file of the same reads -- tests/test_bam.py)."""
+    from svtrek_b200 import simreads as S
+    rs, truth = reference_sample(args)
+    cores = args.ref_threads or os.cpu_count() or 1
+    with tempfile.TemporaryDirectory(prefix="svtk_bam_") as d:
+        bam, vcf, out = (os.path.join(d, x) for x in ("s.bam", "s.vcf", "out.txt"))
+        S.write_bam(bam, rs)
+        S.write_vcf(vcf, S.vcf_lines(truth, end_first=True), pad=3 * cores + 8)      # the same file the reference arm reads
+        times, loads, n = [], [], 0
+        for i in range(2 + steps):
+            t0 = time.perf_counter()
+            st = a.load_bam(bam)
+            n = a.process_vcf(vcf, out)
+            dt = time.perf_counter() - t0
+            if i >= 2:
+                times.append(dt); loads.append(st)
+        got = a.copy_reads()
+        same = bool(np.array_equal(got["pos"], rs.pos) and np.array_equal(got["end"], rs.end) and np.array_equal(got["cigar"], rs.cigar))
+        tot = float(sum(times))
+        best = min(loads, key=lambda r: r["total_ms"])
+        return {"value": n * len(times) / tot, "unit": UNIT, "ms_per_step": tot * 1e3 / len(times), "steps": len(times), "records_per_step": int(n),
+                "path": "svtk_load_bam(BAM + BAI files) + svtk_process_vcf(VCF file -> output file), wall clock, every step; page cache warm",
+                "sample": f"the reference arm's sample: {args.ref_sample_mb} Mb contig, {rs.n_reads} reads, {os.path.getsize(bam) / 1e6:.0f} MB BAM "
+                          f"(random SEQ/QUAL)",
+                "loaded_reads_identical_to_written": same,
+                "load_bam": {"file_MB": best["file_bytes"] / 1e6, "inflated_MB": best["inflated_bytes"] / 1e6, "bgzf_blocks": best["n_blocks"],
+                             "host_scan_ms": best["host_scan_ms"], "upload_ms": best["upload_ms"], "inflate_kernel_ms": best["inflate_ms"],
+                             "record_kernels_ms": best["parse_ms"], "total_ms": best["total_ms"],
+                             "inflate_GBps": best["inflated_bytes"] / max(best["inflate_ms"], 1e-6) / 1e6}}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -493,16 +546,7 @@ def run_reference(args):
     from svtrek_b200 import simreads as S
     K, W = args.steps, args.warmup
     cores = args.ref_threads or os.cpu_count() or 1
-    cfg = dict(S.CONFIGS[args.workload])
-    L = int(args.ref_sample_mb * 1e6)
-    full_L = float(sum(cfg["contig_lens"]))
-    cfg["n_sv"] = max(10, int(round(cfg["n_sv"] * L / full_L)))
-    cfg["contig_lens"] = [L]
-    seed = SEED0 + sorted(S.CONFIGS).index(args.workload)
-    if args.workload == "c5":
-        rs, truth = S._make_c5(seed, cfg)
-    else:
-        rs, truth = S.simulate(seed, **cfg)
+    rs, truth = reference_sample(args)
     w = S.windows_from_truth(truth)
     n_records = int(np.unique(w["record"]).shape[0])
     base = {"metric": METRIC, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "higher_is_better": True, "scaling": "weak",

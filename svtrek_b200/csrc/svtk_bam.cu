@@ -50,7 +50,9 @@ constexpr unsigned FULLMASK = 0xffffffffu;
 __global__ void __launch_bounds__(32) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned n_blocks,
                                                      uint8_t *__restrict__ out, unsigned int *__restrict__ ctl) {
     extern __shared__ uint32_t bz_sm[];
-    BzTables &T = *reinterpret_cast<BzTables *>(bz_sm + threadIdx.x * BZ_TABLE_WORDS);
+    BzTables T;
+    T.lit = reinterpret_cast<uint16_t *>(bz_sm + threadIdx.x * BZ_TABLE_WORDS);
+    T.dist = T.lit + (1 << BZ_LBITS);
     BzLane z;
     z.state = BZ_S_IDLE; z.err = BZ_OK;
     unsigned cur = 0xffffffffu;
@@ -271,7 +273,9 @@ int read_header(const uint8_t *f, size_t n, const std::vector<BgzfBlock> &blk, s
     std::vector<uint32_t> words;                          // the decoder reads aligned words: one block's payload at a time
     std::vector<uint8_t> hd;
     size_t nb = 0;
-    static BzTables T;
+    static uint16_t lit[1 << BZ_LBITS], dist[1 << BZ_DBITS];
+    BzTables T;
+    T.lit = lit; T.dist = dist;
     (void)n;
     auto more = [&](size_t need) -> int {
         while (hd.size() < need) {
@@ -425,7 +429,9 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
         if (!attr_set) { CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
         int sms = 148;
         CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * 3, (blk.size() + 31) / 32);
+        int per_sm = 1;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (blk.size() + 31) / 32);
         k_bgzf_inflate<<<grid, 32, smem, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)blk.size(),
                                                      (uint8_t *)c->bam_infl.p, ctl);
         CU(cudaGetLastError());

@@ -10,7 +10,8 @@
 // Decoder shape (per lane, state in registers, tables in shared memory):
 //   - 64-bit LSB-first bit buffer refilled 32 bits at a time from the (word aligned) compressed buffer;
 //   - canonical Huffman codes: a primary lookup table (9 bits literal/length, 8 bits distance; entry = symbol << 4 | code
-//     length) filled per DEFLATE block, and for the rare longer codes the count/first-code walk over the code lengths;
+//     length) in shared memory, filled per DEFLATE block, and for the rare longer codes the count/first-code walk over the
+//     code lengths (those small arrays live in thread-local memory);
 //   - length / distance bases computed arithmetically (no constant-memory tables: lanes index them divergently);
 //   - every output byte is bounds-checked against the block's ISIZE, every match distance against the bytes produced so far
 //     (a BGZF block has no preset dictionary), so corrupt input yields an error code, never a stray store.
@@ -26,23 +27,31 @@
 
 namespace svtk {
 
-constexpr int BZ_LBITS = 9, BZ_DBITS = 8;
+#ifndef SVTK_BZ_LBITS
+#define SVTK_BZ_LBITS 8
+#endif
+#ifndef SVTK_BZ_DBITS
+#define SVTK_BZ_DBITS 7
+#endif
+constexpr int BZ_LBITS = SVTK_BZ_LBITS, BZ_DBITS = SVTK_BZ_DBITS;     // primary table bits (>= 7: the code-length code borrows the distance table)
 enum { BZ_OK = 0, BZ_ERR_BTYPE = 1, BZ_ERR_STORED = 2, BZ_ERR_LENS = 3, BZ_ERR_CODE = 4, BZ_ERR_DIST = 5, BZ_ERR_OUT = 6,
        BZ_ERR_IN = 7, BZ_ERR_SIZE = 8, BZ_ERR_HEADER = 9 };
 
-struct BzTables {                         // one per lane; all members 16-bit so that a lane's copy can start at any 4-byte boundary
-    uint16_t lit[1 << BZ_LBITS];          // primary literal/length table: sym << 4 | len, 0 = code longer than BZ_LBITS
-    uint16_t dist[1 << BZ_DBITS];
-    uint16_t lsym[288], dsym[32];         // symbols in canonical order (for the long-code walk)
-    uint16_t lcnt[16], dcnt[16];          // codes per length
+struct BzTables {                         // one per lane
+    uint16_t *lit;                        // primary literal/length table [1 << BZ_LBITS]: sym << 4 | len, 0 = code longer than BZ_LBITS
+    uint16_t *dist;                       // primary distance table [1 << BZ_DBITS]   (both in shared memory on the GPU)
+    uint16_t lsym[288], dsym[32];         // symbols in canonical order, codes per length: table builds and the long-code walk only
+    uint16_t lcnt[16], dcnt[16];          //   (thread-local memory on the GPU)
+    uint32_t lresume, dresume;            // long-code walk resumed after the primary bits: first code << 16 | symbol index
 };
-constexpr int BZ_TABLE_WORDS = (int)((sizeof(BzTables) + 3) / 4) | 1;   // odd stride: 32 lanes' copies start in 32 different banks
+constexpr int BZ_TABLE_WORDS = (((1 << BZ_LBITS) + (1 << BZ_DBITS)) / 2) | 1;   // 32-bit words per lane; odd stride: 32 lanes, 32 banks
 
 struct BzBits {
     const uint32_t *w;                    // compressed buffer, 4-byte aligned, readable 8 bytes past the last block
     unsigned long long ip, end;           // byte offsets: next unread byte, end of this block's DEFLATE payload
     unsigned long long buf;
     int cnt;
+    uint32_t nxt;                         // the word at ip, loaded one refill ahead
 };
 
 BZ_HD uint32_t bz_load32(const uint32_t *w, unsigned long long off) {
@@ -56,8 +65,15 @@ BZ_HD uint32_t bz_load32(const uint32_t *w, unsigned long long off) {
 }
 BZ_HD uint32_t bz_byte(const uint32_t *w, unsigned long long off) { return (w[off >> 2] >> ((uint32_t)(off & 3) * 8u)) & 255u; }
 
-BZ_HD void bz_refill(BzBits &b) {         // afterwards cnt >= 32
-    if (b.cnt < 32) { b.buf |= (unsigned long long)bz_load32(b.w, b.ip) << b.cnt; b.ip += 4; b.cnt += 32; }
+// ip is kept 4-byte aligned so that a refill is ONE aligned load (lanes read different lines: every load instruction costs
+// the warp 32 cache accesses, so halving the loads matters more than the shift it costs)
+BZ_HD void bz_prime(BzBits &b, unsigned long long pos) {      // start reading bits at byte offset pos
+    const uint32_t drop = (uint32_t)(pos & 3) * 8u;
+    b.buf = (unsigned long long)(b.w[pos >> 2] >> drop); b.cnt = 32 - (int)drop; b.ip = (pos & ~3ull) + 4;
+    b.nxt = b.w[b.ip >> 2];
+}
+BZ_HD void bz_refill(BzBits &b) {         // afterwards cnt >= 32; the load issued here is consumed by the NEXT refill
+    if (b.cnt < 32) { b.buf |= (unsigned long long)b.nxt << b.cnt; b.ip += 4; b.cnt += 32; b.nxt = b.w[b.ip >> 2]; }
 }
 BZ_HD uint32_t bz_take(BzBits &b, int n) {   // n <= 16, cnt >= n
     const uint32_t v = (uint32_t)b.buf & ((1u << n) - 1u);
@@ -76,7 +92,7 @@ BZ_HD uint32_t bz_rev(uint32_t code, int len) {
 }
 
 // canonical code from lens[0..n): counts, symbols in code order, primary table of `bits` bits.  Over-subscribed -> error.
-BZ_HD int bz_build(const uint8_t *lens, int n, uint16_t *cnt, uint16_t *sym, uint16_t *tab, int bits) {
+BZ_HD int bz_build(const uint8_t *lens, int n, uint16_t *cnt, uint16_t *sym, uint16_t *tab, int bits, uint32_t *resume) {
     for (int l = 0; l < 16; ++l) cnt[l] = 0;
     for (int s = 0; s < n; ++s) cnt[lens[s]]++;
     int left = 1;
@@ -95,16 +111,18 @@ BZ_HD int bz_build(const uint8_t *lens, int n, uint16_t *cnt, uint16_t *sym, uin
         }
         code <<= 1;
     }
+    *resume = code << 16 | (uint32_t)idx;                   // state of the long-code walk after `bits` lengths
     return BZ_OK;
 }
 
 // one symbol: primary table, else the bit-by-bit walk (codes longer than `bits`).  cnt >= 15 bits available.  -1 = invalid code
-BZ_HD int bz_symbol(BzBits &b, const uint16_t *tab, int bits, const uint16_t *cnt, const uint16_t *sym) {
+BZ_HD int bz_symbol(BzBits &b, const uint16_t *tab, int bits, const uint16_t *cnt, const uint16_t *sym, uint32_t resume) {
     const uint32_t e = tab[(uint32_t)b.buf & ((1u << bits) - 1u)];
     if (e) { const int l = (int)(e & 15u); b.buf >>= l; b.cnt -= l; return (int)(e >> 4); }
-    int code = 0, first = 0, index = 0;
-    unsigned long long v = b.buf;
-    for (int l = 1; l < 16; ++l) {
+    // codes longer than the primary table: the canonical walk (first code / count per length), resumed at bits + 1
+    int code = (int)(bz_rev((uint32_t)b.buf & ((1u << bits) - 1u), bits) << 1), first = (int)(resume >> 16), index = (int)(resume & 0xffffu);
+    unsigned long long v = b.buf >> bits;
+    for (int l = bits + 1; l < 16; ++l) {
         code |= (int)(v & 1ull); v >>= 1;
         const int c = (int)cnt[l];
         if (code - c < first) { b.buf >>= l; b.cnt -= l; return (int)sym[index + (code - first)]; }
@@ -128,12 +146,13 @@ enum { BZ_S_IDLE = 0, BZ_S_HEADER = 1, BZ_S_SYMBOLS = 2 };
 struct BzLane {
     BzBits b;
     uint8_t *out;
-    uint32_t op, out_len;
+    uint32_t op, out_len;                 // bytes produced so far / expected (ISIZE)
     int state, last, err;
 };
 
 BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len) {
-    z.b.w = words; z.b.ip = in_beg; z.b.end = in_end; z.b.buf = 0; z.b.cnt = 0;
+    z.b.w = words; z.b.end = in_end;
+    bz_prime(z.b, in_beg);
     z.out = out; z.op = 0; z.out_len = out_len; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
 }
 
@@ -155,15 +174,16 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
     if (type == 3) return bz_fail(z, BZ_ERR_BTYPE);
     if (type == 0) {                                                       // stored: byte align, LEN, ~LEN, bytes
         bz_take(b, b.cnt & 7);
-        b.ip -= (unsigned long long)(b.cnt >> 3); b.buf = 0; b.cnt = 0;    // hand the whole bytes back
-        if (b.ip + 4 > b.end) return bz_fail(z, BZ_ERR_STORED);
-        const uint32_t len = bz_byte(b.w, b.ip) | bz_byte(b.w, b.ip + 1) << 8;
-        const uint32_t nlen = bz_byte(b.w, b.ip + 2) | bz_byte(b.w, b.ip + 3) << 8;
-        b.ip += 4;
-        if ((len ^ nlen) != 0xffffu || b.ip + len > b.end) return bz_fail(z, BZ_ERR_STORED);
+        unsigned long long ip = b.ip - (unsigned long long)(b.cnt >> 3);   // hand the whole bytes back
+        if (ip + 4 > b.end) return bz_fail(z, BZ_ERR_STORED);
+        const uint32_t len = bz_byte(b.w, ip) | bz_byte(b.w, ip + 1) << 8;
+        const uint32_t nlen = bz_byte(b.w, ip + 2) | bz_byte(b.w, ip + 3) << 8;
+        ip += 4;
+        if ((len ^ nlen) != 0xffffu || ip + len > b.end) return bz_fail(z, BZ_ERR_STORED);
         if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
-        for (uint32_t k = 0; k < len; ++k) z.out[z.op + k] = (uint8_t)bz_byte(b.w, b.ip + k);
-        z.op += len; b.ip += len;
+        for (uint32_t k = 0; k < len; ++k) z.out[z.op + k] = (uint8_t)bz_byte(b.w, ip + k);
+        z.op += len;
+        bz_prime(b, ip + len);
         if (z.last) bz_finish(z);
         return;
     }
@@ -183,11 +203,11 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
         for (int i = 0; i < 19; ++i) lens[i] = 0;
         for (int i = 0; i < hclen; ++i) { bz_refill(b); lens[bz_clen_order(i)] = (uint8_t)bz_take(b, 3); }
         // the code-length code borrows the distance table's storage (its 7-bit primary table covers every code)
-        if (bz_build(lens, 19, T.dcnt, T.dsym, T.dist, 7)) return bz_fail(z, BZ_ERR_LENS);
+        if (bz_build(lens, 19, T.dcnt, T.dsym, T.dist, 7, &T.dresume)) return bz_fail(z, BZ_ERR_LENS);
         int n = 0, prev = 0;
         while (n < hlit + hdist) {
             bz_refill(b);
-            const int s = bz_symbol(b, T.dist, 7, T.dcnt, T.dsym);
+            const int s = bz_symbol(b, T.dist, 7, T.dcnt, T.dsym, T.dresume);
             if (s < 0) return bz_fail(z, BZ_ERR_CODE);
             if (s < 16) { lens[n++] = (uint8_t)s; prev = s; continue; }
             int rep, val = 0;
@@ -200,16 +220,44 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
         if (lens[256] == 0) return bz_fail(z, BZ_ERR_LENS);                // no end-of-block code
         if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
     }
-    if (bz_build(lens, hlit, T.lcnt, T.lsym, T.lit, BZ_LBITS)) return bz_fail(z, BZ_ERR_LENS);
-    if (bz_build(lens + hlit, hdist, T.dcnt, T.dsym, T.dist, BZ_DBITS)) return bz_fail(z, BZ_ERR_LENS);
+    if (bz_build(lens, hlit, T.lcnt, T.lsym, T.lit, BZ_LBITS, &T.lresume)) return bz_fail(z, BZ_ERR_LENS);
+    if (bz_build(lens + hlit, hdist, T.dcnt, T.dsym, T.dist, BZ_DBITS, &T.dresume)) return bz_fail(z, BZ_ERR_LENS);
     z.state = BZ_S_SYMBOLS;
+}
+
+// LZ77 copy of len bytes from dist bytes back (bounds checked by the caller).  The window is the block's own output in
+// global memory, so a byte-by-byte loop pays one memory round trip per byte (each load may alias the previous store).
+// dist >= 8: groups of up to 8 loads issued together, then their stores.  dist < 8 (runs): the period is read once into a
+// register and replayed.  (Collecting the output in a 64-bit register and storing aligned words was measured slower on
+// B200: the decoder is bound by instruction latency of the few resident warps, not by cache accesses -- DESIGN.md 10.)
+BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
+    const uint8_t *src = o - dist;
+    if (dist >= 8u) {
+        for (uint32_t k = 0; k < len; k += 8u) {
+            const uint32_t n = len - k < 8u ? len - k : 8u;
+            uint8_t t[8];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t i = 0; i < 8u; ++i) if (i < n) t[i] = src[k + i];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t i = 0; i < 8u; ++i) if (i < n) o[k + i] = t[i];
+        }
+    } else {
+        unsigned long long pat = 0;
+        for (uint32_t i = 0; i < dist; ++i) pat |= (unsigned long long)src[i] << (8u * i);
+        uint32_t ph = 0;
+        for (uint32_t k = 0; k < len; ++k) { o[k] = (uint8_t)(pat >> (8u * ph)); ph = ph + 1u == dist ? 0u : ph + 1u; }
+    }
 }
 
 // one literal/length symbol (and its distance + copy).  Only called in state BZ_S_SYMBOLS.
 BZ_HD void bz_step(BzLane &z, const BzTables &T) {
     BzBits &b = z.b;
     bz_refill(b);
-    const int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym);
+    const int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
     if (s < 256) {
         if (s < 0) return bz_fail(z, BZ_ERR_CODE);
         if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
@@ -226,7 +274,7 @@ BZ_HD void bz_step(BzLane &z, const BzTables &T) {
     else if (s == 285) len = 258;
     else { const int k = s - 261, eb = k >> 2; len = 3u + ((4u + (uint32_t)(k & 3)) << eb) + bz_take(b, eb); }
     bz_refill(b);
-    const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym);
+    const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
     if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
     uint32_t dist;
     if (d < 4) dist = (uint32_t)d + 1u;
@@ -234,8 +282,7 @@ BZ_HD void bz_step(BzLane &z, const BzTables &T) {
     if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
     if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
     if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
-    uint8_t *o = z.out + z.op;
-    for (uint32_t k = 0; k < len; ++k) o[k] = o[(long long)k - (long long)dist];
+    bz_copy(z.out + z.op, dist, len);
     z.op += len;
 }
 

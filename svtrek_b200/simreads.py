@@ -405,3 +405,104 @@ def windows_from_truth(truth: SVTruth, seed=1, *, pos_noise=40, wider=20000, med
     m = 0xFFFFFFFF
     return dict(chrom=w_chrom, start=(w_start & m).astype(np.uint32), end=(w_end & m).astype(np.uint32),
                 pos=(w_pos & m).astype(np.uint32), kind=w_kind, record=w_rec)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# BAM + BAI writer (SAMv1 4.2, 5.2) for the file-level tests and bench legs: same records write_sam describes, BGZF blocks
+# cut the way HTSlib cuts them (a record that does not fit starts a new block, bgzf.c bgzf_flush_try), zlib level 6.
+def _reg2bin(beg, end):
+    end -= 1
+    for shift, base in ((14, 4681), (17, 585), (20, 73), (23, 9), (26, 1)):
+        if beg >> shift == end >> shift:
+            return base + (beg >> shift)
+    return 0
+
+
+def _bgzf_block(data):
+    import struct
+    import zlib
+    c = zlib.compressobj(6, zlib.DEFLATED, -15)
+    comp = c.compress(data) + c.flush()
+    return (b"\x1f\x8b\x08\x04\0\0\0\0\0\xff\x06\0BC\x02\0" + struct.pack("<H", len(comp) + 25) + comp +
+            struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data)))
+
+
+def write_bam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr"):
+    """Coordinate-sorted BAM + `path`.bai of a ReadSet; SEQ / QUAL uniform random like write_sam.  Returns the file size."""
+    import struct
+    rng = np.random.default_rng(seed)
+    BLOCK = 0xff00
+    text = "@HD\tVN:1.6\tSO:coordinate\n" + "".join(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L}\n" for t, L in enumerate(rs.contig_len))
+    hdr = b"BAM\1" + struct.pack("<i", len(text)) + text.encode() + struct.pack("<i", rs.n_tid)
+    for t, L in enumerate(rs.contig_len):
+        nm = f"{chr_prefix}{t + 1}".encode() + b"\0"
+        hdr += struct.pack("<i", len(nm)) + nm + struct.pack("<i", int(L))
+    bins = [dict() for _ in range(rs.n_tid)]
+    lin = [dict() for _ in range(rs.n_tid)]
+    with open(path, "wb") as f:
+        state = {"coff": 0, "buf": bytearray()}
+
+        def flush():
+            if state["buf"]:
+                blk = _bgzf_block(bytes(state["buf"]))
+                f.write(blk)
+                state["coff"] += len(blk)
+                state["buf"] = bytearray()
+
+        def put(data):                     # HTSlib: flush first if the record does not fit; oversized records span blocks
+            if len(state["buf"]) + len(data) > BLOCK:
+                flush()
+            v0 = state["coff"] << 16 | len(state["buf"])
+            while len(state["buf"]) + len(data) > BLOCK:
+                k = BLOCK - len(state["buf"])
+                state["buf"] += data[:k]
+                data = data[k:]
+                flush()
+            state["buf"] += data
+            return v0, state["coff"] << 16 | len(state["buf"])
+
+        put(hdr)
+        flush()
+        for t in range(rs.n_tid):
+            for r in range(int(rs.tid_off[t]), int(rs.tid_off[t + 1])):
+                w = rs.cigar[int(rs.cigar_off[r]):int(rs.cigar_off[r + 1])].astype("<u4")
+                op = w & 15
+                ql = int(((w >> 4)[(op == OP_M) | (op == OP_I) | (op == OP_S) | (op == OP_EQ) | (op == OP_X)]).sum())
+                nib = rng.integers(0, 4, ql + (ql & 1)).astype(np.uint8)
+                nib = (1 << nib).astype(np.uint8)                      # A C G T = 1 2 4 8
+                if ql & 1:
+                    nib[-1] = 0
+                seq = (nib[0::2] << 4 | nib[1::2]).astype(np.uint8).tobytes()
+                qual = rng.integers(10, 41, ql).astype(np.uint8).tobytes()
+                name = f"r{r}".encode() + b"\0"
+                flag = 0 if flags is None else int(flags[r])
+                pos, end = int(rs.pos[r]), int(rs.end[r])
+                if len(w) > 65535:
+                    raise ValueError("write_bam: CIGARs beyond 65535 operations need the CG tag (use the HTSlib-written golden file)")
+                body = struct.pack("<iiBBHHHiiii", t, pos, len(name), 60, _reg2bin(pos, end), len(w), flag, ql, -1, -1, 0) + name + w.tobytes() + seq + qual
+                v0, v1 = put(struct.pack("<i", len(body)) + body)
+                b = bins[t].setdefault(_reg2bin(pos, end), [])
+                if b and b[-1][1] == v0:
+                    b[-1][1] = v1
+                else:
+                    b.append([v0, v1])
+                for win in range(pos >> 14, ((end - 1) >> 14) + 1):
+                    lin[t].setdefault(win, v0)
+        flush()
+        f.write(_bgzf_block(b""))                                         # EOF marker block
+        size = state["coff"] + 28
+    with open(path + ".bai", "wb") as f:
+        f.write(b"BAI\1" + struct.pack("<i", rs.n_tid))
+        for t in range(rs.n_tid):
+            f.write(struct.pack("<i", len(bins[t])))
+            for b in sorted(bins[t]):
+                f.write(struct.pack("<Ii", b, len(bins[t][b])))
+                for v0, v1 in bins[t][b]:
+                    f.write(struct.pack("<QQ", v0, v1))
+            n_intv = (max(lin[t]) + 1) if lin[t] else 0
+            f.write(struct.pack("<i", n_intv))
+            prev = 0
+            for win in range(n_intv):
+                prev = lin[t].get(win, prev)                              # empty windows repeat the previous offset, like HTSlib
+                f.write(struct.pack("<Q", prev))
+    return size

@@ -156,6 +156,7 @@ typedef struct {
     uint64_t n_reads, n_words;
     int32_t n_ref;
     uint32_t n_pieces;               /* pieces the record chain was cut into */
+    uint32_t lanes_per_warp;         /* BGZF blocks decoded side by side in one warp (1..32, grows with the file) */
     float host_scan_ms;              /* mmap + BGZF block table + header + .bai */
     float upload_ms, inflate_ms, parse_ms, total_ms;
 } svtk_bam_stats;

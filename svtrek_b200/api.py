@@ -69,7 +69,7 @@ class PoaStats(C.Structure):
 
 class BamStats(C.Structure):
     _fields_ = [("file_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("inflated_bytes", C.c_uint64), ("n_reads", C.c_uint64), ("n_words", C.c_uint64),
-                ("n_ref", C.c_int32), ("n_pieces", C.c_uint32), ("host_scan_ms", C.c_float), ("upload_ms", C.c_float), ("inflate_ms", C.c_float),
+                ("n_ref", C.c_int32), ("n_pieces", C.c_uint32), ("lanes_per_warp", C.c_uint32), ("host_scan_ms", C.c_float), ("upload_ms", C.c_float), ("inflate_ms", C.c_float),
                 ("parse_ms", C.c_float), ("total_ms", C.c_float)]
 
 

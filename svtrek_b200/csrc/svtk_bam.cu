@@ -24,8 +24,10 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <fcntl.h>
@@ -47,16 +49,22 @@ enum { BW_OK = 0, BW_ERR_SHORT = 1, BW_ERR_SIZE = 2, BW_ERR_FIELDS = 3, BW_ERR_A
 constexpr unsigned FULLMASK = 0xffffffffu;
 
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned n_blocks,
-                                                     uint8_t *__restrict__ out, unsigned int *__restrict__ ctl) {
+// `lanes` = lanes per warp that decode (1 .. 32): the decoder is bound by the instruction latency of one warp, and a warp pays
+// for the union of its lanes' paths (literal / match / long code / block switch), so a file with few blocks runs faster
+// spread over many thin warps; a large file needs all 32 lanes to fit the machine.
+#ifndef SVTK_BZ_MINB
+#define SVTK_BZ_MINB 16           // resident single-warp CTAs per SM the register allocation must allow
+#endif
+__global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned n_blocks,
+                                                     uint8_t *__restrict__ out, unsigned int *__restrict__ ctl, int lanes) {
     extern __shared__ uint32_t bz_sm[];
     BzTables T;
-    T.lit = reinterpret_cast<uint16_t *>(bz_sm + threadIdx.x * BZ_TABLE_WORDS);
+    T.lit = reinterpret_cast<uint16_t *>(bz_sm + (threadIdx.x < (unsigned)lanes ? threadIdx.x : 0u) * BZ_TABLE_WORDS);
     T.dist = T.lit + (1 << BZ_LBITS);
     BzLane z;
     z.state = BZ_S_IDLE; z.err = BZ_OK;
     unsigned cur = 0xffffffffu;
-    bool drained = false;
+    bool drained = threadIdx.x >= (unsigned)lanes;
     for (;;) {
         if (z.state == BZ_S_IDLE && !drained) {
             if (cur != 0xffffffffu && z.err) { if (atomicCAS(&ctl[BAM_CTL_ZERR], 0u, cur + 1u) == 0u) ctl[BAM_CTL_ZCODE] = (unsigned)z.err; }
@@ -71,8 +79,9 @@ __global__ void __launch_bounds__(32) k_bgzf_inflate(const uint32_t *__restrict_
         // burst of symbol steps that all lanes take together
         if (z.state == BZ_S_HEADER) bz_header(z, T);
 #pragma unroll 1
-        for (int it = 0; it < 64; ++it)
+        for (int it = 0; it < BZ_BURST; ++it)
             if (z.state == BZ_S_SYMBOLS) bz_step(z, T);
+        bz_check_input(z);
     }
 }
 
@@ -281,7 +290,7 @@ int read_header(const uint8_t *f, size_t n, const std::vector<BgzfBlock> &blk, s
         while (hd.size() < need) {
             if (nb >= blk.size()) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
             const BgzfBlock &b = blk[nb++];
-            words.assign((size_t)b.in_len / 4 + 4, 0u);
+            words.assign((size_t)(b.in_len + BZ_OVERREAD) / 4 + 4, 0u);
             memcpy(words.data(), f + b.in_beg, b.in_len);
             const size_t at = hd.size();
             hd.resize(at + b.isize);
@@ -349,6 +358,38 @@ int read_bai(const char *path, int n_ref_expected, std::vector<uint64_t> &voffs)
     return 0;
 }
 
+// host -> device copy of a (pageable, memory-mapped) file image: the ctx's two pinned staging buffers, each chunk copied into
+// staging by several threads at once (one thread faults pages in at ~10 GB/s, the DMA engine takes ~50 GB/s)
+int upload_file(Ctx *c, void *dst, const uint8_t *src, size_t bytes) {
+    const size_t CH = 32u << 20;
+    for (int i = 0; i < 2; ++i) {
+        if (int rc = c->stage[i].reserve(CH)) return rc;
+        if (!c->stage_ev[i]) CU(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const int T = (int)std::min(8u, std::max(1u, hw / 2));
+    size_t done = 0;
+    int k = 0;
+    while (done < bytes) {
+        const size_t n = std::min(CH, bytes - done);
+        CU(cudaEventSynchronize(c->stage_ev[k]));
+        char *st = (char *)c->stage[k].p;
+        const size_t per = ((n + T - 1) / T + 4095) & ~(size_t)4095;
+        std::vector<std::thread> th;
+        for (int t = 1; t < T; ++t) {
+            const size_t a = per * t;
+            if (a < n) th.emplace_back([=]() { memcpy(st + a, src + done + a, std::min(per, n - a)); });
+        }
+        memcpy(st, src + done, std::min(per, n));
+        for (auto &x : th) x.join();
+        CU(cudaMemcpyAsync((char *)dst + done, st, n, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaEventRecord(c->stage_ev[k], c->stream));
+        done += n;
+        k ^= 1;
+    }
+    return 0;
+}
+
 double ms_since(std::chrono::steady_clock::time_point t0) {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -367,46 +408,63 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     Mapped bam;
     if (bam.open_file(bam_path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open %s", bam_path);
     if (bam.n == 0) return fail(SVTK_ERR_IO, "bam: %s is empty", bam_path);
+    // the table work runs on a helper thread while this thread feeds the upload ring (both only read the mapping)
     std::vector<BgzfBlock> blk;
     std::vector<uint64_t> coff;
-    if (int rc = scan_bgzf(bam.p, bam.n, blk, coff)) return rc;
-    const unsigned long long total = blk.empty() ? 0ull : blk.back().out_off + blk.back().isize;
-    if (blk.size() >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: shard the file");
-    unsigned long long first_rec = 0;
-    if (int rc = read_header(bam.p, bam.n, blk, c->bam_ref_names, c->bam_ref_lens, &first_rec)) return rc;
-    const int n_ref = (int)c->bam_ref_names.size();
-    if (first_rec > total) return fail(SVTK_ERR_IO, "bam: header longer than the file");
-
-    std::vector<uint64_t> voffs;
-    {
+    std::vector<unsigned long long> splits;
+    unsigned long long total = 0, first_rec = 0;
+    int n_ref = 0, n_seg = 0, prep_rc = 0;
+    std::string prep_msg;
+    double prep_ms = 0;
+    auto prep = [&]() -> int {
+        if (int rc = scan_bgzf(bam.p, bam.n, blk, coff)) return rc;
+        total = blk.empty() ? 0ull : blk.back().out_off + blk.back().isize;
+        if (blk.size() >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: shard the file");
+        if (int rc = read_header(bam.p, bam.n, blk, c->bam_ref_names, c->bam_ref_lens, &first_rec)) return rc;
+        n_ref = (int)c->bam_ref_names.size();
+        if (first_rec > total) return fail(SVTK_ERR_IO, "bam: header longer than the file");
+        std::vector<uint64_t> voffs;
         std::string bai = bai_path ? std::string(bai_path) : std::string(bam_path) + ".bai";
         if (!bai_path && access(bai.c_str(), R_OK) != 0) {
             std::string alt(bam_path);
             if (alt.size() > 4 && alt.compare(alt.size() - 4, 4, ".bam") == 0) { alt.replace(alt.size() - 4, 4, ".bai"); if (access(alt.c_str(), R_OK) == 0) bai = alt; }
         }
         if (int rc = read_bai(bai.c_str(), n_ref, voffs)) return rc;
-    }
-    std::vector<unsigned long long> splits;
-    splits.reserve(voffs.size() + 2);
-    splits.push_back(first_rec);
-    for (uint64_t v : voffs) {
-        const uint64_t co = v >> 16, uo = v & 0xffffu;
-        auto it = std::lower_bound(coff.begin(), coff.end(), co);
-        if (it == coff.end() || *it != co) return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a BGZF block (stale .bai?)", (unsigned long long)co);
-        const BgzfBlock &b = blk[(size_t)(it - coff.begin())];
-        if (uo > b.isize) return fail(SVTK_ERR_IO, "bam: index offset beyond its block (stale .bai?)");
-        const unsigned long long lin = b.out_off + uo;
-        if (lin > first_rec && lin < total) splits.push_back(lin);
-    }
-    std::sort(splits.begin(), splits.end());
-    splits.erase(std::unique(splits.begin(), splits.end()), splits.end());
-    const int n_seg = first_rec < total ? (int)splits.size() : 0;
-    splits.push_back(total);
-    const double host_ms = ms_since(t_all);
+        splits.reserve(voffs.size() + 2);
+        splits.push_back(first_rec);
+        for (uint64_t v : voffs) {
+            const uint64_t co = v >> 16, uo = v & 0xffffu;
+            auto it = std::lower_bound(coff.begin(), coff.end(), co);
+            if (it == coff.end() || *it != co) return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a BGZF block (stale .bai?)", (unsigned long long)co);
+            const BgzfBlock &b = blk[(size_t)(it - coff.begin())];
+            if (uo > b.isize) return fail(SVTK_ERR_IO, "bam: index offset beyond its block (stale .bai?)");
+            const unsigned long long lin = b.out_off + uo;
+            if (lin > first_rec && lin < total) splits.push_back(lin);
+        }
+        std::sort(splits.begin(), splits.end());
+        splits.erase(std::unique(splits.begin(), splits.end()), splits.end());
+        n_seg = first_rec < total ? (int)splits.size() : 0;
+        splits.push_back(total);
+        return 0;
+    };
+    std::thread prep_thread([&]() {
+        prep_rc = prep();
+        if (prep_rc) prep_msg = svtk_last_error();            // the message lives in the helper thread's slot
+        prep_ms = ms_since(t_all);
+    });
+    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{prep_thread};
 
-    // ---- device: file image, inflate
+    // ---- device: the compressed file image (needs nothing from the tables)
     for (int i = 0; i < 4; ++i) if (!c->bam_ev[i]) CU(cudaEventCreate(&c->bam_ev[i]));
-    if (int rc = c->bam_comp.reserve(bam.n + 64)) return rc;
+    if (int rc = c->bam_comp.reserve(bam.n + BZ_OVERREAD)) return rc;
+    CU(cudaMemsetAsync((char *)c->bam_comp.p + (bam.n & ~(size_t)3), 0, BZ_OVERREAD - (bam.n & 3), c->stream));   // the decoder looks a few bytes past the end
+    CU(cudaEventRecord(c->bam_ev[0], c->stream));
+    if (int rc = upload_file(c, c->bam_comp.p, bam.p, bam.n)) return rc;
+    prep_thread.join();
+    if (prep_rc) return fail(prep_rc, "%s", prep_msg.c_str());
+    const double host_ms = prep_ms;
+
+    // ---- device: tables, inflate
     if (int rc = c->bam_infl.reserve((size_t)total + 64)) return rc;
     if (int rc = c->bam_blocks.reserve(sizeof(BgzfBlock) * std::max<size_t>(blk.size(), 1))) return rc;
     if (int rc = c->bam_splits.reserve(8 * splits.size())) return rc;
@@ -414,26 +472,30 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     if (int rc = c->bam_ctl.reserve(256)) return rc;
     if (int rc = c->bam_h.reserve(256 + 8 * (size_t)(n_ref + 1) + 16 * (size_t)std::max(n_seg, 1))) return rc;
     CU(cudaMemsetAsync(c->bam_ctl.p, 0, 256, c->stream));
-    CU(cudaMemsetAsync((char *)c->bam_comp.p + (bam.n & ~(size_t)3), 0, 64 - (bam.n & 3), c->stream));   // the decoder may look 8 bytes past the end
     CU(cudaMemsetAsync((char *)c->bam_infl.p + (total & ~3ull), 0, 64 - (total & 3), c->stream));
-    CU(cudaEventRecord(c->bam_ev[0], c->stream));
-    if (int rc = upload(c, c->bam_comp.p, bam.p, bam.n)) return rc;
     if (int rc = upload(c, c->bam_blocks.p, blk.data(), sizeof(BgzfBlock) * blk.size())) return rc;
     if (int rc = upload(c, c->bam_splits.p, splits.data(), 8 * splits.size())) return rc;
     CU(cudaEventRecord(c->bam_ev[1], c->stream));
     unsigned int *ctl = (unsigned int *)c->bam_ctl.p;
     const uint32_t *infl = (const uint32_t *)c->bam_infl.p;
     if (!blk.empty()) {
-        static bool attr_set = false;
-        const int smem = 32 * BZ_TABLE_WORDS * 4;
-        if (!attr_set) { CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
         int sms = 148;
         CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+        // thin warps while the blocks are few (see k_bgzf_inflate): measured best at 12-16 warps per SM (B200: 85 MB / 238 MB / 950 MB
+        // files 2.9x / 2.0x / 1.2x faster than with 32 lanes), then widen
+        long long want_warps = (long long)sms * 20;
+        if (const char *e = getenv("SVTK_BZ_WARPS")) if (*e) want_warps = std::max(1ll, atoll(e));
+        int lanes = 1;
+        while (lanes < 32 && (long long)((blk.size() + lanes - 1) / lanes) > want_warps) lanes <<= 1;
+        const int smem = lanes * BZ_TABLE_WORDS * 4;
+        static int attr_smem = 0;
+        if (smem > attr_smem) { CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * BZ_TABLE_WORDS * 4)); attr_smem = 32 * BZ_TABLE_WORDS * 4; }
         int per_sm = 1;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (blk.size() + 31) / 32);
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (blk.size() + lanes - 1) / lanes);
         k_bgzf_inflate<<<grid, 32, smem, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)blk.size(),
-                                                     (uint8_t *)c->bam_infl.p, ctl);
+                                                     (uint8_t *)c->bam_infl.p, ctl, lanes);
+        if (stats) stats->lanes_per_warp = (uint32_t)lanes;
         CU(cudaGetLastError());
         c->launches += 1;
     }

@@ -229,10 +229,22 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
 // global memory, so a byte-by-byte loop pays one memory round trip per byte (each load may alias the previous store).
 // dist >= 8: groups of up to 8 loads issued together, then their stores.  dist < 8 (runs): the period is read once into a
 // register and replayed.  (Collecting the output in a 64-bit register and storing aligned words was measured slower on
-// B200: the decoder is bound by instruction latency of the few resident warps, not by cache accesses -- DESIGN.md 10.)
+// B200: the decoder is bound by instruction latency of the few resident warps, not by cache accesses -- DESIGN.md 9.)
 BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
     const uint8_t *src = o - dist;
     if (dist >= 8u) {
+        if (len <= 4u) {                                    // the common short match: one group of 4
+            uint8_t t[4];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t i = 0; i < 4u; ++i) if (i < len) t[i] = src[i];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (uint32_t i = 0; i < 4u; ++i) if (i < len) o[i] = t[i];
+            return;
+        }
         for (uint32_t k = 0; k < len; k += 8u) {
             const uint32_t n = len - k < 8u ? len - k : 8u;
             uint8_t t[8];
@@ -251,6 +263,14 @@ BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
         uint32_t ph = 0;
         for (uint32_t k = 0; k < len; ++k) { o[k] = (uint8_t)(pat >> (8u * ph)); ph = ph + 1u == dist ? 0u : ph + 1u; }
     }
+}
+
+// A corrupt stream can keep decoding "symbols" out of whatever follows its payload; the bound is checked once per burst of
+// BZ_BURST steps (a step consumes at most 48 bits), so the compressed buffer must be readable BZ_OVERREAD bytes past its end.
+constexpr int BZ_BURST = 64;
+constexpr int BZ_OVERREAD = 8 * BZ_BURST + 64;
+BZ_HD void bz_check_input(BzLane &z) {
+    if (z.state != BZ_S_IDLE && z.b.ip > z.b.end + 8) bz_fail(z, BZ_ERR_IN);
 }
 
 // one literal/length symbol (and its distance + copy).  Only called in state BZ_S_SYMBOLS.
@@ -281,7 +301,6 @@ BZ_HD void bz_step(BzLane &z, const BzTables &T) {
     else { const int eb = (d >> 1) - 1; dist = 1u + ((2u + (uint32_t)(d & 1)) << eb) + bz_take(b, eb); }
     if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
     if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
-    if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
     bz_copy(z.out + z.op, dist, len);
     z.op += len;
 }
@@ -296,6 +315,7 @@ BZ_HD int bz_inflate(const uint32_t *words, unsigned long long in_beg, unsigned 
     while (z.state != BZ_S_IDLE) {
         if (z.state == BZ_S_HEADER) bz_header(z, T);
         else bz_step(z, T);
+        bz_check_input(z);
     }
     return z.err;
 }

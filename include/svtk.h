@@ -168,6 +168,28 @@ int svtk_bam_ref(const svtk_ctx *ctx, int tid, const char **name, uint32_t *len)
 int svtk_copy_reads(svtk_ctx *ctx, int64_t *n_tid, int64_t *n_reads, int64_t *n_words, int64_t *tid_off, uint32_t *pos, uint32_t *end,
                     uint32_t *n_cigar, uint64_t *cigar_off, uint32_t *cigar);
 
+/* ---- inserted sequences behind the refined insertion breakpoints (no call site in the reference, which never
+ * looks at the bases: refinement.c:299-310 pushes positions only, and abPOA is linked but never called -- SURVEY F5).
+ * For every SVTK_INS window w with refined[w] >= 0 (the result svtk_refine_windows gave for it): every `I` op with
+ * len >= min_len (the reference's signature threshold is 50, refinement.c:299) that refine_ins would have pushed for this
+ * window -- same reads (sam_itr_queryi selection), same walk and stop rule -- and whose reference position lies within
+ * `tol` bases of refined[w] contributes its inserted bases, taken from the 4-bit SEQ of the BAM image svtk_load_bam left in
+ * HBM (bam_get_seq / bam_seqi).  One read set per window that has at least one such op, sequences in file order (read, then
+ * position in the read), in svtk_poa_consensus' layout: pass {n_sets, set_off, seq_off, bases} on as a svtk_poa_batch.
+ * The arrays belong to the ctx and stay valid until the next svtk_ins_sequences / svtk_destroy.  Needs reads loaded with
+ * svtk_load_bam (SVTK_ERR_STATE otherwise).  Reads stored without SEQ (`*`) contribute nothing. */
+typedef struct {
+    int32_t n_sets;
+    int64_t n_seqs;
+    const int64_t *set_off;   /* [n_sets + 1] */
+    const int64_t *seq_off;   /* [n_seqs + 1] */
+    const uint8_t *bases;     /* abPOA codes A0 C1 G2 T3 other 4 */
+    const int32_t *window;    /* [n_sets]  window index of each set */
+    const int32_t *read;      /* [n_seqs]  resident read index of each sequence */
+    const uint32_t *ref_pos;  /* [n_seqs]  reference cursor of the I op (what refine_ins pushed) */
+} svtk_ins_sets;
+int svtk_ins_sequences(svtk_ctx *ctx, const svtk_windows *host_windows, const int32_t *refined, int32_t tol, int32_t min_len, svtk_ins_sets *out);
+
 /* ---- batch seam: N refine_* calls in one go.  result[i] == the reference's return value (-1 == NA). */
 /* host buffers in, host buffer out; H2D + kernels + D2H, synchronous */
 int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *host_windows, int32_t *host_result);

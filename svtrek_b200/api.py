@@ -73,11 +73,16 @@ class BamStats(C.Structure):
                 ("parse_ms", C.c_float), ("total_ms", C.c_float)]
 
 
+class InsSets(C.Structure):
+    _fields_ = [("n_sets", C.c_int32), ("n_seqs", C.c_int64), ("set_off", C.POINTER(C.c_int64)), ("seq_off", C.POINTER(C.c_int64)),
+                ("bases", C.POINTER(C.c_uint8)), ("window", C.POINTER(C.c_int32)), ("read", C.POINTER(C.c_int32)), ("ref_pos", C.POINTER(C.c_uint32))]
+
+
 EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create", "svtk_destroy", "svtk_set_params", "svtk_get_params",
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences"]
 
 _lib = None
 
@@ -120,6 +125,7 @@ def load_library():
     L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
     L.svtk_bam_n_ref.argtypes = [C.c_void_p]
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
+    L.svtk_ins_sequences.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p, C.c_int32, C.c_int32, C.POINTER(InsSets)]
     L.svtk_copy_reads.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)] + [C.c_void_p] * 6
     _lib = L
     return L
@@ -254,6 +260,26 @@ class Auditor:
             _check(self.lib.svtk_bam_ref(self.ctx, t, C.byref(nm), C.byref(ln)))
             out.append((nm.value.decode(), int(ln.value)))
         return out
+
+    def ins_sequences(self, chrom, start, end, pos, kind, refined, tol=5, min_len=50):
+        """svtk_ins_sequences: per INS window with a refined position, the inserted bases of the `I >= min_len` ops within
+        `tol` of it, as read sets in poa_consensus' layout (copies of the ctx-owned arrays)."""
+        chrom = np.ascontiguousarray(chrom, dtype=np.int32)
+        start, end, pos = _u32(start), _u32(end), _u32(pos)
+        kind = np.ascontiguousarray(kind, dtype=np.uint8)
+        refined = np.ascontiguousarray(refined, dtype=np.int32)
+        n = int(chrom.shape[0])
+        w = Windows(n, chrom.ctypes.data, start.ctypes.data, end.ctypes.data, pos.ctypes.data, kind.ctypes.data)
+        o = InsSets()
+        _check(self.lib.svtk_ins_sequences(self.ctx, C.byref(w), refined.ctypes.data, int(tol), int(min_len), C.byref(o)))
+        ns, nq = int(o.n_sets), int(o.n_seqs)
+
+        def arr(ptr, count, dt):
+            return np.ctypeslib.as_array(ptr, shape=(count,)).astype(dt, copy=True) if count else np.zeros(0, dt)
+        seq_off = arr(o.seq_off, nq + 1, np.int64) if nq else np.zeros(1, np.int64)
+        return dict(set_off=arr(o.set_off, ns + 1, np.int64) if ns else np.zeros(1, np.int64), seq_off=seq_off,
+                    bases=arr(o.bases, int(seq_off[-1]), np.uint8), window=arr(o.window, ns, np.int32), read=arr(o.read, nq, np.int32),
+                    ref_pos=arr(o.ref_pos, nq, np.uint32))
 
     def copy_reads(self):
         """The resident read set as host arrays (dict with the svtk_reads field names)."""

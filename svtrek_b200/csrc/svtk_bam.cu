@@ -135,7 +135,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(128) k_bam_walk(const uint32_t *__restrict__ w, const unsigned long long *__restrict__ splits, int n_seg,
                                                   ulonglong2 *__restrict__ seg, unsigned long long *__restrict__ rec_off,
                                                   unsigned long long *__restrict__ cig_src, uint32_t *__restrict__ n_cigar_out,
-                                                  unsigned long long *__restrict__ cigar_off, unsigned int *__restrict__ ctl) {
+                                                  unsigned long long *__restrict__ cigar_off, unsigned long long *__restrict__ seq_src,
+                                                  uint32_t *__restrict__ l_seq_out, unsigned int *__restrict__ ctl) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
     unsigned long long off = splits[s];
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(128) k_bam_walk(const uint32_t *__restrict__ w
             const uint32_t lrn = ld32(w, off + 12) & 255u, w4 = ld32(w, off + 16), l_seq = ld32(w, off + 20);
             uint32_t nc = w4 & 0xffffu;
             unsigned long long src = off + 36ull + lrn;
+            const unsigned long long seq_at = src + 4ull * nc;             // SEQ follows the CIGAR the record stores in place
             const unsigned long long aux = src + 4ull * nc + ((unsigned long long)l_seq + 1) / 2 + l_seq, rend = off + 4ull + bs;
             if (aux > rend) { err = BW_ERR_FIELDS; break; }
             if (nc > 0u && pos >= 0) {
@@ -164,7 +166,7 @@ __global__ void __launch_bounds__(128) k_bam_walk(const uint32_t *__restrict__ w
                     if (k > 0) { nc = (uint32_t)k; src = cg; }
                 }
             }
-            if (FILL) { rec_off[nr] = off; cig_src[nr] = src; n_cigar_out[nr] = nc; cigar_off[nr] = nw; }
+            if (FILL) { rec_off[nr] = off; cig_src[nr] = src; n_cigar_out[nr] = nc; cigar_off[nr] = nw; seq_src[nr] = seq_at; l_seq_out[nr] = l_seq; }
             ++nr; nw += nc;
         }
         off += 4ull + bs;
@@ -507,7 +509,7 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     std::vector<unsigned long long> base(2 * (size_t)std::max(n_seg, 1), 0ull);
     if (n_seg > 0) {
         k_bam_walk<false><<<(n_seg + 127) / 128, 128, 0, c->stream>>>(infl, (const unsigned long long *)c->bam_splits.p, n_seg, (ulonglong2 *)c->bam_seg.p,
-                                                                      nullptr, nullptr, nullptr, nullptr, ctl);
+                                                                      nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, ctl);
         CU(cudaGetLastError());
         c->launches += 1;
     }
@@ -528,14 +530,15 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     if (int rc = c->r_ncig.reserve(4 * std::max<size_t>(nr, 1))) return rc;
     if (int rc = c->r_off.reserve(8 * std::max<size_t>(nr, 1))) return rc;
     if (int rc = c->r_cigar.reserve(4 * nw + 16)) return rc;
-    if (int rc = c->bam_rec.reserve(16 * std::max<size_t>(nr, 1))) return rc;     // [0, nr): record offsets, [nr, 2 nr): CIGAR sources
+    if (int rc = c->bam_rec.reserve(28 * std::max<size_t>(nr, 1))) return rc;     // per read: record offset, CIGAR source, SEQ source (u64 each), l_seq (u32)
     if (int rc = c->tmp_a.reserve(4 * std::max<size_t>(nr, 1))) return rc;        // tid per read
     if (int rc = c->tmp_b.reserve(8 * (size_t)(n_ref + 1))) return rc;
-    unsigned long long *rec_off = (unsigned long long *)c->bam_rec.p, *cig_src = rec_off + nr;
+    unsigned long long *rec_off = (unsigned long long *)c->bam_rec.p, *cig_src = rec_off + nr, *seq_src = cig_src + nr;
+    uint32_t *l_seq = (uint32_t *)(seq_src + nr);
     if (n_reads > 0) {
         if (int rc = upload(c, c->bam_seg.p, base.data(), 16 * (size_t)n_seg)) return rc;
         k_bam_walk<true><<<(n_seg + 127) / 128, 128, 0, c->stream>>>(infl, (const unsigned long long *)c->bam_splits.p, n_seg, (ulonglong2 *)c->bam_seg.p, rec_off,
-                                                                     cig_src, (uint32_t *)c->r_ncig.p, (unsigned long long *)c->r_off.p, ctl);
+                                                                     cig_src, (uint32_t *)c->r_ncig.p, (unsigned long long *)c->r_off.p, seq_src, l_seq, ctl);
         CU(cudaGetLastError());
         const long long threads = n_reads * 32;
         k_bam_extract<<<(unsigned)((threads + 255) / 256), 256, 0, c->stream>>>(infl, rec_off, cig_src, (const uint32_t *)c->r_ncig.p,
@@ -563,6 +566,7 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     d.pos = (const uint32_t *)c->r_pos.p; d.end = (const uint32_t *)c->r_end.p; d.n_cigar = (const uint32_t *)c->r_ncig.p;
     d.cigar_off = (const uint64_t *)c->r_off.p; d.cigar = (const uint32_t *)c->r_cigar.p;
     if (int rc = adopt_device_reads(c, &d)) return rc;
+    c->reads_from_bam = true;
     if (stats) {
         float up = 0, inf = 0, par = 0;
         cudaEventElapsedTime(&up, c->bam_ev[0], c->bam_ev[1]); cudaEventElapsedTime(&inf, c->bam_ev[1], c->bam_ev[2]); cudaEventElapsedTime(&par, c->bam_ev[2], c->bam_ev[3]);

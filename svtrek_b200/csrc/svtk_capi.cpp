@@ -92,6 +92,7 @@ int set_device(Ctx *c) {
 }
 
 static int finish_reads(Ctx *c) {
+    c->reads_from_bam = false;            // svtk_load_bam sets it again after adopting its own arrays
     // planner look-back bound: max(end - pos) over the read set; and the packed-CIGAR contract of svtk_reads
     if (int rc = c->scratch4.reserve(64)) return rc;
     CU(cudaMemsetAsync(c->scratch4.p, 0, 8, c->stream));

@@ -84,6 +84,12 @@ struct Ctx {
     std::vector<uint32_t> bam_ref_lens;
     unsigned long long bam_infl_bytes = 0;
     long long bam_n_rec = 0;
+    bool reads_from_bam = false;          // the resident reads are the records of the resident BAM image (index r == record r)
+    // svtk_ins_sequences (svtk_ins.cu): the last batch of read sets, host side, owned by the ctx
+    std::vector<int64_t> ins_set_off, ins_seq_off;
+    std::vector<uint8_t> ins_bases;
+    std::vector<int32_t> ins_window, ins_read;
+    std::vector<uint32_t> ins_ref_pos;
 
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;

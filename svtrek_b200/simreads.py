@@ -427,10 +427,18 @@ def _bgzf_block(data):
             struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data)))
 
 
-def write_bam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr"):
-    """Coordinate-sorted BAM + `path`.bai of a ReadSet; SEQ / QUAL uniform random like write_sam.  Returns the file size."""
+def write_bam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr", truth=None, ins_err=0.02):
+    """Coordinate-sorted BAM + `path`.bai of a ReadSet; SEQ / QUAL uniform random like write_sam.  With `truth`, the bases
+    under an `I` op that carries a planted insertion (same contig, same length, cursor within 3 bases) are a copy of that
+    insertion's own sequence with substitutions at rate ins_err, so that a consensus over the carriers means something.
+    Returns the file size."""
     import struct
     rng = np.random.default_rng(seed)
+    templates = {}
+    if truth is not None:
+        trng = np.random.default_rng(seed + 1)
+        for k in np.flatnonzero(~truth.is_del):
+            templates.setdefault(int(truth.tid[k]), []).append((int(truth.pos0[k]), int(truth.length[k]), trng.integers(0, 4, int(truth.length[k])).astype(np.uint8)))
     BLOCK = 0xff00
     text = "@HD\tVN:1.6\tSO:coordinate\n" + "".join(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L}\n" for t, L in enumerate(rs.contig_len))
     hdr = b"BAM\1" + struct.pack("<i", len(text)) + text.encode() + struct.pack("<i", rs.n_tid)
@@ -469,6 +477,22 @@ def write_bam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr"):
                 op = w & 15
                 ql = int(((w >> 4)[(op == OP_M) | (op == OP_I) | (op == OP_S) | (op == OP_EQ) | (op == OP_X)]).sum())
                 nib = rng.integers(0, 4, ql + (ql & 1)).astype(np.uint8)
+                if t in templates and bool(((op == OP_I) & ((w >> 4) >= 50)).any()):
+                    cur, q = int(rs.pos[r]), 0
+                    for cw in w:
+                        o, ln = int(cw) & 15, int(cw) >> 4
+                        if o == OP_I and ln >= 50:
+                            for p0, L, tpl in templates[t]:
+                                if L == ln and abs(p0 - cur) <= 3:
+                                    copy = tpl.copy()
+                                    m = rng.random(ln) < ins_err
+                                    copy[m] = (copy[m] + rng.integers(1, 4, int(m.sum()))) & 3
+                                    nib[q:q + ln] = copy
+                                    break
+                        if o not in (OP_I, OP_S):
+                            cur += ln
+                        if o in (OP_M, OP_I, OP_S, OP_EQ, OP_X):
+                            q += ln
                 nib = (1 << nib).astype(np.uint8)                      # A C G T = 1 2 4 8
                 if ql & 1:
                     nib[-1] = 0

@@ -264,3 +264,49 @@ def test_load_bam_from_python_writer_multi_contig(tmp_path):
     res = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
     want_r = B.refine_batch(B.OracleReads(rs3), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
     assert np.array_equal(res, want_r) and int((want_r >= 0).sum()) > 5
+
+
+@pytest.mark.gpu
+def test_ins_sequences_equal_the_restatement_and_feed_the_poa(tmp_path):
+    """svtk_ins_sequences: read sets == the plain-Python restatement on the same BAM; their POA consensus
+    (svtk_poa_consensus) == abPOA's on the same sets and recovers the planted insertion."""
+    from oracle import binding as B
+    from svtrek_b200 import api, simreads as S
+    from tests import util_bam as U
+    rs, truth = S.make_config("c1", scale=0.25)
+    bam = str(tmp_path / "i.bam")
+    S.write_bam(bam, rs, truth=truth)
+    a = api.Auditor(0)
+    a.load_bam(bam)
+    w = S.windows_from_truth(truth)
+    refined = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    got = a.ins_sequences(w["chrom"], w["start"], w["end"], w["pos"], w["kind"], refined, tol=5)
+    rd = U.read_bam(bam)
+    want = U.ins_sequences(rd, w["chrom"], w["start"], w["end"], w["kind"], refined, tol=5)
+    assert len(want) > 20 and len(got["window"]) == len(want)
+    for s, (win, seqs) in enumerate(want):
+        lo, hi = int(got["set_off"][s]), int(got["set_off"][s + 1])
+        assert int(got["window"][s]) == win and hi - lo == len(seqs)
+        for k, (r, rp, codes) in enumerate(seqs):
+            assert int(got["read"][lo + k]) == r and int(got["ref_pos"][lo + k]) == rp
+            assert np.array_equal(got["bases"][int(got["seq_off"][lo + k]):int(got["seq_off"][lo + k + 1])], codes), (win, r)
+    # straight into K3
+    cons, st = a.poa_consensus(got["set_off"], got["seq_off"], got["bases"])
+    assert st["n_sets"] == len(want)
+    ins = np.flatnonzero(~truth.is_del)
+    rec_of_win = w["record"]
+    checked = 0
+    for s, (win, seqs) in enumerate(want):
+        if len(seqs) < 5:
+            continue
+        L = int(truth.length[int(rec_of_win[win])])
+        assert abs(len(cons[s]) - L) <= max(2, L // 50), (win, len(cons[s]), L)
+        if B.have_abpoa() and checked < 6:
+            ref_cons, _ = B.ref_poa_msa([c for _, _, c in seqs])
+            assert np.array_equal(cons[s], ref_cons), win
+            checked += 1
+    assert len(ins) > 0
+    # needs the BAM image: decoded-array loads cannot serve it
+    a.load_reads(rs)
+    with pytest.raises(api.SvtkError):
+        a.ins_sequences(w["chrom"], w["start"], w["end"], w["pos"], w["kind"], refined)

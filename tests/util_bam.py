@@ -78,7 +78,7 @@ def read_bam(path):
         name = data[p + 4:p + 4 + ln].rstrip(b"\0").decode()
         refs.append((name, struct.unpack_from("<i", data, p + 4 + ln)[0]))
         p += 8 + ln
-    tid, pos, end, ncig, cig = [], [], [], [], []
+    tid, pos, end, ncig, cig, seqs = [], [], [], [], [], []
     n_records = 0
     while p < len(data):
         bs, refid, ps, lrn, _mapq, _bin, nc, flag, l_seq = struct.unpack_from("<iiiBBHHHi", data, p)
@@ -93,6 +93,10 @@ def read_bam(path):
             rlen = int((words >> 4)[REF_CONSUMING[words & 15] != 0].sum()) if len(words) else 0
             if (flag & 4) or rlen == 0:
                 rlen = 1
+            packed = np.frombuffer(data, np.uint8, (l_seq + 1) // 2, c0 + 4 * nc)
+            nib = np.empty(2 * len(packed), np.uint8)
+            nib[0::2] = packed >> 4; nib[1::2] = packed & 15              # bam_seqi: high nibble first
+            seqs.append(nib[:l_seq])
             tid.append(refid); pos.append(ps & 0xFFFFFFFF); end.append((ps + rlen) & 0xFFFFFFFF); ncig.append(len(words)); cig.append(words)
         p += 4 + bs
     assert p == len(data)
@@ -101,6 +105,47 @@ def read_bam(path):
     off = np.zeros(len(ncig), np.uint64)
     if len(ncig):
         off[1:] = np.cumsum(ncig[:-1].astype(np.uint64))
-    return dict(refs=refs, n_records=n_records, tid=tid, tid_off=np.searchsorted(tid, np.arange(n_ref + 1)).astype(np.int64),
+    return dict(refs=refs, n_records=n_records, tid=tid, seq=seqs, tid_off=np.searchsorted(tid, np.arange(n_ref + 1)).astype(np.int64),
                 pos=np.asarray(pos, np.uint32), end=np.asarray(end, np.uint32), n_cigar=ncig, cigar_off=off,
                 cigar=np.concatenate(cig).astype(np.uint32) if cig else np.zeros(0, np.uint32))
+
+
+NIB2CODE = np.full(16, 4, np.uint8)
+NIB2CODE[[1, 2, 4, 8]] = [0, 1, 2, 3]                                     # =ACMGRSVTWYHKDBN -> abPOA's A0 C1 G2 T3 other 4
+
+
+def ins_sequences(rd, chrom, start, end, kind, refined, tol=5, min_len=50):
+    """Restatement of svtk_ins_sequences on read_bam() output: per INS window with refined >= 0, the inserted bases of the
+    `I >= min_len` ops refine_ins would push (selection hts.c:3913-3916; walk + stop rule refinement.c:299-318) within tol of the
+    refined position.  Returns [(window, [(read, ref_pos, codes)])] for windows with at least one sequence."""
+    out = []
+    for w in range(len(chrom)):
+        if int(kind[w]) != 2 or int(refined[w]) < 0:
+            continue
+        ws, we = int(start[w]) & 0xFFFFFFFF, int(end[w]) & 0xFFFFFFFF
+        t = int(chrom[w]) - 1
+        beg, endq = (ws - 1) & 0xFFFFFFFF, (we - 1) & 0xFFFFFFFF
+        if t < 0 or t >= len(rd["tid_off"]) - 1 or endq < beg:
+            continue
+        got = []
+        for r in range(int(rd["tid_off"][t]), int(rd["tid_off"][t + 1])):
+            p = int(rd["pos"][r])
+            if p >= endq:
+                break
+            if not int(rd["end"][r]) > beg:
+                continue
+            cur, q = p, 0
+            o = int(rd["cigar_off"][r])
+            for cw in rd["cigar"][o:o + int(rd["n_cigar"][r])]:
+                op, ln = int(cw) & 15, int(cw) >> 4
+                if op == 1 and ln >= min_len and abs(cur - int(refined[w])) <= tol and q + ln <= len(rd["seq"][r]):
+                    got.append((r, cur, NIB2CODE[rd["seq"][r][q:q + ln]]))
+                if op not in (1, 4):
+                    cur += ln
+                if op in (0, 1, 4, 7, 8):
+                    q += ln
+                if cur > we:
+                    break
+        if got:
+            out.append((w, got))
+    return out

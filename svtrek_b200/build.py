@@ -22,6 +22,10 @@ def nvcc() -> str:
     raise RuntimeError("nvcc not found")
 
 
+CLI = os.path.join(HERE, "svtrek_gpu")          # the C host driver (csrc/svtrek_gpu.c): `svtrek audt` over the C ABI
+CLI_SRC = os.path.join(CSRC, "svtrek_gpu.c")
+
+
 def stale() -> bool:
     if not os.path.exists(LIB):
         return True
@@ -29,8 +33,21 @@ def stale() -> bool:
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
+def build_cli() -> str:
+    """gcc: the driver links libsvtk_b200.so next to it (rpath $ORIGIN)."""
+    if os.path.exists(CLI) and os.path.getmtime(CLI) >= max(os.path.getmtime(CLI_SRC), os.path.getmtime(os.path.join(HERE, "libsvtk_b200.so"))):
+        return CLI
+    cmd = ["gcc", "-O2", "-std=c99", "-D_GNU_SOURCE", "-Wall", "-o", CLI, CLI_SRC, "-L" + HERE, "-lsvtk_b200", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("gcc failed:\n" + r.stdout + r.stderr)
+    return CLI
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
+        if LIB == os.path.join(HERE, "libsvtk_b200.so"):
+            build_cli()
         return LIB
     cmd = [nvcc(), *NVCC_FLAGS, *os.environ.get("SVTK_NVCC_EXTRA", "").split(), "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
     if verbose:
@@ -40,6 +57,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
+    if LIB == os.path.join(HERE, "libsvtk_b200.so"):
+        build_cli()
     return LIB
 
 

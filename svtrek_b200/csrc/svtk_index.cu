@@ -36,7 +36,10 @@ namespace svtk {
 
 constexpr int EV_DEL = 0, EV_INS = 1, EV_TCLIP = 2, EV_LCLIP = 3;
 
-constexpr int IDX_WARPS = 4;                // warps (= chunks) per CTA of k_index_reads
+#ifndef SVTK_IDX_WARPS
+#define SVTK_IDX_WARPS 4
+#endif
+constexpr int IDX_WARPS = SVTK_IDX_WARPS;    // warps (= chunks) per CTA of k_index_reads
 #ifndef SVTK_IDX_WPT
 #define SVTK_IDX_WPT 8
 #endif

@@ -6,7 +6,8 @@
  * messages for malformed VCF lines.  Differences, all deliberate: every record is printed, in VCF order (the reference drops
  * up to 2 x t queued lines at end of file and interleaves output at -t > 1: SURVEY F2/F3) -- i.e. the output of
  * `svtrek audt -t 1` on a VCF padded past the tail drop; -t is accepted and ignored (the GPU replaces the thread pool);
- * -o is accepted and, like in the reference, not written to (audit.c prints to stdout only: SURVEY F1).
+ * -o, when given, receives a copy of the record lines in addition to stdout (the reference accepts -o and never writes to
+ * it -- SURVEY F1; the additional sink is SURVEY 8f-3's reading of the option).
  * Extra options: --device N (default 0), --stats (loader counters on stderr).  `disc` mode is not part of this path. */
 #include <getopt.h>
 #include <stdio.h>
@@ -40,7 +41,7 @@ static void need_file(const char *name, const char *missing) {
 }
 
 int main(int argc, char *argv[]) {
-    const char *bam = NULL, *vcf = NULL, *out = "svtrek.out";
+    const char *bam = NULL, *vcf = NULL, *out = NULL;
     svtk_params p = {20000, 10000, 2000, 500, 5, 3};
     int device = 0, stats = 0, verbose = 0, opt, li, threads = 4;
     static struct option lo[] = {
@@ -77,7 +78,7 @@ int main(int argc, char *argv[]) {
                 return EXIT_FAILURE;
         }
     }
-    (void)out; (void)verbose; (void)threads;
+    (void)verbose; (void)threads;
     need_file(bam, "[ERROR] BAM file is not provided.");
     need_file(vcf, "[ERROR] VCF file is not provided.");
 
@@ -94,8 +95,14 @@ int main(int argc, char *argv[]) {
                         "records %.2f ms, total %.1f ms\n", bam, st.file_bytes / 1e6, (unsigned long long)st.n_blocks, st.inflated_bytes / 1e6,
                 (unsigned long long)st.n_reads, (unsigned long long)st.n_words, st.upload_ms, st.inflate_ms, st.parse_ms, st.total_ms);
     int64_t n = 0;
-    int rc = svtk_process_vcf(ctx, vcf, NULL, &n);
+    int rc = svtk_process_vcf(ctx, vcf, out, &n);            /* out == NULL: stdout */
     if (rc != 0) fprintf(stderr, "[ERROR] %s\n", svtk_last_error());
+    if (out && rc == 0) {                                    /* -o is an additional sink: the lines still go to stdout */
+        FILE *f = fopen(out, "r");
+        char buf[1 << 16];
+        size_t k;
+        if (f) { while ((k = fread(buf, 1, sizeof buf, f)) > 0) fwrite(buf, 1, k, stdout); fclose(f); }
+    }
     if (stats) fprintf(stderr, "[svtrek_gpu] %lld records\n", (long long)n);
     svtk_destroy(ctx);
     return 0;                                               /* the reference's exit status is 0 whatever happened (svtrek.c:15-21) */

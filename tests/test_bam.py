@@ -310,3 +310,40 @@ def test_ins_sequences_equal_the_restatement_and_feed_the_poa(tmp_path):
     a.load_reads(rs)
     with pytest.raises(api.SvtkError):
         a.ins_sequences(w["chrom"], w["start"], w["end"], w["pos"], w["kind"], refined)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["empty", "ont", "contigs24", "deep"])
+def test_load_bam_shapes(tmp_path, case):
+    """header-only file; ONT-like reads (1-3 k CIGAR words each); 24 references, some without reads; a 200x pile-up (long record
+    chains between two index offsets).  Loader == written reads, refinement == oracle."""
+    from oracle import binding as B
+    from svtrek_b200 import api, simreads as S
+    if case == "empty":
+        rs = S.ReadSet(tid_off=np.zeros(3, np.int64), pos=np.zeros(0, np.uint32), end=np.zeros(0, np.uint32), n_cigar=np.zeros(0, np.uint32),
+                       cigar_off=np.zeros(1, np.uint64), cigar=np.zeros(0, np.uint32), contig_len=[1000, 2000])
+        truth = None
+    elif case == "ont":
+        rs, truth = S.simulate(3, contig_lens=[300_000], coverage=20, read_len=15000, small_rate=0.08, n_sv=40, sv_kind="ins", min_len=50, max_len=3000,
+                               log_uniform=True, min_gap=1500)
+    elif case == "contigs24":
+        rs, truth = S.simulate(4, contig_lens=[250_000 if t % 5 else 200_000 for t in range(24)], coverage=4, read_len=8000, small_rate=0.01, n_sv=120, min_gap=1500)
+    else:
+        rs, truth = S.simulate(5, contig_lens=[250_000], coverage=200, read_len=5000, small_rate=0.005, n_sv=30, min_gap=1500)
+    bam = str(tmp_path / "x.bam")
+    S.write_bam(bam, rs, truth=truth)
+    a = api.Auditor(0)
+    st = a.load_bam(bam)
+    got = a.copy_reads()
+    want = dict(tid_off=rs.tid_off, pos=rs.pos, end=rs.end, n_cigar=rs.n_cigar, cigar_off=rs.cigar_off[:-1], cigar=rs.cigar)
+    for k in FIELDS:
+        assert np.array_equal(got[k].astype(np.int64), np.asarray(want[k]).astype(np.int64)), (case, k)
+    assert st["n_reads"] == rs.n_reads
+    if truth is None:
+        assert a.refine_windows([1], [100], [900], [500], [2])[0] == -1
+        return
+    if case == "ont":
+        assert int(rs.n_cigar.max()) > 1000
+    w = S.windows_from_truth(truth)
+    res = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    assert np.array_equal(res, B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])), case

@@ -38,5 +38,9 @@ def test_cli_stdout_equals_the_reference_binary(tmp_path, extra):
     ref_out, _ = B.run_ref_cli(bam, vcf, threads=1, extra=extra)
     p = subprocess.run([CLI, "audt", "-b", bam, "-v", vcf, "-t", "1", *extra], stdout=subprocess.PIPE, stderr=subprocess.PIPE, check=True)
     assert p.stdout.decode() == ref_out
+    if not extra:                                            # -o: the same lines in the file as well
+        o = str(tmp_path / "lines.out")
+        p2 = subprocess.run([CLI, "audt", "-b", bam, "-v", vcf, "-o", o], stdout=subprocess.PIPE, stderr=subprocess.PIPE, check=True)
+        assert p2.stdout.decode() == ref_out and open(o).read() == ref_out
     n = ref_out.count("(DEL) ") + ref_out.count("(INS) ")
     assert n >= 100 and ref_out.startswith("[INFO] Started") and "NA" in ref_out or n >= 100

@@ -150,7 +150,7 @@ int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *dev_reads);
  * record chain is cut at the record-aligned offsets the .bai holds, and pos / endpos / CIGAR are extracted into the same
  * arrays svtk_load_reads fills.  Every record with refID >= 0 becomes a read (no FLAG / MAPQ filter, like the reference).
  * bai_path NULL: "<bam_path>.bai", else "<bam_path minus .bam>.bai".  Errors (SVTK_ERR_IO): unreadable / corrupt file,
- * stale index, records out of coordinate order.  BGZF CRC32 footers are not verified. */
+ * stale index, records out of coordinate order, CRC32 mismatch of a block (checked on the GPU, like bgzf.c:776). */
 typedef struct {
     uint64_t file_bytes, n_blocks, inflated_bytes;
     uint64_t n_reads, n_words;

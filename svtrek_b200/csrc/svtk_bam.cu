@@ -43,7 +43,7 @@ struct BgzfBlock {
     uint32_t in_len, isize;
 };
 
-enum { BAM_CTL_NEXT = 0, BAM_CTL_ZERR = 1, BAM_CTL_ZCODE = 2, BAM_CTL_WERR = 4, BAM_CTL_WSEG = 5, BAM_CTL_ORDER = 6, BAM_CTL_WORDS = 8 };
+enum { BAM_CTL_NEXT = 0, BAM_CTL_ZERR = 1, BAM_CTL_ZCODE = 2, BAM_CTL_WERR = 4, BAM_CTL_WSEG = 5, BAM_CTL_ORDER = 6, BAM_CTL_CRC = 7 };
 enum { BW_OK = 0, BW_ERR_SHORT = 1, BW_ERR_SIZE = 2, BW_ERR_FIELDS = 3, BW_ERR_AUX = 4, BW_ERR_END = 5 };
 
 constexpr unsigned FULLMASK = 0xffffffffu;
@@ -82,6 +82,39 @@ __global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_
         for (int it = 0; it < BZ_BURST; ++it)
             if (z.state == BZ_S_SYMBOLS) bz_step(z, T);
         bz_check_input(z);
+    }
+}
+
+// CRC-32 of every block's inflated bytes against its gzip footer (HTSlib: bgzf.c:776-780 "CRC32 checksum mismatch").  One warp
+// per block, 32 slices, merged with the x^(8n) identity (svtk_bgzf_core.cuh); word loads once a lane's slice is aligned.
+__global__ void __launch_bounds__(256) k_bgzf_crc(const uint32_t *__restrict__ comp, const BgzfBlock *__restrict__ blk, unsigned n_blocks,
+                                                  const uint8_t *__restrict__ infl, unsigned int *__restrict__ ctl) {
+    __shared__ uint32_t tab[256];
+    tab[threadIdx.x] = bz_crc_table_entry(threadIdx.x);
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31u, warps = gridDim.x * (blockDim.x >> 5);
+    for (unsigned b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < n_blocks; b += warps) {
+        const BgzfBlock k = blk[b];
+        const uint32_t n = k.isize, per = ((n + 31u) / 32u + 3u) & ~3u;
+        const unsigned long long s0 = (unsigned long long)lane * per;
+        const uint32_t len = s0 >= n ? 0u : min(per, n - (uint32_t)s0);
+        const uint8_t *p = infl + k.out_off + s0;
+        uint32_t c = 0xffffffffu, i = 0;
+        for (; i < len && ((uintptr_t)(p + i) & 3u); ++i) c = tab[(c ^ p[i]) & 255u] ^ (c >> 8);
+        for (; i + 4u <= len; i += 4u) {
+            uint32_t w = *reinterpret_cast<const uint32_t *>(p + i);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { c = tab[(c ^ w) & 255u] ^ (c >> 8); w >>= 8; }
+        }
+        for (; i < len; ++i) c = tab[(c ^ p[i]) & 255u] ^ (c >> 8);
+        uint32_t share = (len > 0u || lane == 0u) ? bz_crc_share(c ^ 0xffffffffu, lane, per, n) : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) share ^= __shfl_xor_sync(FULLMASK, share, d);
+        if (lane == 0u) {
+            const unsigned long long f = k.in_beg + k.in_len;                  // gzip footer: CRC32, ISIZE
+            const uint32_t want = bz_byte(comp, f) | bz_byte(comp, f + 1) << 8 | bz_byte(comp, f + 2) << 16 | bz_byte(comp, f + 3) << 24;
+            if (share != want) atomicCAS(&ctl[BAM_CTL_CRC], 0u, b + 1u);
+        }
     }
 }
 
@@ -502,6 +535,15 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
         c->launches += 1;
     }
     CU(cudaEventRecord(c->bam_ev[2], c->stream));
+    if (!blk.empty()) {
+        int sms = 148;
+        CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * 8, (blk.size() + 7) / 8);
+        k_bgzf_crc<<<grid, 256, 0, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)blk.size(),
+                                              (const uint8_t *)c->bam_infl.p, ctl);
+        CU(cudaGetLastError());
+        c->launches += 1;
+    }
 
     // ---- record chain: count, prefix (host: a few thousand pieces), fill
     unsigned int *hctl = (unsigned int *)c->bam_h.p;
@@ -516,6 +558,7 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     CU(cudaMemcpyAsync(hctl, ctl, 64, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (hctl[BAM_CTL_ZERR]) return fail(SVTK_ERR_IO, "bam: BGZF block %u does not inflate (code %u)", hctl[BAM_CTL_ZERR] - 1, hctl[BAM_CTL_ZCODE]);
+    if (hctl[BAM_CTL_CRC]) return fail(SVTK_ERR_IO, "bam: CRC32 checksum mismatch in BGZF block %u", hctl[BAM_CTL_CRC] - 1);
     if (hctl[BAM_CTL_WERR]) return fail(SVTK_ERR_IO, "bam: record chain broken in piece %u of %d (code %u): corrupt BAM or stale index", hctl[BAM_CTL_WSEG], n_seg, hctl[BAM_CTL_WERR]);
     if (n_seg > 0) {
         CU(cudaMemcpyAsync(c->bam_h.p, c->bam_seg.p, 16 * (size_t)n_seg, cudaMemcpyDeviceToHost, c->stream));

@@ -321,3 +321,56 @@ BZ_HD int bz_inflate(const uint32_t *words, unsigned long long in_beg, unsigned 
 }
 
 }  // namespace svtk
+
+// ---- CRC-32 of a block's inflated bytes (gzip footer, RFC 1952; HTSlib verifies it for every block it inflates,
+// bgzf.c:776-780).  The bytes are cut into up to 32 slices, one per lane; every lane runs the table-driven byte loop on its
+// slice, and the slice CRCs are merged with the identity zlib's crc32_combine rests on: appending n bytes to a message
+// multiplies its CRC by x^(8n) modulo the CRC polynomial, so crc(A || B) = crc(A) * x^(8|B|) xor crc(B) (zlib 1.2.12+
+// crc32.c: multmodp / x2nmodp; restated here, reflected polynomial 0xEDB88320).
+namespace svtk {
+
+constexpr uint32_t BZ_CRC_POLY = 0xedb88320u;
+
+BZ_HD uint32_t bz_crc_table_entry(uint32_t i) {             // the classic 256-entry table, one entry
+    uint32_t c = i;
+    for (int k = 0; k < 8; ++k) c = (c & 1u) ? (c >> 1) ^ BZ_CRC_POLY : c >> 1;
+    return c;
+}
+
+BZ_HD uint32_t bz_crc_bytes(const uint32_t *tab, const uint8_t *p, uint32_t n) {   // standard CRC-32 of n bytes (init / final xor included)
+    uint32_t c = 0xffffffffu;
+    for (uint32_t i = 0; i < n; ++i) c = tab[(c ^ p[i]) & 255u] ^ (c >> 8);
+    return c ^ 0xffffffffu;
+}
+
+BZ_HD uint32_t bz_crc_multmodp(uint32_t a, uint32_t b) {    // a(x) * b(x) mod p(x), bit 31 = x^0 (reflected)
+    uint32_t m = 1u << 31, p = 0;
+    for (;;) {
+        if (a & m) { p ^= b; if ((a & (m - 1u)) == 0u) break; }
+        m >>= 1;
+        b = (b & 1u) ? (b >> 1) ^ BZ_CRC_POLY : b >> 1;
+    }
+    return p;
+}
+
+BZ_HD uint32_t bz_crc_x8n(uint32_t n) {                     // x^(8 n) mod p(x): square-and-multiply over the bits of n
+    uint32_t sq = bz_crc_multmodp(1u << 30, 1u << 30);      // x^2
+    sq = bz_crc_multmodp(sq, sq); sq = bz_crc_multmodp(sq, sq);   // x^8
+    uint32_t p = 1u << 31;                                  // x^0
+    while (n) {
+        if (n & 1u) p = bz_crc_multmodp(sq, p);
+        n >>= 1;
+        if (n) sq = bz_crc_multmodp(sq, sq);
+    }
+    return p;
+}
+
+// CRC of `n` bytes from the CRCs of its slices: slice s covers bytes [s * per, min(n, (s + 1) * per)); this is lane s's share
+// (XOR the shares of all slices to get the CRC of the whole)
+BZ_HD uint32_t bz_crc_share(uint32_t slice_crc, uint32_t s, uint32_t per, uint32_t n) {
+    const unsigned long long endb = (unsigned long long)(s + 1u) * per;
+    const uint32_t after = endb >= n ? 0u : n - (uint32_t)endb;
+    return after ? bz_crc_multmodp(bz_crc_x8n(after), slice_crc) : slice_crc;
+}
+
+}  // namespace svtk

@@ -11,3 +11,18 @@ extern "C" int hostsim_inflate(const uint8_t *comp, long long n, long long in_be
     T.lit = lit; T.dist = dist;
     return svtk::bz_inflate(w.data(), (unsigned long long)in_beg, (unsigned long long)in_end, out, out_len, T);
 }
+
+// CRC-32 of data[0..n) computed the way the kernel does: `slices` slice CRCs merged with the x^(8n) identity
+extern "C" unsigned hostsim_crc32(const uint8_t *data, unsigned n, unsigned slices) {
+    uint32_t tab[256];
+    for (uint32_t i = 0; i < 256; ++i) tab[i] = svtk::bz_crc_table_entry(i);
+    const unsigned per = (n + slices - 1) / slices;
+    uint32_t crc = 0;
+    for (unsigned s = 0; s < slices; ++s) {
+        const unsigned long long b = (unsigned long long)s * per;
+        const unsigned len = b >= n ? 0u : (n - (unsigned)b < per ? n - (unsigned)b : per);
+        if (len == 0 && s > 0) continue;                 // empty slices contribute nothing (an all-empty message: slice 0 gives 0)
+        crc ^= svtk::bz_crc_share(svtk::bz_crc_bytes(tab, data + b, len), s, per, n);
+    }
+    return crc;
+}

@@ -104,6 +104,17 @@ def test_decoder_rejects_or_matches_zlib_on_corrupt_streams(hostsim):
     assert run_inflate(hostsim, comp[:len(comp) // 2], len(data))[0] != 0
 
 
+def test_sliced_crc32_equals_zlib(hostsim):
+    """the CRC the loader checks every block with: per-slice CRCs merged by the x^(8n) identity == zlib.crc32"""
+    hostsim.hostsim_crc32.argtypes = [C.c_void_p, C.c_uint, C.c_uint]
+    hostsim.hostsim_crc32.restype = C.c_uint
+    rng = np.random.default_rng(0)
+    for n in (0, 1, 2, 31, 32, 33, 100, 255, 4096, 12345, 65280, 65535, 65536):
+        d = rng.integers(0, 256, max(n, 1), dtype=np.uint8)
+        for slices in (1, 2, 7, 32):
+            assert hostsim.hostsim_crc32(d.ctypes.data, n, slices) == zlib.crc32(d[:n].tobytes()) & 0xFFFFFFFF, (n, slices)
+
+
 # ---- golden BAM written by the reference's HTSlib (tools/make_bam_golden.py)
 GOLD_BAM = os.path.join(ROOT, "tests", "golden", "bam_small.bam")
 GOLD_NPZ = os.path.join(ROOT, "tests", "golden", "bam_small.npz")
@@ -183,6 +194,26 @@ def test_load_bam_errors(tmp_path):
     assert struct.unpack_from("<i", bai, 8)[0] > 0 and struct.unpack_from("<i", bai, 16)[0] > 0       # ref 0 has a bin with a chunk at byte 20
     attempt("stale1.bam", buf, index=bai[:20] + struct.pack("<Q", 12345 << 16) + bai[28:])          # chunk start inside no block
     attempt("stale2.bam", buf, index=bai[:20] + struct.pack("<Q", off << 16 | 7) + bai[28:])        # a real block, but not a record boundary
+    # a flip that still inflates to the right length (raw DEFLATE has no checksum): only the block's CRC32 catches it
+    rng = np.random.default_rng(5)
+    off, p, n, isize = U.bgzf_blocks(bytes(buf))[5]
+    good = zlib.decompress(bytes(buf[p:p + n]), -15)
+    for _ in range(4000):
+        c2 = bytearray(buf)
+        c2[p + int(rng.integers(n // 4, n))] ^= 1 << int(rng.integers(0, 8))
+        try:
+            d = zlib.decompressobj(-15)
+            alt = d.decompress(bytes(c2[p:p + n]))
+            if d.eof and len(alt) == isize and alt != good and not d.unused_data:
+                break
+        except zlib.error:
+            pass
+    else:
+        pytest.fail("no silent flip found")
+    (tmp_path / "crc.bam").write_bytes(bytes(c2))
+    (tmp_path / "crc.bam.bai").write_bytes(bai)
+    with pytest.raises(api.SvtkError, match="CRC32"):
+        a.load_bam(str(tmp_path / "crc.bam"))
     with pytest.raises(api.SvtkError):
         a.load_bam(str(tmp_path / "does_not_exist.bam"))
     # the ctx is still usable afterwards

@@ -351,13 +351,14 @@ def run_ours(args):
 
     def step_device():
         a.index_reads()                      # the whole job every step: one pass over every CIGAR word ...
-        a.refine_windows_device(*wargs, d_res.data_ptr())   # ... then every window
-        a.sync()
+        a.refine_windows_device(*wargs, d_res.data_ptr())   # ... then every window (asynchronous on the ctx stream)
 
     with torch.cuda.stream(stream):
         for _ in range(W):
             flush.zero_()
             step_device()
+            a.sync()
+    overflow_work = int(stats["n_overflow"]) != 0 or int(walker["n_overflow"]) != 0
     sampler = NvmlSampler(local)
     barrier()
     sampler.start()
@@ -371,7 +372,10 @@ def run_ours(args):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
             step_device()
-            e1.record(stream)
+            if overflow_work:
+                a.sync()                     # windows beyond the fast path are finished by svtk_sync: that work belongs to the step
+            e1.record(stream)                # closes the step's device work; the host-side wait comes after it
+            a.sync()
             evs.append((e0, e1))
     barrier()
     t_wall = time.perf_counter() - t_wall0

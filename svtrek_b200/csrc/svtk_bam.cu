@@ -443,6 +443,7 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     Mapped bam;
     if (bam.open_file(bam_path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open %s", bam_path);
     if (bam.n == 0) return fail(SVTK_ERR_IO, "bam: %s is empty", bam_path);
+    if (bam.n >= (1ull << 34) - 65536) return fail(SVTK_ERR_ARG, "bam: files of 16 GiB and more must be sharded by region (32-bit word index in the decoder)");
     // the table work runs on a helper thread while this thread feeds the upload ring (both only read the mapping)
     std::vector<BgzfBlock> blk;
     std::vector<uint64_t> coff;

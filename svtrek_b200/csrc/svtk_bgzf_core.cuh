@@ -48,7 +48,8 @@ constexpr int BZ_TABLE_WORDS = (((1 << BZ_LBITS) + (1 << BZ_DBITS)) / 2) | 1;   
 
 struct BzBits {
     const uint32_t *w;                    // compressed buffer, 4-byte aligned, readable 8 bytes past the last block
-    unsigned long long ip, end;           // byte offsets: next unread byte, end of this block's DEFLATE payload
+    unsigned long long end;               // byte offset of the end of this block's DEFLATE payload
+    uint32_t wi;                          // index of the word held in nxt: everything before it is in buf or consumed (files < 16 GiB)
     unsigned long long buf;
     int cnt;
     uint32_t nxt;                         // the word at ip, loaded one refill ahead
@@ -69,11 +70,13 @@ BZ_HD uint32_t bz_byte(const uint32_t *w, unsigned long long off) { return (w[of
 // the warp 32 cache accesses, so halving the loads matters more than the shift it costs)
 BZ_HD void bz_prime(BzBits &b, unsigned long long pos) {      // start reading bits at byte offset pos
     const uint32_t drop = (uint32_t)(pos & 3) * 8u;
-    b.buf = (unsigned long long)(b.w[pos >> 2] >> drop); b.cnt = 32 - (int)drop; b.ip = (pos & ~3ull) + 4;
-    b.nxt = b.w[b.ip >> 2];
+    b.wi = (uint32_t)(pos >> 2) + 1u;
+    b.buf = (unsigned long long)(b.w[b.wi - 1u] >> drop); b.cnt = 32 - (int)drop;
+    b.nxt = b.w[b.wi];
 }
+BZ_HD unsigned long long bz_ip(const BzBits &b) { return (unsigned long long)b.wi * 4ull; }   // byte offset of the first byte not yet in buf
 BZ_HD void bz_refill(BzBits &b) {         // afterwards cnt >= 32; the load issued here is consumed by the NEXT refill
-    if (b.cnt < 32) { b.buf |= (unsigned long long)b.nxt << b.cnt; b.ip += 4; b.cnt += 32; b.nxt = b.w[b.ip >> 2]; }
+    if (b.cnt < 32) { b.buf |= (unsigned long long)b.nxt << b.cnt; b.cnt += 32; b.nxt = b.w[++b.wi]; }
 }
 BZ_HD uint32_t bz_take(BzBits &b, int n) {   // n <= 16, cnt >= n
     const uint32_t v = (uint32_t)b.buf & ((1u << n) - 1u);
@@ -159,7 +162,7 @@ BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg,
 BZ_HD void bz_fail(BzLane &z, int e) { z.err = e; z.state = BZ_S_IDLE; }
 
 BZ_HD void bz_finish(BzLane &z) {        // after the final block
-    if (z.b.ip - (unsigned long long)(z.b.cnt >> 3) > z.b.end) z.err = BZ_ERR_IN;
+    if (bz_ip(z.b) - (unsigned long long)(z.b.cnt >> 3) > z.b.end) z.err = BZ_ERR_IN;
     else if (z.op != z.out_len) z.err = BZ_ERR_SIZE;
     z.state = BZ_S_IDLE;
 }
@@ -167,14 +170,14 @@ BZ_HD void bz_finish(BzLane &z) {        // after the final block
 // one DEFLATE block header: stored blocks are copied here; for Huffman blocks the lane's tables are (re)built
 BZ_HD void bz_header(BzLane &z, BzTables &T) {
     BzBits &b = z.b;
-    if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
+    if (bz_ip(b) > b.end + 8) return bz_fail(z, BZ_ERR_IN);
     bz_refill(b);
     z.last = (int)bz_take(b, 1);
     const uint32_t type = bz_take(b, 2);
     if (type == 3) return bz_fail(z, BZ_ERR_BTYPE);
     if (type == 0) {                                                       // stored: byte align, LEN, ~LEN, bytes
         bz_take(b, b.cnt & 7);
-        unsigned long long ip = b.ip - (unsigned long long)(b.cnt >> 3);   // hand the whole bytes back
+        unsigned long long ip = bz_ip(b) - (unsigned long long)(b.cnt >> 3);   // hand the whole bytes back
         if (ip + 4 > b.end) return bz_fail(z, BZ_ERR_STORED);
         const uint32_t len = bz_byte(b.w, ip) | bz_byte(b.w, ip + 1) << 8;
         const uint32_t nlen = bz_byte(b.w, ip + 2) | bz_byte(b.w, ip + 3) << 8;
@@ -218,7 +221,7 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
             while (rep--) lens[n++] = (uint8_t)val;
         }
         if (lens[256] == 0) return bz_fail(z, BZ_ERR_LENS);                // no end-of-block code
-        if (b.ip > b.end + 8) return bz_fail(z, BZ_ERR_IN);
+        if (bz_ip(b) > b.end + 8) return bz_fail(z, BZ_ERR_IN);
     }
     if (bz_build(lens, hlit, T.lcnt, T.lsym, T.lit, BZ_LBITS, &T.lresume)) return bz_fail(z, BZ_ERR_LENS);
     if (bz_build(lens + hlit, hdist, T.dcnt, T.dsym, T.dist, BZ_DBITS, &T.dresume)) return bz_fail(z, BZ_ERR_LENS);
@@ -233,6 +236,7 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
 BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
     const uint8_t *src = o - dist;
     if (dist >= 8u) {
+#ifndef SVTK_BZ_NOSHORT
         if (len <= 4u) {                                    // the common short match: one group of 4
             uint8_t t[4];
 #if defined(__CUDA_ARCH__)
@@ -245,6 +249,7 @@ BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
             for (uint32_t i = 0; i < 4u; ++i) if (i < len) o[i] = t[i];
             return;
         }
+#endif
         for (uint32_t k = 0; k < len; k += 8u) {
             const uint32_t n = len - k < 8u ? len - k : 8u;
             uint8_t t[8];
@@ -270,7 +275,7 @@ BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
 constexpr int BZ_BURST = 64;
 constexpr int BZ_OVERREAD = 8 * BZ_BURST + 64;
 BZ_HD void bz_check_input(BzLane &z) {
-    if (z.state != BZ_S_IDLE && z.b.ip > z.b.end + 8) bz_fail(z, BZ_ERR_IN);
+    if (z.state != BZ_S_IDLE && bz_ip(z.b) > z.b.end + 8) bz_fail(z, BZ_ERR_IN);
 }
 
 // one literal/length symbol (and its distance + copy).  Only called in state BZ_S_SYMBOLS.

@@ -236,6 +236,13 @@ int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int w
  * reference's end-of-file tail drop, audit.c:35-41,342, is not reproduced).  *n_records (may be NULL)
  * receives the number of (INS)/(DEL)/(INV) lines written. */
 int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records);
+/* The same, plus the side file the north star's "abPOA for insertion consensus" needs (the reference's stdout has no slot for a
+ * sequence): for every INS record whose refinement gave a position and that has carrier reads, one FASTA entry
+ *   >INS chr=<chrom> org_pos=<VCF pos> ref_pos=<refined> reads=<carriers> len=<bases>
+ * holding the POA consensus (svtk_poa_consensus == abpoa_msa defaults) of the inserted sequences svtk_ins_sequences finds
+ * within tol bases of the refined position (tol < 0: the ctx's consensus_interval).  Needs reads loaded with svtk_load_bam. */
+int svtk_process_vcf_ins(svtk_ctx *ctx, const char *vcf_path, const char *out_path, const char *fasta_path, int32_t tol, int64_t *n_records,
+                         int64_t *n_consensus);
 
 /* ---- K3: insertion consensus (partial-order alignment).  SVTrek builds abPOA but never calls it (no
  * source includes abpoa.h, Makefile:32-33), so this entry has no call site in audit.c; it replaces what the

@@ -82,7 +82,7 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins"]
 
 _lib = None
 
@@ -125,6 +125,7 @@ def load_library():
     L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
     L.svtk_bam_n_ref.argtypes = [C.c_void_p]
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
+    L.svtk_process_vcf_ins.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.svtk_ins_sequences.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p, C.c_int32, C.c_int32, C.POINTER(InsSets)]
     L.svtk_copy_reads.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)] + [C.c_void_p] * 6
     _lib = L
@@ -388,6 +389,13 @@ class Auditor:
         return tuple(res)
 
     # ---- whole path (audit.c:250 process_vcf)
+    def process_vcf_ins(self, vcf_path, out_path, fasta_path, tol=-1):
+        """process_vcf + a FASTA side file with the POA consensus of every refined INS record; returns (records, consensuses)."""
+        n, k = C.c_int64(0), C.c_int64(0)
+        _check(self.lib.svtk_process_vcf_ins(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, fasta_path.encode(), int(tol),
+                                             C.byref(n), C.byref(k)))
+        return n.value, k.value
+
     def process_vcf(self, vcf_path, out_path):
         n = C.c_int64(0)
         _check(self.lib.svtk_process_vcf(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, C.byref(n)))

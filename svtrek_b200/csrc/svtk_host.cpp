@@ -5,6 +5,7 @@
 #include "../../include/svtk.h"
 #include "svtk_ctx.h"
 
+#include <algorithm>
 #include <cerrno>
 #include <cstdio>
 #include <cstdlib>
@@ -150,11 +151,49 @@ static void format_record(std::string &out, const Record &r, const int32_t *res)
     }
 }
 
-static int flush_batch(svtk_ctx *ctx, Batch &b, FILE *out, int64_t *n_lines) {
+// the inserted sequences of the batch's refined INS records -> POA consensus -> FASTA (one entry per record that has carriers)
+static int write_ins_consensus(svtk_ctx *ctx, const Batch &b, const svtk_windows &w, const int32_t *res, int tol, FILE *fa, int64_t *n_cons) {
+    svtk_ins_sets sets;
+    if (int rc = svtk_ins_sequences(ctx, &w, res, tol, 50, &sets)) return rc;
+    if (sets.n_sets == 0) return 0;
+    std::vector<int> rec_of_win(b.chrom.size(), -1);
+    for (size_t i = 0; i < b.rec.size(); ++i) if (b.first[i] >= 0) rec_of_win[(size_t)b.first[i]] = (int)i;
+    std::vector<int64_t> cons_off((size_t)sets.n_sets + 1, 0);
+    for (int s = 0; s < sets.n_sets; ++s) {
+        int64_t longest = 0;
+        for (int64_t k = sets.set_off[s]; k < sets.set_off[s + 1]; ++k) longest = std::max(longest, sets.seq_off[k + 1] - sets.seq_off[k]);
+        cons_off[(size_t)s + 1] = cons_off[(size_t)s] + 2 * longest + 64;
+    }
+    std::vector<uint8_t> cons((size_t)cons_off.back());
+    std::vector<int32_t> clen((size_t)sets.n_sets), status((size_t)sets.n_sets);
+    // the set arrays belong to the ctx and svtk_poa_consensus does not touch them
+    const svtk_poa_batch pb = {sets.n_sets, sets.set_off, sets.seq_off, sets.bases};
+    if (int rc = svtk_poa_consensus(ctx, &pb, cons.data(), cons_off.data(), clen.data(), nullptr, status.data(), nullptr, nullptr)) return rc;
+    std::string text;
+    for (int s = 0; s < sets.n_sets; ++s) {
+        const int win = sets.window[s], ri = rec_of_win[(size_t)win];
+        if (ri < 0 || status[(size_t)s] != 0) continue;
+        const int64_t room = cons_off[(size_t)s + 1] - cons_off[(size_t)s];
+        const int32_t n = (int32_t)std::min<int64_t>(clen[(size_t)s], room);
+        char head[160];
+        snprintf(head, sizeof head, ">INS chr=%d org_pos=%u ref_pos=%d reads=%lld len=%d\n", b.rec[(size_t)ri].chrom, b.rec[(size_t)ri].pos, res[win],
+                 (long long)(sets.set_off[s + 1] - sets.set_off[s]), n);
+        text += head;
+        const uint8_t *q = cons.data() + cons_off[(size_t)s];
+        for (int32_t k = 0; k < n; ++k) text += "ACGTN"[q[k] < 4 ? q[k] : 4];
+        text += '\n';
+        ++*n_cons;
+    }
+    fwrite(text.data(), 1, text.size(), fa);
+    return 0;
+}
+
+static int flush_batch(svtk_ctx *ctx, Batch &b, FILE *out, int64_t *n_lines, FILE *fa = nullptr, int tol = 0, int64_t *n_cons = nullptr) {
     if (b.rec.empty()) return 0;
     std::vector<int32_t> res(b.chrom.size());
     const svtk_windows w = {(int32_t)b.chrom.size(), b.chrom.data(), b.start.data(), b.end.data(), b.pos.data(), b.kind.data()};
     if (int rc = svtk_refine_windows(ctx, &w, res.data())) return rc;
+    if (fa) if (int rc = write_ins_consensus(ctx, b, w, res.data(), tol, fa, n_cons)) return rc;
     std::string text;
     text.reserve(b.rec.size() * 96);
     for (size_t i = 0; i < b.rec.size(); ++i) {
@@ -171,9 +210,15 @@ static int flush_batch(svtk_ctx *ctx, Batch &b, FILE *out, int64_t *n_lines) {
 
 using namespace svtk;
 
-extern "C" int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records) {
+static int process_vcf_impl(svtk_ctx *ctx, const char *vcf_path, const char *out_path, const char *fasta_path, int tol, int64_t *n_records,
+                            int64_t *n_consensus) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c || !vcf_path) return fail(SVTK_ERR_ARG, "null argument");
+    if (fasta_path && !c->reads_from_bam) return fail(SVTK_ERR_STATE, "insertion consensus needs the BAM image: load the reads with svtk_load_bam");
+    FILE *fa = fasta_path ? fopen(fasta_path, "w") : nullptr;
+    if (fasta_path && !fa) return fail(SVTK_ERR_IO, "cannot open %s: %s", fasta_path, strerror(errno));
+    struct Closer { FILE *f; ~Closer() { if (f) fclose(f); } } fa_closer{fa};
+    int64_t n_cons = 0;
     if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded (svtk_load_reads)");
     FILE *vf = fopen(vcf_path, "r");
     if (!vf) return fail(SVTK_ERR_IO, "cannot open %s: %s", vcf_path, strerror(errno));
@@ -193,13 +238,25 @@ extern "C" int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char 
         if (line[len - 1] == '\n') line[--len] = 0;                            // audit.c:327-330
         Record r;
         if (parse_record(line, &r) == 1) add_record(b, r, c->params);
-        if (b.rec.size() >= BATCH_RECORDS && (rc = flush_batch(ctx, b, out, &n_lines))) break;
+        if (b.rec.size() >= BATCH_RECORDS && (rc = flush_batch(ctx, b, out, &n_lines, fa, tol, &n_cons))) break;
     }
-    if (!rc) rc = flush_batch(ctx, b, out, &n_lines);
+    if (!rc) rc = flush_batch(ctx, b, out, &n_lines, fa, tol, &n_cons);
     free(line);
     fclose(vf);
     if (!rc) fputs("[INFO] Ended processing variation file\n", out);           // audit.c:354
     if (to_stdout) fflush(out); else fclose(out);
     if (n_records) *n_records = n_lines;
+    if (n_consensus) *n_consensus = n_cons;
     return rc;
+}
+
+extern "C" int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records) {
+    return process_vcf_impl(ctx, vcf_path, out_path, nullptr, 0, n_records, nullptr);
+}
+
+extern "C" int svtk_process_vcf_ins(svtk_ctx *ctx, const char *vcf_path, const char *out_path, const char *fasta_path, int32_t tol, int64_t *n_records,
+                                    int64_t *n_consensus) {
+    if (!fasta_path) return fail(SVTK_ERR_ARG, "null fasta path");
+    if (tol < 0) tol = reinterpret_cast<Ctx *>(ctx) ? reinterpret_cast<Ctx *>(ctx)->params.consensus_interval : 0;
+    return process_vcf_impl(ctx, vcf_path, out_path, fasta_path, tol, n_records, n_consensus);
 }

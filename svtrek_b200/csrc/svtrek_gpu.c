@@ -8,7 +8,8 @@
  * `svtrek audt -t 1` on a VCF padded past the tail drop; -t is accepted and ignored (the GPU replaces the thread pool);
  * -o, when given, receives a copy of the record lines in addition to stdout (the reference accepts -o and never writes to
  * it -- SURVEY F1; the additional sink is SURVEY 8f-3's reading of the option).
- * Extra options: --device N (default 0), --stats (loader counters on stderr).  `disc` mode is not part of this path. */
+ * Extra options: --device N (default 0), --stats (loader counters on stderr), --ins-consensus FILE (FASTA side file with the POA
+ * consensus of the inserted sequence of every refined INS record: the north star's "abPOA for insertion consensus").  `disc` mode is not part of this path. */
 #include <getopt.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -29,7 +30,8 @@ static void usage(void) {
     printf("    --consensus-interval <num>        The interval that is considered into the same position [DEFAULT: 5]\n");
     printf("    --consensus-min-count <num>       Minimum number of elements needs for the consensus [Default: 3]\n\n");
     printf("    --device <num>                    CUDA device [Default: 0]\n");
-    printf("    --stats                           BAM loader counters on stderr\n\n");
+    printf("    --stats                           BAM loader counters on stderr\n");
+    printf("    --ins-consensus <filename>        FASTA with the consensus of the inserted sequence of every refined INS record\n\n");
 }
 
 static void need_file(const char *name, const char *missing) {
@@ -41,7 +43,7 @@ static void need_file(const char *name, const char *missing) {
 }
 
 int main(int argc, char *argv[]) {
-    const char *bam = NULL, *vcf = NULL, *out = NULL;
+    const char *bam = NULL, *vcf = NULL, *out = NULL, *fasta = NULL;
     svtk_params p = {20000, 10000, 2000, 500, 5, 3};
     int device = 0, stats = 0, verbose = 0, opt, li, threads = 4;
     static struct option lo[] = {
@@ -49,7 +51,8 @@ int main(int argc, char *argv[]) {
         {"verbose", no_argument, NULL, 4}, {"wider-interval", required_argument, NULL, 5}, {"median-interval", required_argument, NULL, 6},
         {"narrow-interval", required_argument, NULL, 7}, {"consensus-interval-range", required_argument, NULL, 8},
         {"consensus-interval", required_argument, NULL, 9}, {"consensus-min-count", required_argument, NULL, 10},
-        {"help", no_argument, NULL, 11}, {"device", required_argument, NULL, 12}, {"stats", no_argument, NULL, 13}, {NULL, 0, NULL, 0}};
+        {"help", no_argument, NULL, 11}, {"device", required_argument, NULL, 12}, {"stats", no_argument, NULL, 13}, {"ins-consensus", required_argument, NULL, 14},
+        {NULL, 0, NULL, 0}};
     if (argc < 2 || strcmp(argv[1], "audt") != 0) {
         printf("Usage: ./svtrek_gpu audt [OPTIONS]   (only the audt mode runs on the GPU)\n");
         return 1;
@@ -72,6 +75,7 @@ int main(int argc, char *argv[]) {
             case 'h': case 11: usage(); return EXIT_SUCCESS;
             case 12: device = atoi(optarg); break;
             case 13: stats = 1; break;
+            case 14: fasta = optarg; break;
             default:
                 printf("[ERROR] Option %d is invalid.\n", opt);
                 usage();
@@ -94,8 +98,9 @@ int main(int argc, char *argv[]) {
         fprintf(stderr, "[svtrek_gpu] %s: %.1f MB, %llu BGZF blocks -> %.1f MB, %llu reads, %llu CIGAR words; upload %.1f ms, inflate %.1f ms, "
                         "records %.2f ms, total %.1f ms\n", bam, st.file_bytes / 1e6, (unsigned long long)st.n_blocks, st.inflated_bytes / 1e6,
                 (unsigned long long)st.n_reads, (unsigned long long)st.n_words, st.upload_ms, st.inflate_ms, st.parse_ms, st.total_ms);
-    int64_t n = 0;
-    int rc = svtk_process_vcf(ctx, vcf, out, &n);            /* out == NULL: stdout */
+    int64_t n = 0, n_cons = 0;
+    int rc = fasta ? svtk_process_vcf_ins(ctx, vcf, out, fasta, -1, &n, &n_cons)
+                   : svtk_process_vcf(ctx, vcf, out, &n);    /* out == NULL: stdout */
     if (rc != 0) fprintf(stderr, "[ERROR] %s\n", svtk_last_error());
     if (out && rc == 0) {                                    /* -o is an additional sink: the lines still go to stdout */
         FILE *f = fopen(out, "r");
@@ -103,7 +108,7 @@ int main(int argc, char *argv[]) {
         size_t k;
         if (f) { while ((k = fread(buf, 1, sizeof buf, f)) > 0) fwrite(buf, 1, k, stdout); fclose(f); }
     }
-    if (stats) fprintf(stderr, "[svtrek_gpu] %lld records\n", (long long)n);
+    if (stats) fprintf(stderr, "[svtrek_gpu] %lld records, %lld insertion consensus sequences\n", (long long)n, (long long)n_cons);
     svtk_destroy(ctx);
     return 0;                                               /* the reference's exit status is 0 whatever happened (svtrek.c:15-21) */
 }

@@ -478,6 +478,9 @@ def run_ours(args):
                 out["poa_gcups"]["cpu_baseline"] = poa_cpu_baseline(poa_sets_l, poa_cons)
         if world == 1 and not args.no_bam:
             out["bam_e2e"] = bam_e2e_leg(a, args)
+            out["e2e"]["note"] = ("inputs are decoded reads in pinned host arrays (the C ABI's svtk_reads); the reference CLI also inflates and parses "
+                                  "the BAM -- the file-to-file number on the reference arm's own sample is bam_e2e.value")
+            out["e2e"]["file_to_file_records_per_s"] = out["bam_e2e"].get("value")
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_port_baseline(rs, w, n_records)
         print(json.dumps(out), flush=True)

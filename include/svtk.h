@@ -152,8 +152,9 @@ int svtk_attach_reads_device(svtk_ctx *ctx, const svtk_reads *dev_reads);
  * bai_path NULL: "<bam_path>.bai", else "<bam_path minus .bam>.bai".  Errors (SVTK_ERR_IO): unreadable / corrupt file,
  * stale index, records out of coordinate order, CRC32 mismatch of a block (checked on the GPU, like bgzf.c:776). */
 typedef struct {
-    uint64_t file_bytes, n_blocks, inflated_bytes;
+    uint64_t file_bytes, n_blocks, inflated_bytes;   /* n_blocks / inflated_bytes: of the part of the file that was loaded */
     uint64_t n_reads, n_words;
+    uint64_t image_bytes;            /* compressed bytes shipped to the GPU (== file_bytes for a whole-file load) */
     int32_t n_ref;
     uint32_t n_pieces;               /* pieces the record chain was cut into */
     uint32_t lanes_per_warp;         /* BGZF blocks decoded side by side in one warp (1..32, grows with the file) */
@@ -161,6 +162,11 @@ typedef struct {
     float upload_ms, inflate_ms, parse_ms, total_ms;
 } svtk_bam_stats;
 int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats);
+/* The same for the reads of references tid_lo .. tid_hi only (region shard of a multi-GPU run, SURVEY 8e: one ctx per GPU, each
+ * loads its own contiguous group of references): the index's bin chunks say where those references' records start and end in
+ * the file, so only that byte range is shipped and inflated.  Read indices and tid_off are those of the shard (other
+ * references are empty); windows on other references refine to NA. */
+int svtk_load_bam_refs(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int32_t tid_lo, int32_t tid_hi, svtk_bam_stats *stats);
 /* the BAM header's reference dictionary (bam_hdr_t target_name / target_len) after svtk_load_bam */
 int svtk_bam_n_ref(const svtk_ctx *ctx);
 int svtk_bam_ref(const svtk_ctx *ctx, int tid, const char **name, uint32_t *len);

@@ -68,7 +68,7 @@ class PoaStats(C.Structure):
 
 
 class BamStats(C.Structure):
-    _fields_ = [("file_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("inflated_bytes", C.c_uint64), ("n_reads", C.c_uint64), ("n_words", C.c_uint64),
+    _fields_ = [("file_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("inflated_bytes", C.c_uint64), ("n_reads", C.c_uint64), ("n_words", C.c_uint64), ("image_bytes", C.c_uint64),
                 ("n_ref", C.c_int32), ("n_pieces", C.c_uint32), ("lanes_per_warp", C.c_uint32), ("host_scan_ms", C.c_float), ("upload_ms", C.c_float), ("inflate_ms", C.c_float),
                 ("parse_ms", C.c_float), ("total_ms", C.c_float)]
 
@@ -82,7 +82,7 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs"]
 
 _lib = None
 
@@ -123,6 +123,7 @@ def load_library():
     L.svtk_poa_consensus.argtypes = [C.c_void_p, C.POINTER(PoaBatch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.POINTER(PoaTrace), C.POINTER(PoaStats)]
     L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
+    L.svtk_load_bam_refs.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(BamStats)]
     L.svtk_bam_n_ref.argtypes = [C.c_void_p]
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
     L.svtk_process_vcf_ins.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -247,10 +248,15 @@ class Auditor:
         return {k: getattr(t, k) for k, _ in Timing._fields_}
 
     # ---- BAM in (svtk_load_bam): what hts_open + sam_index_load + the per-window iterators give the reference
-    def load_bam(self, bam_path, bai_path=None):
-        """BGZF inflate + BAM record extraction on the GPU; returns the loader's counters / timings."""
+    def load_bam(self, bam_path, bai_path=None, refs=None):
+        """BGZF inflate + BAM record extraction on the GPU; returns the loader's counters / timings.
+        refs=(tid_lo, tid_hi): only the reads of those references (a region shard), only their part of the file."""
         st = BamStats()
-        _check(self.lib.svtk_load_bam(self.ctx, os.fsencode(bam_path), os.fsencode(bai_path) if bai_path else None, C.byref(st)))
+        bai = os.fsencode(bai_path) if bai_path else None
+        if refs is None:
+            _check(self.lib.svtk_load_bam(self.ctx, os.fsencode(bam_path), bai, C.byref(st)))
+        else:
+            _check(self.lib.svtk_load_bam_refs(self.ctx, os.fsencode(bam_path), bai, int(refs[0]), int(refs[1]), C.byref(st)))
         return {k: getattr(st, k) for k, _ in BamStats._fields_}
 
     def bam_refs(self):

@@ -284,10 +284,12 @@ inline uint32_t le32(const uint8_t *p) { return (uint32_t)p[0] | (uint32_t)p[1] 
 inline uint64_t le64(const uint8_t *p) { return (uint64_t)le32(p) | (uint64_t)le32(p + 4) << 32; }
 
 // BGZF block table (SAMv1 4.1): gzip member with the BC extra subfield carrying BSIZE
-int scan_bgzf(const uint8_t *f, size_t n, std::vector<BgzfBlock> &blk, std::vector<uint64_t> &coff) {
-    size_t off = 0;
+// [from, to): `from` must be the start of a block; scanning stops at the first block starting at or after `to`.
+// in_beg is relative to `base` (the file offset the device image starts at).
+int scan_bgzf(const uint8_t *f, size_t n, size_t from, size_t to, size_t base, std::vector<BgzfBlock> &blk, std::vector<uint64_t> &coff) {
+    size_t off = from;
     unsigned long long out = 0;
-    while (off < n) {
+    while (off < n && off < to) {
         if (off + 18 > n) return fail(SVTK_ERR_IO, "bam: truncated BGZF header at byte %zu", off);
         const uint8_t *h = f + off;
         if (h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) return fail(SVTK_ERR_IO, "bam: not a BGZF block at byte %zu", off);
@@ -302,7 +304,7 @@ int scan_bgzf(const uint8_t *f, size_t n, std::vector<BgzfBlock> &blk, std::vect
         }
         if (bsize < xlen + 20 || off + bsize > n) return fail(SVTK_ERR_IO, "bam: bad BGZF block size at byte %zu", off);
         BgzfBlock b;
-        b.in_beg = off + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = le32(h + bsize - 4); b.out_off = out;
+        b.in_beg = off - base + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = le32(h + bsize - 4); b.out_off = out;
         if (b.isize > 65536u) return fail(SVTK_ERR_IO, "bam: BGZF block at byte %zu claims %u inflated bytes", off, b.isize);
         blk.push_back(b); coff.push_back(off);
         out += b.isize;
@@ -312,18 +314,25 @@ int scan_bgzf(const uint8_t *f, size_t n, std::vector<BgzfBlock> &blk, std::vect
 }
 
 // the BAM header (magic, text, reference dictionary): inflated on the host with the same decoder, block by block, until complete
-int read_header(const uint8_t *f, size_t n, const std::vector<BgzfBlock> &blk, std::vector<std::string> &names, std::vector<uint32_t> &lens,
-                unsigned long long *first_rec) {
+int read_header(const uint8_t *f, size_t n, std::vector<std::string> &names, std::vector<uint32_t> &lens, unsigned long long *first_rec) {
+    std::vector<BgzfBlock> blk;                           // the header's own blocks, scanned lazily from the start of the file
+    std::vector<uint64_t> hcoff;
+    size_t scanned = 0;
     std::vector<uint32_t> words;                          // the decoder reads aligned words: one block's payload at a time
     std::vector<uint8_t> hd;
     size_t nb = 0;
-    static uint16_t lit[1 << BZ_LBITS], dist[1 << BZ_DBITS];
+    std::vector<uint16_t> tabs((1 << BZ_LBITS) + (1 << BZ_DBITS));
     BzTables T;
-    T.lit = lit; T.dist = dist;
-    (void)n;
+    T.lit = tabs.data(); T.dist = tabs.data() + (1 << BZ_LBITS);
     auto more = [&](size_t need) -> int {
         while (hd.size() < need) {
-            if (nb >= blk.size()) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
+            if (nb >= blk.size()) {
+                if (scanned >= n) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
+                const size_t before = blk.size();
+                if (int rc = scan_bgzf(f, n, scanned, std::min(n, scanned + (1u << 20)), 0, blk, hcoff)) return rc;
+                if (blk.size() == before) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
+                scanned = (size_t)(blk.back().in_beg + blk.back().in_len + 8);      // base 0: in_beg is a file offset
+            }
             const BgzfBlock &b = blk[nb++];
             words.assign((size_t)(b.in_len + BZ_OVERREAD) / 4 + 4, 0u);
             memcpy(words.data(), f + b.in_beg, b.in_len);
@@ -360,14 +369,18 @@ int read_header(const uint8_t *f, size_t n, const std::vector<BgzfBlock> &blk, s
 }
 
 // record-aligned cut points from the .bai (SAMv1 5.2): linear-index offsets and the chunk starts of every real bin
-int read_bai(const char *path, int n_ref_expected, std::vector<uint64_t> &voffs) {
+struct BaiRef { uint64_t beg = ~0ull, end = 0; };          // virtual offsets: first record / past the last record of one reference
+
+int read_bai(const char *path, int *n_ref_out, std::vector<uint64_t> &voffs, std::vector<BaiRef> &refs) {
     Mapped m;
     if (m.open_file(path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open index %s (the reference needs it too: sam_index_load, audit.c:272)", path);
     const uint8_t *f = m.p;
     const size_t n = m.n;
     if (n < 8 || memcmp(f, "BAI\1", 4) != 0) return fail(SVTK_ERR_IO, "bam: %s is not a BAI index", path);
     const int32_t n_ref = (int32_t)le32(f + 4);
-    if (n_ref != n_ref_expected) return fail(SVTK_ERR_IO, "bam: index has %d references, BAM header %d", n_ref, n_ref_expected);
+    if (n_ref < 0) return fail(SVTK_ERR_IO, "bam: bad index");
+    *n_ref_out = n_ref;
+    refs.assign((size_t)n_ref, BaiRef());
     size_t p = 8;
     for (int r = 0; r < n_ref; ++r) {
         if (p + 4 > n) return fail(SVTK_ERR_IO, "bam: truncated index");
@@ -380,7 +393,11 @@ int read_bai(const char *path, int n_ref_expected, std::vector<uint64_t> &voffs)
             p += 8;
             if (n_chunk < 0 || p + 16ull * (size_t)n_chunk > n) return fail(SVTK_ERR_IO, "bam: truncated index");
             if (bin != 37450u)                                      // the pseudo-bin holds file-level metadata, not record offsets
-                for (int k = 0; k < n_chunk; ++k) voffs.push_back(le64(f + p + 16 * (size_t)k));
+                for (int k = 0; k < n_chunk; ++k) {
+                    const uint64_t vb = le64(f + p + 16 * (size_t)k), ve = le64(f + p + 16 * (size_t)k + 8);
+                    voffs.push_back(vb);
+                    refs[(size_t)r].beg = std::min(refs[(size_t)r].beg, vb); refs[(size_t)r].end = std::max(refs[(size_t)r].end, ve);
+                }
             p += 16 * (size_t)n_chunk;
         }
         if (p + 4 > n) return fail(SVTK_ERR_IO, "bam: truncated index");
@@ -431,56 +448,95 @@ double ms_since(std::chrono::steady_clock::time_point t0) {
 
 }  // namespace
 
-extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats) {
+static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int tid_lo, int tid_hi, svtk_bam_stats *stats) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c || !bam_path) return fail(SVTK_ERR_ARG, "null argument");
     if (stats) memset(stats, 0, sizeof(*stats));
     if (int rc = set_device(c)) return rc;
     const auto t_all = std::chrono::steady_clock::now();
     c->have_reads = false;
+    const bool ranged = tid_lo >= 0;
 
-    // ---- host: map the file, BGZF block table, BAM header, cut points from the index
+    // ---- host: map the file; the index first (it says which bytes of the file a reference range needs)
     Mapped bam;
     if (bam.open_file(bam_path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open %s", bam_path);
     if (bam.n == 0) return fail(SVTK_ERR_IO, "bam: %s is empty", bam_path);
     if (bam.n >= (1ull << 34) - 65536) return fail(SVTK_ERR_ARG, "bam: files of 16 GiB and more must be sharded by region (32-bit word index in the decoder)");
-    // the table work runs on a helper thread while this thread feeds the upload ring (both only read the mapping)
-    std::vector<BgzfBlock> blk;
-    std::vector<uint64_t> coff;
-    std::vector<unsigned long long> splits;
-    unsigned long long total = 0, first_rec = 0;
-    int n_ref = 0, n_seg = 0, prep_rc = 0;
-    std::string prep_msg;
-    double prep_ms = 0;
-    auto prep = [&]() -> int {
-        if (int rc = scan_bgzf(bam.p, bam.n, blk, coff)) return rc;
-        total = blk.empty() ? 0ull : blk.back().out_off + blk.back().isize;
-        if (blk.size() >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: shard the file");
-        if (int rc = read_header(bam.p, bam.n, blk, c->bam_ref_names, c->bam_ref_lens, &first_rec)) return rc;
-        n_ref = (int)c->bam_ref_names.size();
-        if (first_rec > total) return fail(SVTK_ERR_IO, "bam: header longer than the file");
-        std::vector<uint64_t> voffs;
+    std::vector<uint64_t> voffs;
+    std::vector<BaiRef> bai_refs;
+    int bai_n_ref = 0;
+    {
         std::string bai = bai_path ? std::string(bai_path) : std::string(bam_path) + ".bai";
         if (!bai_path && access(bai.c_str(), R_OK) != 0) {
             std::string alt(bam_path);
             if (alt.size() > 4 && alt.compare(alt.size() - 4, 4, ".bam") == 0) { alt.replace(alt.size() - 4, 4, ".bai"); if (access(alt.c_str(), R_OK) == 0) bai = alt; }
         }
-        if (int rc = read_bai(bai.c_str(), n_ref, voffs)) return rc;
+        if (int rc = read_bai(bai.c_str(), &bai_n_ref, voffs, bai_refs)) return rc;
+    }
+    // byte range [fb, fe) of the file to ship and record range [v_beg, v_end) (virtual offsets) to walk; whole file: everything
+    size_t fb = 0, fe = bam.n;
+    uint64_t v_beg = 0, v_end = ~0ull;
+    bool nothing = false;
+    if (ranged) {
+        if (tid_hi < tid_lo || tid_hi >= bai_n_ref) return fail(SVTK_ERR_ARG, "bam: reference range [%d, %d] outside the index's %d references", tid_lo, tid_hi, bai_n_ref);
+        v_beg = ~0ull; v_end = 0;
+        for (int t = tid_lo; t <= tid_hi; ++t) { v_beg = std::min(v_beg, bai_refs[(size_t)t].beg); v_end = std::max(v_end, bai_refs[(size_t)t].end); }
+        if (v_beg >= v_end) nothing = true;                        // no reads on these references
+        else {
+            fb = (size_t)(v_beg >> 16);
+            fe = (size_t)(v_end >> 16) + 1;                        // the block holding v_end is the last one scanned (scan stops at the first block at or after fe)
+            if (fb >= bam.n) return fail(SVTK_ERR_IO, "bam: index offset beyond the end of the file (stale .bai?)");
+        }
+    }
+
+    // the table work runs on a helper thread while this thread feeds the upload ring (both only read the mapping)
+    std::vector<BgzfBlock> blk;
+    std::vector<uint64_t> coff;
+    std::vector<unsigned long long> splits;
+    unsigned long long total = 0, first_rec = 0, last_rec = 0;
+    int n_ref = 0, n_seg = 0, prep_rc = 0;
+    std::string prep_msg;
+    double prep_ms = 0;
+    size_t image_bytes = 0;                                        // bytes of the file the device image holds, from fb
+    auto to_linear = [&](uint64_t v, unsigned long long *lin) -> int {
+        const uint64_t co = v >> 16, uo = v & 0xffffu;
+        auto it = std::lower_bound(coff.begin(), coff.end(), co);
+        if (it == coff.end() || *it != co) {
+            if (!coff.empty() && co == coff.back() + (blk.back().in_beg + fb - coff.back()) + blk.back().in_len + 8 && uo == 0) { *lin = total; return 0; }   // just past the last block
+            return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a BGZF block (stale .bai?)", (unsigned long long)co);
+        }
+        const BgzfBlock &b = blk[(size_t)(it - coff.begin())];
+        if (uo > b.isize) return fail(SVTK_ERR_IO, "bam: index offset beyond its block (stale .bai?)");
+        *lin = b.out_off + uo;
+        return 0;
+    };
+    auto prep = [&]() -> int {
+        unsigned long long hdr_end = 0;
+        if (int rc = read_header(bam.p, bam.n, c->bam_ref_names, c->bam_ref_lens, &hdr_end)) return rc;
+        n_ref = (int)c->bam_ref_names.size();
+        if (n_ref != bai_n_ref) return fail(SVTK_ERR_IO, "bam: index has %d references, BAM header %d", bai_n_ref, n_ref);
+        if (nothing) { splits.push_back(0); return 0; }
+        if (int rc = scan_bgzf(bam.p, bam.n, fb, fe, fb, blk, coff)) return rc;
+        if (blk.empty()) return fail(SVTK_ERR_IO, "bam: no BGZF block at index offset %zu (stale .bai?)", fb);
+        total = blk.back().out_off + blk.back().isize;
+        if (blk.size() >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: shard the file");
+        if (ranged) {
+            if (int rc = to_linear(v_beg, &first_rec)) return rc;
+            if (int rc = to_linear(v_end, &last_rec)) return rc;
+        } else { first_rec = hdr_end; last_rec = total; }
+        if (first_rec > last_rec || last_rec > total) return fail(SVTK_ERR_IO, "bam: header / index offsets beyond the file");
         splits.reserve(voffs.size() + 2);
         splits.push_back(first_rec);
         for (uint64_t v : voffs) {
-            const uint64_t co = v >> 16, uo = v & 0xffffu;
-            auto it = std::lower_bound(coff.begin(), coff.end(), co);
-            if (it == coff.end() || *it != co) return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a BGZF block (stale .bai?)", (unsigned long long)co);
-            const BgzfBlock &b = blk[(size_t)(it - coff.begin())];
-            if (uo > b.isize) return fail(SVTK_ERR_IO, "bam: index offset beyond its block (stale .bai?)");
-            const unsigned long long lin = b.out_off + uo;
-            if (lin > first_rec && lin < total) splits.push_back(lin);
+            if (ranged && (v <= v_beg || v >= v_end)) continue;
+            unsigned long long lin = 0;
+            if (int rc = to_linear(v, &lin)) return rc;
+            if (lin > first_rec && lin < last_rec) splits.push_back(lin);
         }
         std::sort(splits.begin(), splits.end());
         splits.erase(std::unique(splits.begin(), splits.end()), splits.end());
-        n_seg = first_rec < total ? (int)splits.size() : 0;
-        splits.push_back(total);
+        n_seg = first_rec < last_rec ? (int)splits.size() : 0;
+        splits.push_back(last_rec);
         return 0;
     };
     std::thread prep_thread([&]() {
@@ -490,12 +546,14 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     });
     struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{prep_thread};
 
-    // ---- device: the compressed file image (needs nothing from the tables)
+    // ---- device: the compressed image (needs nothing from the tables).  A ranged load does not know yet where its last block
+    // ends: it ships up to the end of the block that holds v_end, which is at most 64 KiB past fe
     for (int i = 0; i < 4; ++i) if (!c->bam_ev[i]) CU(cudaEventCreate(&c->bam_ev[i]));
-    if (int rc = c->bam_comp.reserve(bam.n + BZ_OVERREAD)) return rc;
-    CU(cudaMemsetAsync((char *)c->bam_comp.p + (bam.n & ~(size_t)3), 0, BZ_OVERREAD - (bam.n & 3), c->stream));   // the decoder looks a few bytes past the end
+    image_bytes = nothing ? 0 : std::min(bam.n, ranged ? fe + 65536 : bam.n) - fb;
+    if (int rc = c->bam_comp.reserve(image_bytes + BZ_OVERREAD)) return rc;
+    CU(cudaMemsetAsync((char *)c->bam_comp.p + (image_bytes & ~(size_t)3), 0, BZ_OVERREAD - (image_bytes & 3), c->stream));   // the decoder looks a few bytes past the end
     CU(cudaEventRecord(c->bam_ev[0], c->stream));
-    if (int rc = upload_file(c, c->bam_comp.p, bam.p, bam.n)) return rc;
+    if (image_bytes) if (int rc = upload_file(c, c->bam_comp.p, bam.p + fb, image_bytes)) return rc;
     prep_thread.join();
     if (prep_rc) return fail(prep_rc, "%s", prep_msg.c_str());
     const double host_ms = prep_ms;
@@ -603,7 +661,7 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     if (hctl[BAM_CTL_ORDER]) return fail(SVTK_ERR_IO, "bam: records are not in coordinate order (or a refID is outside the header's dictionary)");
     memcpy(tid_off.data(), hctl + 16, 8 * (size_t)(n_ref + 1));
     c->bam_infl_bytes = total; c->bam_n_rec = n_reads;
-    c->h2d_bytes += bam.n + sizeof(BgzfBlock) * blk.size() + 8 * splits.size();
+    c->h2d_bytes += image_bytes + sizeof(BgzfBlock) * blk.size() + 8 * splits.size();
 
     svtk_reads d{};
     d.n_tid = n_ref; d.n_reads = n_reads; d.n_words = n_words; d.tid_off = tid_off.data();
@@ -614,11 +672,20 @@ extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *ba
     if (stats) {
         float up = 0, inf = 0, par = 0;
         cudaEventElapsedTime(&up, c->bam_ev[0], c->bam_ev[1]); cudaEventElapsedTime(&inf, c->bam_ev[1], c->bam_ev[2]); cudaEventElapsedTime(&par, c->bam_ev[2], c->bam_ev[3]);
-        stats->file_bytes = bam.n; stats->n_blocks = blk.size(); stats->inflated_bytes = total; stats->n_reads = (uint64_t)n_reads;
+        stats->file_bytes = bam.n; stats->image_bytes = image_bytes; stats->n_blocks = blk.size(); stats->inflated_bytes = total; stats->n_reads = (uint64_t)n_reads;
         stats->n_words = (uint64_t)n_words; stats->n_ref = n_ref; stats->n_pieces = (uint32_t)n_seg; stats->host_scan_ms = (float)host_ms;
         stats->upload_ms = up; stats->inflate_ms = inf; stats->parse_ms = par; stats->total_ms = (float)ms_since(t_all);
     }
     return 0;
+}
+
+extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats) {
+    return load_bam_impl(ctx, bam_path, bai_path, -1, -1, stats);
+}
+
+extern "C" int svtk_load_bam_refs(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int32_t tid_lo, int32_t tid_hi, svtk_bam_stats *stats) {
+    if (tid_lo < 0) return fail(SVTK_ERR_ARG, "bad reference range");
+    return load_bam_impl(ctx, bam_path, bai_path, tid_lo, tid_hi, stats);
 }
 
 extern "C" int svtk_bam_n_ref(const svtk_ctx *ctx) { return ctx ? (int)reinterpret_cast<const Ctx *>(ctx)->bam_ref_names.size() : 0; }

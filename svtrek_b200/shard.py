@@ -90,3 +90,47 @@ def audit_sharded(refine_fn, rs: ReadSet, windows: dict, rank: int, world: int, 
     out = [torch.empty_like(buf) for _ in range(world)]
     dist.all_gather(out, buf, group=group)
     return np.concatenate([o[:n].cpu().numpy() for o, n in zip(out, sizes)])
+
+
+def bai_reference_spans(bai_path):
+    """Per reference of a .bai (SAMv1 5.2): (first virtual offset, last virtual offset) of its records' bin chunks, or None
+    for a reference without reads.  What svtk_load_bam_refs uses to find a reference group's bytes in the file."""
+    import struct
+    b = open(bai_path, "rb").read()
+    assert b[:4] == b"BAI\1", "not a BAI index"
+    n_ref = struct.unpack_from("<i", b, 4)[0]
+    p, out = 8, []
+    for _ in range(n_ref):
+        n_bin = struct.unpack_from("<i", b, p)[0]
+        p += 4
+        lo, hi = None, None
+        for _ in range(n_bin):
+            bin_id, n_chunk = struct.unpack_from("<Ii", b, p)
+            p += 8
+            if bin_id != 37450:
+                for k in range(n_chunk):
+                    vb, ve = struct.unpack_from("<QQ", b, p + 16 * k)
+                    lo = vb if lo is None else min(lo, vb)
+                    hi = ve if hi is None else max(hi, ve)
+            p += 16 * n_chunk
+        n_intv = struct.unpack_from("<i", b, p)[0]
+        p += 4 + 8 * n_intv
+        out.append(None if lo is None else (lo, hi))
+    return out
+
+
+def plan_ref_shards(bai_path, n_shards):
+    """Contiguous groups of references, one per shard, balanced by the compressed bytes their records occupy in the file
+    (north star: records sharded by genomic region, no collective).  Returns [(tid_lo, tid_hi)], possibly fewer than n_shards."""
+    spans = bai_reference_spans(bai_path)
+    size = [0 if s is None else max(1, (s[1] >> 16) - (s[0] >> 16)) for s in spans]
+    total = float(sum(size)) or 1.0
+    shards, lo, acc, done = [], 0, 0.0, 0.0
+    for t, sz in enumerate(size):
+        acc += sz
+        left = n_shards - len(shards)
+        if left > 1 and acc >= (total - done) / left and t + 1 < len(size):
+            shards.append((lo, t)); lo = t + 1; done += acc; acc = 0.0
+    if lo < len(size):
+        shards.append((lo, len(size) - 1))
+    return shards

@@ -378,3 +378,46 @@ def test_load_bam_shapes(tmp_path, case):
     w = S.windows_from_truth(truth)
     res = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
     assert np.array_equal(res, B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])), case
+
+
+@pytest.mark.gpu
+def test_load_bam_refs_shards_equal_the_whole(tmp_path):
+    """svtk_load_bam_refs: every reference group's reads == that slice of the whole-file load, only its part of the file is
+    shipped, and the windows of its references refine to the whole-file results (region shards, no collective)."""
+    from svtrek_b200 import api, shard as SH, simreads as S
+    rs, truth = S.simulate(4, contig_lens=[250_000 if t % 5 else 200_000 for t in range(24)], coverage=4, read_len=8000, small_rate=0.01, n_sv=120, min_gap=1500)
+    bam = str(tmp_path / "g.bam")
+    S.write_bam(bam, rs, truth=truth)
+    w = S.windows_from_truth(truth)
+    a = api.Auditor(0)
+    whole_st = a.load_bam(bam)
+    whole = a.copy_reads()
+    want = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    shards = SH.plan_ref_shards(bam + ".bai", 3)
+    assert len(shards) == 3
+    got = np.full(len(want), -1, np.int32)
+    for lo, hi in shards:
+        st = a.load_bam(bam, refs=(lo, hi))
+        part = a.copy_reads()
+        r0, r1 = int(whole["tid_off"][lo]), int(whole["tid_off"][hi + 1])
+        assert st["n_reads"] == r1 - r0 and st["image_bytes"] < 0.6 * whole_st["file_bytes"]
+        for k in ("pos", "end", "n_cigar"):
+            assert np.array_equal(part[k], whole[k][r0:r1]), k
+        c0 = int(whole["cigar_off"][r0])
+        assert np.array_equal(part["cigar"], whole["cigar"][c0:c0 + len(part["cigar"])])
+        assert np.array_equal(part["tid_off"], np.clip(whole["tid_off"], r0, r1) - r0)
+        mine = (w["chrom"] - 1 >= lo) & (w["chrom"] - 1 <= hi)
+        res = a.refine_windows(w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+        assert (res[~mine] == -1).all()
+        got[mine] = res[mine]
+    assert np.array_equal(got, want)
+    # HTSlib-written file with an empty reference in the middle
+    z = np.load(GOLD_NPZ)
+    for lo, hi in ((0, 0), (1, 1), (2, 2), (0, 2), (1, 2)):
+        st = a.load_bam(GOLD_BAM, refs=(lo, hi))
+        part = a.copy_reads()
+        r0, r1 = int(z["tid_off"][lo]), int(z["tid_off"][hi + 1])
+        assert st["n_reads"] == r1 - r0
+        assert np.array_equal(part["pos"], z["pos"][r0:r1]) and np.array_equal(part["end"], z["end"][r0:r1])
+    with pytest.raises(api.SvtkError):
+        a.load_bam(GOLD_BAM, refs=(2, 5))

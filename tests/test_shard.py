@@ -84,3 +84,15 @@ def test_gpu_sharded_equals_whole(auditor):
     parts = [shard.audit_sharded(refine, shard.shard_reads(rs, w, lo, hi), {k: v[lo:hi] for k, v in w.items()}, 0, 1)
              for lo, hi in shard.plan_shards(w, 4)]
     assert np.array_equal(np.concatenate(parts), whole)
+
+
+def test_plan_ref_shards_on_the_golden_index():
+    import os
+    from svtrek_b200 import shard as SH
+    bai = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bam_small.bam.bai")
+    spans = SH.bai_reference_spans(bai)
+    assert len(spans) == 3 and spans[1] is None and spans[0][0] < spans[0][1] <= spans[2][0] < spans[2][1]
+    for n in (1, 2, 3, 5):
+        sh = SH.plan_ref_shards(bai, n)
+        assert 1 <= len(sh) <= n and sh[0][0] == 0 and sh[-1][1] == 2
+        assert all(a[1] + 1 == b[0] for a, b in zip(sh, sh[1:]))

@@ -127,9 +127,11 @@ static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     return 0;
 }
 
-// fold the event pairs of the previous profiled batch into the running totals (waits for that batch's kernels)
-static int collect_timing(Ctx *c) {
-    if (c->prof_pending) {
+// harvest finished kernel timings.  which: 1 = refine pair, 2 = index pair, 3 = both.  A pair is only waited for when it is
+// about to be re-recorded (or read); svtk_sync harvests both after the stream has drained, so a step that ends in svtk_sync
+// never blocks the host between its two kernels.
+static int collect_timing(Ctx *c, int which = 3) {
+    if ((which & 1) && c->prof_pending) {
         c->prof_pending = false;
         CU(cudaEventSynchronize(c->prof_ev[1]));
         float ms = 0.f;
@@ -137,7 +139,7 @@ static int collect_timing(Ctx *c) {
         c->refine_ms += (double)ms;
         c->refine_launches += 1;
     }
-    if (c->prof_idx_pending) {
+    if ((which & 2) && c->prof_idx_pending) {
         c->prof_idx_pending = false;
         CU(cudaEventSynchronize(c->prof_ev[3]));
         float ms = 0.f;
@@ -158,7 +160,7 @@ static int build_index(Ctx *c) {
         if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 64 + 1024, c->idx.seg_cap))) return rc;
     }
     CU(cudaMemsetAsync(c->idx_ctrl.p, 0, 4 * (size_t)index_ctrl_words(), c->stream));
-    if (c->profile) { if (int rc = collect_timing(c)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
+    if (c->profile) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
     CU(launch_index_reads(c->reads, c->idx, c->stream));
     if (c->profile) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
     c->launches += c->reads.n_reads > 0;
@@ -200,7 +202,7 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
     } else {
         if (!c->index_valid) if (int rc = build_index(c)) return rc;
         if (c->profile) {
-            if (int rc = collect_timing(c)) return rc;
+            if (int rc = collect_timing(c, 1)) return rc;
             CU(cudaEventRecord(c->prof_ev[0], c->stream));
         }
         CU(launch_refine_indexed(c->reads, w, c->idx, (int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
@@ -436,6 +438,7 @@ int svtk_sync(svtk_ctx *ctx) {
     if (!c) return fail(SVTK_ERR_ARG, "null ctx");
     if (int rc = set_device(c)) return rc;
     CU(cudaStreamSynchronize(c->stream));
+    if (c->profile) if (int rc = collect_timing(c)) return rc;
     return resolve_overflow(c);
 }
 

@@ -42,7 +42,10 @@ struct DevWindows {
 
 struct Tunables { int range, interval, min_count; };
 
-constexpr int IDX_READS = 8;               // reads per chunk of the signature index: one warp's share (svtk_index.cu)
+#ifndef SVTK_IDX_READS
+#define SVTK_IDX_READS 8
+#endif
+constexpr int IDX_READS = SVTK_IDX_READS;               // reads per chunk of the signature index: one warp's share (svtk_index.cu)
 constexpr int IDX_POOLS = 16;              // event sub-pools (spreads the per-flush atomicAdd over 16 L2 lines)
 
 struct OverflowList {

@@ -582,8 +582,8 @@ static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_pa
         int lanes = 1;
         while (lanes < 32 && (long long)((blk.size() + lanes - 1) / lanes) > want_warps) lanes <<= 1;
         const int smem = lanes * BZ_TABLE_WORDS * 4;
-        static int attr_smem = 0;
-        if (smem > attr_smem) { CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * BZ_TABLE_WORDS * 4)); attr_smem = 32 * BZ_TABLE_WORDS * 4; }
+        static unsigned long long attr_seen = 0;
+        if (first_use_on_device(attr_seen)) CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * BZ_TABLE_WORDS * 4));
         int per_sm = 1;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
         const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (blk.size() + lanes - 1) / lanes);

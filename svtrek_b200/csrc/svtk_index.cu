@@ -820,12 +820,11 @@ cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaS
     if (r.n_reads <= 0) return cudaSuccess;
 #if SVTK_IDX_LANE
     const long long warps = (r.n_reads + 31) / 32;
-    static bool lane_attr = false;
+    static unsigned long long lane_seen = 0;
     const int smem = (int)(sizeof(LaneWarpShared) * LANE_WARPS);
-    if (!lane_attr) {
+    if (first_use_on_device(lane_seen)) {
         cudaError_t e = cudaFuncSetAttribute(k_index_reads_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        lane_attr = true;
     }
     k_index_reads_lane<<<(unsigned)((warps + LANE_WARPS - 1) / LANE_WARPS), LANE_WARPS * 32, smem, s>>>(to_dev(r), to_dev(x));
 #else
@@ -852,12 +851,11 @@ cudaError_t launch_refine_indexed(const LaunchReads &r, const LaunchWindows &w, 
 cudaError_t launch_refine_block(const LaunchReads &r, const LaunchWindows &w, const LaunchIndex &x, const int2 *range, int range_,
                                 int interval, int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
                                 int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag, cudaStream_t s) {
-    static bool attr_set = false;
+    static unsigned long long attr_seen = 0;
     const int cap = refine_block_segment_ints();
-    if (!attr_set) {
+    if (first_use_on_device(attr_seen)) {
         cudaError_t e = cudaFuncSetAttribute(k_refine_block<RB_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap * 4);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const Tunables t{range_, interval, min_count};
     const OverflowList ov{ov_count, ov_items, ov_capacity};

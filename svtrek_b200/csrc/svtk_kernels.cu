@@ -315,12 +315,11 @@ cudaError_t launch_refine_overflow(const LaunchReads &r, const LaunchWindows &w,
                                    int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
                                    int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag,
                                    cudaStream_t s) {
-    static bool attr_set = false;
+    static unsigned long long attr_seen = 0;
     const int cap = big_segment_ints();
-    if (!attr_set) {
+    if (first_use_on_device(attr_seen)) {
         cudaError_t e = cudaFuncSetAttribute(k_refine_overflow<BIG_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap * 4);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const Tunables t{range_, interval, min_count};
     const OverflowList ov{ov_count, ov_items, ov_capacity};

@@ -5,6 +5,16 @@
 
 namespace svtk {
 
+// function attributes (dynamic shared memory limits) are per device: one process may drive several GPUs, one ctx each
+inline bool first_use_on_device(unsigned long long &seen) {
+    int d = 0;
+    cudaGetDevice(&d);
+    const unsigned long long bit = 1ull << (d & 63);
+    if (seen & bit) return false;
+    seen |= bit;
+    return true;
+}
+
 struct LaunchReads {            // device pointers
     int n_tid;
     long long n_reads;

@@ -109,6 +109,16 @@ static int finish_reads(Ctx *c) {
     return 0;
 }
 
+// ---- control block: the index counters followed by the batch flags, so that a step which builds the index clears both with
+// one memset and reads both back with one copy.  flags: [0] overflow count  [1] fail flag  [2..3] arena top (u64)
+static size_t ctl_index_bytes() { return 4 * (size_t)index_ctrl_words(); }
+static int ensure_ctl(Ctx *c) {
+    if (int rc = c->idx_ctrl.reserve(ctl_index_bytes() + 64)) return rc;
+    return c->h_idx.reserve(ctl_index_bytes() + 64);
+}
+static int *ov_flags(Ctx *c) { return (int *)((char *)c->idx_ctrl.p + ctl_index_bytes()); }
+static int *host_flags(Ctx *c) { return (int *)((char *)c->h_idx.p + ctl_index_bytes()); }
+
 // ---- signature index (svtk_index.cu)
 static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     const long long nr = c->reads.n_reads;
@@ -120,8 +130,7 @@ static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     if (int rc = c->idx_chunks.reserve(16 * (size_t)std::max(n_chunks, 1ll))) return rc;
     if (int rc = c->idx_segs.reserve(16 * (size_t)seg_cap)) return rc;
     if (int rc = c->idx_rend.reserve(4 * (size_t)std::max(nr, 1ll))) return rc;
-    if (int rc = c->idx_ctrl.reserve(4 * (size_t)index_ctrl_words())) return rc;
-    if (int rc = c->h_idx.reserve(4 * (size_t)index_ctrl_words())) return rc;
+    if (int rc = ensure_ctl(c)) return rc;
     c->idx = LaunchIndex{c->idx_events.p, c->idx_chunks.p, c->idx_segs.p, (uint32_t *)c->idx_rend.p, (unsigned int *)c->idx_ctrl.p,
                          (unsigned int)pool_cap, (unsigned int)seg_cap, (int)n_chunks};
     return 0;
@@ -159,7 +168,7 @@ static int build_index(Ctx *c) {
         const uint64_t pool = ev / (uint64_t)index_pools() * 5 / 4 + 1024;
         if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 64 + 1024, c->idx.seg_cap))) return rc;
     }
-    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, 4 * (size_t)index_ctrl_words(), c->stream));
+    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, ctl_index_bytes() + 64, c->stream));     // the batch flags too
     if (c->profile) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
     CU(launch_index_reads(c->reads, c->idx, c->stream));
     if (c->profile) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
@@ -172,9 +181,7 @@ static int build_index(Ctx *c) {
 static int ensure_batch(Ctx *c, int n_win) {
     if (int rc = c->range.reserve((size_t)n_win * sizeof(int2))) return rc;
     if (int rc = c->ov_items.reserve((size_t)n_win * sizeof(int2))) return rc;
-    if (int rc = c->ov_count.reserve(64)) return rc;      // [0] overflow count  [1] fail flag  [2..3] arena top (u64)
-    if (int rc = c->h_flags.reserve(64)) return rc;       // [0] overflow count  [1] fail flag
-    return 0;
+    return ensure_ctl(c);
 }
 
 enum { MODE_INDEXED = 0, MODE_WALKER_STATS = 1, MODE_INDEXED_STATS = 2 };
@@ -185,7 +192,8 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
     if (int rc = ensure_batch(c, std::max(w.n_win, 1))) return rc;
     c->pending = false;
     if (w.n_win <= 0) return 0;
-    CU(cudaMemsetAsync(c->ov_count.p, 0, 64, c->stream));
+    const bool with_index = mode != MODE_WALKER_STATS && !c->index_valid;      // build_index clears the whole control block
+    if (!with_index) CU(cudaMemsetAsync(ov_flags(c), 0, 64, c->stream));
     unsigned long long *counters = nullptr;
     if (mode != MODE_INDEXED) {
         if (int rc = c->counters.reserve(64)) return rc;
@@ -196,7 +204,7 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
         // the reference-shaped walker (one CIGAR walk per (window, read) pair): instrumented cross-check
         CU(launch_plan(c->reads, w, (int2 *)c->range.p, c->stream));
         CU(launch_refine_fused(c->reads, w, (const int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
-                               c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
+                               c->params.consensus_min_count, dev_result, ov_flags(c), (int2 *)c->ov_items.p, w.n_win, counters,
                                c->stream));
         c->launches += 2;
     } else {
@@ -206,16 +214,18 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
             CU(cudaEventRecord(c->prof_ev[0], c->stream));
         }
         CU(launch_refine_indexed(c->reads, w, c->idx, (int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
-                                 c->params.consensus_min_count, dev_result, (int *)c->ov_count.p, (int2 *)c->ov_items.p, w.n_win, counters,
+                                 c->params.consensus_min_count, dev_result, ov_flags(c), (int2 *)c->ov_items.p, w.n_win, counters,
                                  c->stream));
         if (c->profile) {
             CU(cudaEventRecord(c->prof_ev[1], c->stream));
             c->prof_pending = true;
         }
         c->launches += 1;
-        if (c->index_fresh) CU(cudaMemcpyAsync(c->h_idx.p, c->idx_ctrl.p, 4 * (size_t)index_ctrl_words(), cudaMemcpyDeviceToHost, c->stream));
     }
-    CU(cudaMemcpyAsync(c->h_flags.p, c->ov_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    if (mode != MODE_WALKER_STATS && c->index_fresh)
+        CU(cudaMemcpyAsync(c->h_idx.p, c->idx_ctrl.p, ctl_index_bytes() + 4, cudaMemcpyDeviceToHost, c->stream));
+    else
+        CU(cudaMemcpyAsync(host_flags(c), ov_flags(c), 4, cudaMemcpyDeviceToHost, c->stream));
     c->pending = true;
     c->pend_mode = mode;
     c->pend_win = w;
@@ -257,7 +267,7 @@ static int resolve_overflow(Ctx *c) {
             return resolve_overflow(c);
         }
     }
-    const int n_ov = *(int *)c->h_flags.p;
+    const int n_ov = *host_flags(c);
     c->last_overflow = n_ov;
     if (n_ov <= 0) return 0;
     std::vector<int2> items((size_t)n_ov);
@@ -271,7 +281,7 @@ static int resolve_overflow(Ctx *c) {
         if (p > (unsigned long long)big) arena_need += p;
     }
     if (arena_need) if (int rc = c->arena.reserve(arena_need * 4)) return rc;
-    int *flags = (int *)c->ov_count.p;
+    int *flags = ov_flags(c);
     CU(cudaMemsetAsync(flags + 1, 0, 12, c->stream));     // fail flag + arena top
     if (walker)
         CU(launch_refine_overflow(c->reads, c->pend_win, (const int2 *)c->range.p, c->params.consensus_interval_range,
@@ -284,9 +294,9 @@ static int resolve_overflow(Ctx *c) {
                                c->pend_win.n_win, n_ov, (int *)c->arena.p, arena_need, (unsigned long long *)(flags + 2), flags + 1,
                                c->stream));
     c->launches += 1;
-    CU(cudaMemcpyAsync((int *)c->h_flags.p + 1, flags + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(host_flags(c) + 1, flags + 1, 4, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (((int *)c->h_flags.p)[1]) return fail(SVTK_ERR_STATE, "overflow arena exhausted");
+    if (host_flags(c)[1]) return fail(SVTK_ERR_STATE, "overflow arena exhausted");
     return 0;
 }
 
@@ -359,12 +369,12 @@ void svtk_destroy(svtk_ctx *ctx) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items, &c->ov_count,
+    for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items,
                       &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
                       &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl, &c->bam_comp, &c->bam_infl, &c->bam_blocks,
                       &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl})
         b->release();
-    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_flags, &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
+    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
     for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
     c->bam_h.release();
@@ -540,7 +550,7 @@ int svtk_refine_windows(svtk_ctx *ctx, const svtk_windows *w, int32_t *host_resu
     if (int rc = launch_batch(c, lw, (int32_t *)c->result.p, MODE_INDEXED)) return rc;
     CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (*(int *)c->h_flags.p > 0 || (c->index_fresh && ((const unsigned int *)c->h_idx.p)[(index_pools() + 1) * index_ctrl_stride()])) {
+    if (*host_flags(c) > 0 || (c->index_fresh && ((const unsigned int *)c->h_idx.p)[(index_pools() + 1) * index_ctrl_stride()])) {
         // some windows left the fast path, or the fresh index ran out of room: finish them, then fetch again
         if (int rc = resolve_overflow(c)) return rc;
         CU(cudaMemcpyAsync(c->h_result.p, c->result.p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
@@ -659,10 +669,10 @@ int svtk_window_signatures(svtk_ctx *ctx, int kind, int chrom, svtk_interval int
     long long buf_ints = 1 << 16;
     for (int attempt = 0; attempt < 3; ++attempt) {
         if (int rc = c->tmp_a.reserve((size_t)buf_ints * 4 + 16)) return rc;
-        CU(launch_window_signatures(c->reads, lw, (const int2 *)c->range.p, (int *)c->tmp_a.p, (int)buf_ints, (int *)c->ov_count.p, c->stream));
+        CU(launch_window_signatures(c->reads, lw, (const int2 *)c->range.p, (int *)c->tmp_a.p, (int)buf_ints, ov_flags(c), c->stream));
         c->launches += 1;
         int n = 0;
-        CU(cudaMemcpyAsync(&n, c->ov_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(&n, ov_flags(c), 4, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         long long p = 1; while (p < n) p <<= 1;
         if (p <= buf_ints) {
@@ -709,7 +719,7 @@ int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int w
     if (int rc = c->tmp_b.reserve(sizeof(int2) * (size_t)nt)) return rc;
     CU(launch_plan(c->reads, lw, (int2 *)c->range.p, c->stream));
     c->launches += 1;
-    int *need_d = (int *)c->ov_count.p;
+    int *need_d = ov_flags(c);
     long long stride = 0;
     std::vector<int2> out((size_t)nt);
     for (int attempt = 0; attempt < 2; ++attempt) {

@@ -43,13 +43,12 @@ struct Ctx {
     bool index_valid = false;
     bool index_fresh = false;      // built by the batch in flight: its error bits still have to be checked at sync
     LaunchIndex idx{};
-    DevBuf idx_events, idx_chunks, idx_segs, idx_rend, idx_ctrl;
+    DevBuf idx_events, idx_chunks, idx_segs, idx_rend, idx_ctrl;      // idx_ctrl: index counters, then the batch flags (svtk_capi.cpp ensure_ctl)
     uint64_t idx_n_events = 0, idx_n_segs = 0;
 
     // per-batch scratch
     DevBuf range;        // int2 per window: candidate read range
     DevBuf ov_items;     // int2 per window: (window, signature count) of fast-path overflows
-    DevBuf ov_count;     // [0] overflow count, [1] fail flag, [2..3] arena top
     DevBuf arena;        // global signature segments for windows beyond the big shared segment
     DevBuf counters;     // WorkCounters
     DevBuf scratch4;
@@ -57,7 +56,7 @@ struct Ctx {
     DevBuf tmp_a, tmp_b, tmp_c;
     PinBuf stage[2];
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};
-    PinBuf h_flags, h_idx, h_win, h_result;
+    PinBuf h_idx, h_win, h_result;      // h_idx mirrors idx_ctrl: index counters, then the batch flags
 
     // a launched batch whose overflow windows have not been resolved yet
     bool pending = false;

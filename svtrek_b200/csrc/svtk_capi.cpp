@@ -166,7 +166,7 @@ static int build_index(Ctx *c) {
         // 25% slack for imbalance; grown on demand (resolve_overflow)
         const uint64_t ev = (uint64_t)c->n_words / 16 + 2 * (uint64_t)c->reads.n_reads;
         const uint64_t pool = ev / (uint64_t)index_pools() * 5 / 4 + 1024;
-        if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 64 + 1024, c->idx.seg_cap))) return rc;
+        if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 32 + 1024, c->idx.seg_cap))) return rc;
     }
     CU(cudaMemsetAsync(c->idx_ctrl.p, 0, ctl_index_bytes() + 64, c->stream));     // the batch flags too
     if (c->profile) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
@@ -256,7 +256,7 @@ static int resolve_overflow(Ctx *c) {
             int32_t *res = c->pend_result;
             const int mode = c->pend_mode;
             // every flush bumped its counter even when it found no room: the tops are the exact need
-            if (int rc = ensure_index_buffers(c, (uint64_t)max_pool + 64, c->idx_n_segs + c->idx_n_events / 64 + 1024)) return rc;
+            if (int rc = ensure_index_buffers(c, (uint64_t)max_pool + 64, c->idx_n_segs + c->idx_n_events / 32 + 1024)) return rc;
             c->index_valid = false;
             if (int rc = launch_batch(c, w, res, mode)) return rc;
             CU(cudaStreamSynchronize(c->stream));

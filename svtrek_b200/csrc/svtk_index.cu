@@ -28,6 +28,9 @@
 #ifndef SVTK_IDX_LANE
 #define SVTK_IDX_LANE 0        // 1: k_index_reads_lane (one lane per read, TMA-staged) instead of k_index_reads -- measured slower, see DESIGN.md 7
 #endif
+#ifndef SVTK_IDX_DEFER
+#define SVTK_IDX_DEFER 1       // k_index_reads_defer: marks per step, one resolve pass per 8 steps (else k_index_reads)
+#endif
 #ifndef SVTK_IDX_PREFETCH
 #define SVTK_IDX_PREFETCH 1    // software-pipelined loads
 #endif
@@ -96,7 +99,8 @@ __device__ __forceinline__ uint32_t mad_hi_u32(uint32_t a, uint32_t b, uint32_t 
 }
 
 // append the warp's staged events to the chunk as one more segment; `head` (uniform) is the chunk's newest segment
-__device__ __forceinline__ void index_flush_warp(IndexWarpShared &s, const DevIndex &X, int pool, int nev, uint4 &head) {
+template <class SH>
+__device__ __forceinline__ void index_flush_warp(SH &s, const DevIndex &X, int pool, int nev, uint4 &head) {
     const int lane = lane_id();
     __syncwarp();
     uint32_t fb = 0xffffffffu;
@@ -271,6 +275,319 @@ __global__ void __launch_bounds__(IDX_WARPS * 32, SVTK_IDX_MINB) k_index_reads(D
     if (nev > 0) index_flush_warp(s, X, pool, nev, head);
     if (lane == 0) X.chunks[c] = head;
 }
+
+#if SVTK_IDX_DEFER
+// ---------------------------------------------------------------------------------------------------------
+// k_index_reads_defer: the same index with the per-step work cut to decode + scan.  A step leaves only two things behind,
+// per lane: the cursor before its first word (lanebase) and the 8-bit mask of its signature words (candb).  Every IDX_NS
+// steps (and at the end of the chunk) ONE resolve pass turns the marks into events, one item per lane: the item re-reads its
+// lane's <= 7 preceding words (L1/L2 hits) to rebuild the cursor at the word.  The reads' first words are items of the same
+// pass (they give base[r]).  Against k_index_reads this drops, from every step, the prefix array in shared memory, the second
+// scan, the per-read base lookup and the divergent candidate loop.  Same events, same segments, same rend.
+static_assert(IDX_WPT == 8, "the deferred marks are one byte per lane and step");
+#ifndef SVTK_IDX_NS
+#define SVTK_IDX_NS 8
+#endif
+constexpr int IDX_NS = SVTK_IDX_NS;          // steps between two resolve passes (8: 2 048 words); 4 or 8
+static_assert(IDX_NS == 4 || IDX_NS == 8, "a lane owns IDX_NS mark bytes: one or two words");
+constexpr int IDX_LIST = IDX_TILE + IDX_READS;
+#ifndef SVTK_IDX_STAGE
+#define SVTK_IDX_STAGE 2       // steps each lane keeps in flight through the cp.async ring (0: two-deep register pipeline).  Measured on B200,
+                               // C2: 2 -> 35.8 us (10 CTAs/SM), 3 -> 39.0 (8), 4 -> 40.6 (7), 6 -> 46.8 (5): resident warps beat bytes in flight
+#endif
+constexpr int IDX_STAGE = SVTK_IDX_STAGE;
+#ifndef SVTK_IDX_DEVCAP
+#define SVTK_IDX_DEVCAP 64
+#endif
+constexpr int IDX_DEVCAP = SVTK_IDX_DEVCAP;  // events a warp stages between flushes (>= 32 + 2 * IDX_READS: one resolve round, the clip events)
+static_assert(IDX_DEVCAP >= 32 + 2 * IDX_READS, "event staging too small");
+
+struct __align__(16) IndexDeferShared {
+    uint4 ev[IDX_DEVCAP];
+    uint32_t lanebase[IDX_NS * 32];          // [step * 32 + lane]: cursor (chunk relative) before the lane's first word of the step
+    uint32_t candw[IDX_NS * 8];              // bytes [step * 32 + lane]: which of the lane's 8 words are signatures
+    uint32_t rel[IDX_READS + 4];
+    uint32_t pos[IDX_READS], endp[IDX_READS];
+    uint32_t base[IDX_READS + 1];
+    uint16_t list[IDX_LIST];                 // items of one resolve pass: word id (11 bits) | read << 11 | 0x8000 for a read's first word
+#if SVTK_IDX_STAGE
+    __align__(16) uint4 ring[IDX_STAGE * (IDX_TILE / 4)];   // cp.async staging: IDX_STAGE steps of 1 KB, lane l owns bytes [32 l, 32 l + 32) of each
+#endif
+};
+
+// inclusive warp scan on the shuffle's own in-range predicate: SHFL + predicated IADD per level
+__device__ __forceinline__ uint32_t warp_inclusive_scan_p(uint32_t v) {
+    asm("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, 1, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, 2, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, 4, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, 8, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, 16, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t}"
+        : "+r"(v));
+    return v;
+}
+
+// {advance multiplier, signature threshold} of a CIGAR word's op: one LOP3 for the address, one LDS.64
+__device__ __forceinline__ uint2 optab_lookup(uint32_t tab, uint32_t word) {
+    uint2 ot;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ot.x), "=r"(ot.y) : "r"(((word << 3) & 0x78u) | tab));
+    return ot;
+}
+
+// one resolve pass over the marks of buffered steps: all of them (st < 0; needs <= IDX_TILE marks) or step st alone
+__device__ __forceinline__ void index_resolve(IndexDeferShared &s, const DevIndex &X, const uint32_t *__restrict__ cg, int pool, int &nev,
+                                              uint4 &head, uint32_t tb0, int st, int nsteps, uint32_t head_pad, uint32_t span, int nr,
+                                              long long r0, uint32_t tab) {
+    const int lane = lane_id();
+    const unsigned below = (1u << lane) - 1u;
+    unsigned long long bits;
+    uint32_t base_id, lo_w, hi_w;
+    if (st < 0) {
+        if constexpr (IDX_NS == 8) {
+            const uint2 v = reinterpret_cast<const uint2 *>(s.candw)[lane];
+            bits = (unsigned long long)v.x | ((unsigned long long)v.y << 32);
+        } else bits = s.candw[lane];
+        base_id = (uint32_t)lane * (8u * IDX_NS); lo_w = tb0; hi_w = tb0 + (uint32_t)nsteps * IDX_TILE;
+    } else {
+        bits = reinterpret_cast<const uint8_t *>(s.candw)[st * 32 + lane];
+        base_id = (uint32_t)(st * 32 + lane) * 8u; lo_w = tb0 + (uint32_t)st * IDX_TILE; hi_w = lo_w + IDX_TILE;
+    }
+    const int cnt = __popcll(bits);
+    uint32_t rel = 0xffffffffu;
+    if (lane < nr) rel = s.rel[lane];
+    const bool isstart = rel >= lo_w && rel < hi_w && rel < span;
+    const unsigned ms = __ballot_sync(FULL, isstart);
+    const int ns = __popc(ms);
+    if (isstart) s.list[__popc(ms & below)] = (uint16_t)(0x8000u | ((uint32_t)lane << 11) | (rel - tb0));
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += o; }
+    const int nc = __shfl_sync(FULL, incl, 31);
+    int slot = ns + incl - cnt;
+    while (bits) { const int b = __ffsll((long long)bits) - 1; bits &= bits - 1; s.list[slot++] = (uint16_t)(base_id + (uint32_t)b); }
+    __syncwarp();
+    const int total = ns + nc;
+    for (int j0 = 0; j0 < total; j0 += 32) {
+        const int j = j0 + lane;
+        const int first = j0 ? j0 : ns;                      // first signature item of this round
+        const int nround = min(total, j0 + 32) - first;
+        if (nev + nround > IDX_DEVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
+        const bool act = j < total;
+        uint32_t it = 0x8000u, c = 0, gi = 0;
+        if (act) {
+            it = s.list[j];
+            const uint32_t id = it & 2047u, k = id & 7u;
+            gi = tb0 + id;
+            const uint32_t g0 = gi - k;                      // the owning lane's first word of that step (32-byte aligned)
+            const uint4 *src = reinterpret_cast<const uint4 *>(cg + g0);
+            uint4 a = make_uint4(0u, 0u, 0u, 0u), b = make_uint4(0u, 0u, 0u, 0u);
+            if (k > 0) a = __ldg(src);
+            if (k > 4) b = __ldg(src + 1);
+            const uint32_t w[7] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z};
+            c = s.lanebase[id >> 3];
+#pragma unroll
+            for (int q = 0; q < 7; ++q)
+                if ((uint32_t)q < k && g0 + q >= head_pad) c = mad_hi_u32(w[q], optab_lookup(tab, w[q]).x, c);
+            if (it & 0x8000u) s.base[(it >> 11) & 7u] = c;
+        }
+        __syncwarp();
+        if (!(it & 0x8000u)) {
+            const uint4 ra = *reinterpret_cast<const uint4 *>(&s.rel[0]), rb = *reinterpret_cast<const uint4 *>(&s.rel[4]);
+            const int r = (int)(ra.y <= gi) + (int)(ra.z <= gi) + (int)(ra.w <= gi) + (int)(rb.x <= gi) + (int)(rb.y <= gi) +
+                          (int)(rb.z <= gi) + (int)(rb.w <= gi);
+            const uint32_t word = __ldg(cg + gi);
+            const uint32_t x = s.pos[r] + (c - s.base[r]);
+            const uint32_t type = ((word & 15u) == (uint32_t)OP_DEL) ? EV_DEL : EV_INS;
+            s.ev[nev + j - first] = make_uint4(x, (word & ~15u) | type, (uint32_t)(r0 + r), s.endp[r]);
+        }
+        nev += nround;
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ void index_resolve_all(IndexDeferShared &s, const DevIndex &X, const uint32_t *__restrict__ cg, int pool, int &nev,
+                                                  uint4 &head, uint32_t tb0, int nsteps, uint32_t head_pad, uint32_t span, int nr,
+                                                  long long r0, uint32_t tab) {
+    const int lane = lane_id();
+    __syncwarp();
+    int mine;
+    if constexpr (IDX_NS == 8) { const uint2 v = reinterpret_cast<const uint2 *>(s.candw)[lane]; mine = __popc(v.x) + __popc(v.y); }
+    else mine = __popc(s.candw[lane]);
+    const int tot = __reduce_add_sync(FULL, mine);
+    if (tot <= IDX_TILE) index_resolve(s, X, cg, pool, nev, head, tb0, -1, nsteps, head_pad, span, nr, r0, tab);
+    else
+        for (int st = 0; st < nsteps; ++st) index_resolve(s, X, cg, pool, nev, head, tb0, st, nsteps, head_pad, span, nr, r0, tab);
+    if constexpr (IDX_NS == 8) reinterpret_cast<uint2 *>(s.candw)[lane] = make_uint2(0u, 0u);
+    else s.candw[lane] = 0u;
+    __syncwarp();
+}
+
+#ifndef SVTK_IDX_DMINB
+#define SVTK_IDX_DMINB 10       // 48 registers, 20 KB of shared memory per CTA: 40 warps per SM (12 CTAs at 40 registers spill: 43 us)
+#endif
+__global__ void __launch_bounds__(IDX_WARPS * 32, SVTK_IDX_DMINB) k_index_reads_defer(DevReads R, DevIndex X) {
+    __shared__ IndexDeferShared sh[IDX_WARPS];
+    __shared__ __align__(128) uint2 optab[16];               // one per CTA: every warp writes the same 16 entries, then reads after its own __syncwarp
+    const int lane = lane_id(), warp = threadIdx.x >> 5;
+    const long long c = (long long)blockIdx.x * IDX_WARPS + warp;
+    if (c >= X.n_chunks) return;
+    IndexDeferShared &s = sh[warp];
+    const int pool = (int)(blockIdx.x % IDX_POOLS);
+    const long long r0 = c * IDX_READS;
+    const int nr = (int)min((long long)IDX_READS, R.n_reads - r0);
+    unsigned long long off = 0;
+    if (lane <= nr) {
+        const long long r = r0 + lane;
+        off = (lane < nr) ? __ldg(R.cigar_off + r) : __ldg(R.cigar_off + r - 1) + __ldg(R.n_cigar + r - 1);
+        if (lane < nr) { s.pos[lane] = __ldg(R.pos + r); s.endp[lane] = __ldg(R.end + r); }
+    }
+    const unsigned long long w0 = __shfl_sync(FULL, off, 0);
+    const unsigned long long w0a = w0 & ~3ull;
+    if (lane < IDX_READS + 4) s.rel[lane] = lane <= nr ? (uint32_t)(off - w0a) : 0xffffffffu;
+    if (lane < 16) {
+        const uint32_t adv = (lane == OP_INS || lane == OP_SOFT) ? 0u : (1u << 28);
+        const uint32_t thr = lane == OP_INS ? ((uint32_t)SV_MIN_LENGTH << 4 | OP_INS)
+                           : lane == OP_DEL ? ((uint32_t)(SV_MIN_LENGTH + 1) << 4 | OP_DEL) : 0xffffffffu;
+        optab[lane] = make_uint2(adv, thr);
+    }
+    if constexpr (IDX_NS == 8) reinterpret_cast<uint2 *>(s.candw)[lane] = make_uint2(0u, 0u);
+    else s.candw[lane] = 0u;
+    __syncwarp();
+    const uint32_t head_pad = (uint32_t)(w0 - w0a);
+    const uint32_t span = s.rel[nr];
+    const uint32_t *__restrict__ cg = R.cigar + w0a;
+    uint4 head = make_uint4(0u, 0u, 0xffffffffu, s.pos[0]);
+    uint8_t *candb = reinterpret_cast<uint8_t *>(s.candw);
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(optab);
+
+    uint32_t run = 0;       // cursor advance of all words before the current step (uniform)
+    int nev = 0;            // staged events (uniform)
+    int sidx = 0;           // buffered steps (uniform)
+#if SVTK_IDX_STAGE
+    // Asynchronous staging: every lane keeps IDX_STAGE steps of its own 32-byte pieces in flight with 16-byte cp.async copies
+    // into a per-warp ring in shared memory (no registers held by loads in flight: the kernel is bound by bytes in flight, not
+    // by issue slots).  A lane reads back only what it copied itself, so cp.async.wait_group is the only synchronisation.  A
+    // piece that starts at or beyond `span` is not copied; the stale ring contents are blanked by the edge rule below.
+    const uint32_t ring = (uint32_t)__cvta_generic_to_shared(s.ring) + (uint32_t)lane * 32u;
+    const uint32_t *__restrict__ np = cg + lane * IDX_WPT;
+    uint32_t ni = (uint32_t)lane * IDX_WPT;                  // word index of the lane's next piece to copy
+    int wslot = 0;
+    auto issue = [&]() {
+        const uint32_t dst = ring + (uint32_t)wslot * (IDX_TILE * 4u);
+        if (ni < span) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(np) : "memory");
+        if (ni + 4u < span) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u), "l"(np + 4) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        np += IDX_TILE; ni += IDX_TILE;
+        wslot = (wslot + 1 == IDX_STAGE) ? 0 : wslot + 1;
+    };
+#pragma unroll
+    for (int t = 0; t < IDX_STAGE; ++t) issue();
+    uint32_t i0 = (uint32_t)lane * IDX_WPT;
+    for (uint32_t tb = 0; tb < span; tb += IDX_TILE, i0 += IDX_TILE) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(IDX_STAGE - 1) : "memory");
+        uint32_t w[IDX_WPT];
+        {
+            const uint32_t src = ring + (uint32_t)wslot * (IDX_TILE * 4u);   // the oldest slot == the one the next copy reuses
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(src) : "memory");
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(src + 16u) : "memory");
+        }
+        issue();
+        // edge steps: blank the neighbouring chunks' words ("0M", inert).  head_pad <= 3: only lane 0's first words of step 0
+        if (i0 == 0u) { if (head_pad > 0u) w[0] = 0u; if (head_pad > 1u) w[1] = 0u; if (head_pad > 2u) w[2] = 0u; }
+        if (tb + IDX_TILE > span) {
+            const int rem = (int)(span - i0);                // < 8: words from `rem` on are not this chunk's (<= 0: all of them)
+#pragma unroll
+            for (int k = 0; k < IDX_WPT; ++k) if (k >= rem) w[k] = 0u;
+        }
+        uint32_t sum = 0;
+        unsigned candm = 0;
+#pragma unroll
+        for (int k = 0; k < IDX_WPT; ++k) {
+            const uint2 ot = optab_lookup(tab, w[k]);
+            sum = mad_hi_u32(w[k], ot.x, sum);               // += len for ops that advance (refinement.c:137)
+            if (w[k] >= ot.y) candm |= 1u << k;              // I >= 50 (refinement.c:299), D > 50 (refinement.c:124)
+        }
+        const uint32_t incl = warp_inclusive_scan_p(sum);
+        s.lanebase[sidx * 32 + lane] = run + (incl - sum);
+        candb[sidx * 32 + lane] = (uint8_t)candm;
+        run += __shfl_sync(FULL, incl, 31);
+        if (++sidx == IDX_NS) {
+            index_resolve_all(s, X, cg, pool, nev, head, tb + IDX_TILE - IDX_NS * IDX_TILE, IDX_NS, head_pad, span, nr, r0, tab);
+            sidx = 0;
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#else
+    // software pipeline: the next step's 32 bytes per lane are in flight while this step is decoded.  A piece that starts at
+    // or beyond `span` is not loaded; its stale register contents are blanked by the edge rule below (every word >= span).
+    uint4 A0 = make_uint4(0u, 0u, 0u, 0u), A1 = A0, B0 = A0, B1 = A0;
+    const uint4 *__restrict__ np = reinterpret_cast<const uint4 *>(cg + lane * IDX_WPT);
+    uint32_t ni = (uint32_t)lane * IDX_WPT;                  // word index of the lane's next piece
+    if (ni < span) A0 = __ldg(np);
+    if (ni + 4u < span) A1 = __ldg(np + 1);
+    // one step: decode the pieces (c0, c1) while the next step's pieces load into (n0, n1)
+    auto step = [&](const uint4 &c0, const uint4 &c1, uint4 &n0, uint4 &n1, const uint32_t tb) {
+        const uint32_t i0 = ni;
+        uint32_t w[IDX_WPT] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+        np += IDX_TILE / 4; ni += IDX_TILE;
+        if (ni < span) n0 = __ldg(np);
+        if (ni + 4u < span) n1 = __ldg(np + 1);
+        if (tb == 0 || tb + IDX_TILE > span) {               // edge steps: blank the neighbouring chunks' words ("0M", inert)
+#pragma unroll
+            for (int k = 0; k < IDX_WPT; ++k) { const uint32_t gi = i0 + k; if (gi < head_pad || gi >= span) w[k] = 0u; }
+        }
+        uint32_t sum = 0;
+        unsigned candm = 0;
+#pragma unroll
+        for (int k = 0; k < IDX_WPT; ++k) {
+            const uint2 ot = optab_lookup(tab, w[k]);
+            sum = mad_hi_u32(w[k], ot.x, sum);               // += len for ops that advance (refinement.c:137)
+            if (w[k] >= ot.y) candm |= 1u << k;              // I >= 50 (refinement.c:299), D > 50 (refinement.c:124)
+        }
+        const uint32_t incl = warp_inclusive_scan_p(sum);
+        s.lanebase[sidx * 32 + lane] = run + (incl - sum);
+        candb[sidx * 32 + lane] = (uint8_t)candm;
+        run += __shfl_sync(FULL, incl, 31);
+        ++sidx;
+    };
+    // two steps per trip (the piece registers ping-pong, no copies); IDX_NS is even, so a full buffer is seen after the pair
+    for (uint32_t tb = 0; tb < span; tb += 2 * IDX_TILE) {
+        step(A0, A1, B0, B1, tb);
+        if (tb + IDX_TILE < span) step(B0, B1, A0, A1, tb + IDX_TILE);
+        if (sidx == IDX_NS) {
+            index_resolve_all(s, X, cg, pool, nev, head, tb + 2 * IDX_TILE - IDX_NS * IDX_TILE, IDX_NS, head_pad, span, nr, r0, tab);
+            sidx = 0;
+        }
+    }
+#endif  // SVTK_IDX_STAGE
+    if (sidx) index_resolve_all(s, X, cg, pool, nev, head, (span + IDX_TILE - 1) / IDX_TILE * IDX_TILE - (uint32_t)sidx * IDX_TILE, sidx,
+                                head_pad, span, nr, r0, tab);
+    // reads that start at the very end of the chunk's span (empty CIGARs) and the end-of-span sentinel
+    if (lane <= nr && s.rel[lane] >= span) s.base[lane] = run;
+    __syncwarp();
+    if (nev + 2 * IDX_READS > IDX_DEVCAP) { index_flush_warp(s, X, pool, nev, head); nev = 0; }
+    bool tclip = false, lclip = false;
+    uint32_t rendv = 0;
+    if (lane < nr) {
+        const uint32_t n = s.rel[lane + 1] - s.rel[lane];
+        rendv = s.pos[lane];
+        if (n > 0) {
+            rendv += s.base[lane + 1] - s.base[lane];
+            const uint32_t first = __ldg(cg + s.rel[lane]), last = __ldg(cg + s.rel[lane + 1] - 1);
+            tclip = (last & 15u) == (uint32_t)OP_SOFT;       // refinement.c:120,147: trailing soft clip, value = final cursor
+            lclip = (first & 15u) == (uint32_t)OP_SOFT;      // refinement.c:210: leading soft clip, keyed by core.pos
+        }
+        X.rend[r0 + lane] = rendv;
+    }
+    const unsigned mt = __ballot_sync(FULL, tclip), ml = __ballot_sync(FULL, lclip);
+    const unsigned below = (1u << lane) - 1u;
+    if (tclip) s.ev[nev + __popc(mt & below)] = make_uint4(rendv, EV_TCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
+    if (lclip) s.ev[nev + __popc(mt) + __popc(ml & below)] = make_uint4(s.pos[lane], EV_LCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
+    nev += __popc(mt) + __popc(ml);
+    if (nev > 0) index_flush_warp(s, X, pool, nev, head);
+    if (lane == 0) X.chunks[c] = head;
+}
+#endif  // SVTK_IDX_DEFER
 
 #if SVTK_IDX_LANE
 // ---------------------------------------------------------------------------------------------------------
@@ -827,6 +1144,8 @@ cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaS
         if (e != cudaSuccess) return e;
     }
     k_index_reads_lane<<<(unsigned)((warps + LANE_WARPS - 1) / LANE_WARPS), LANE_WARPS * 32, smem, s>>>(to_dev(r), to_dev(x));
+#elif SVTK_IDX_DEFER
+    k_index_reads_defer<<<(x.n_chunks + IDX_WARPS - 1) / IDX_WARPS, IDX_WARPS * 32, 0, s>>>(to_dev(r), to_dev(x));
 #else
     k_index_reads<<<(x.n_chunks + IDX_WARPS - 1) / IDX_WARPS, IDX_WARPS * 32, 0, s>>>(to_dev(r), to_dev(x));
 #endif

@@ -124,7 +124,7 @@ static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     const long long nr = c->reads.n_reads;
     const int per = index_reads_per_chunk();
     const long long n_chunks = (nr + per - 1) / per;
-    const uint64_t ev_cap = pool_cap * (uint64_t)index_pools();
+    const uint64_t ev_cap = pool_cap * (uint64_t)index_pools() + (uint64_t)n_chunks * (uint64_t)index_fixed_slots();
     if (ev_cap >= (1ull << 31) || seg_cap >= (1ull << 31)) return fail(SVTK_ERR_ARG, "signature index beyond 2^31 events: shard the read set");
     if (int rc = c->idx_events.reserve(16 * (size_t)ev_cap)) return rc;
     if (int rc = c->idx_chunks.reserve(16 * (size_t)std::max(n_chunks, 1ll))) return rc;
@@ -241,6 +241,7 @@ static void index_totals(const Ctx *c, uint64_t *events, uint64_t *segs, unsigne
     const int st = index_ctrl_stride(), np = index_pools();
     uint64_t ev = 0; unsigned int mx = 0;
     for (int p = 0; p < np; ++p) { ev += ctrl[p * st]; mx = std::max(mx, ctrl[p * st]); }
+    if (index_fixed_slots()) for (int p = 0; p < np; ++p) ev += ctrl[p * st + 1];          // events in the chunks' own slots
     *events = ev; *segs = ctrl[np * st]; *max_pool = mx; *err = ctrl[(np + 1) * st];
 }
 

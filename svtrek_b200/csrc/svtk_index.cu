@@ -296,6 +296,11 @@ constexpr int IDX_LIST = IDX_TILE + IDX_READS;
                                // C2: 2 -> 35.8 us (10 CTAs/SM), 3 -> 39.0 (8), 4 -> 40.6 (7), 6 -> 46.8 (5): resident warps beat bytes in flight
 #endif
 constexpr int IDX_STAGE = SVTK_IDX_STAGE;
+#ifndef SVTK_IDX_FIXK
+#define SVTK_IDX_FIXK 32        // event slots every chunk owns behind the sub-pools (<= 32: one store per lane); 0: always allocate
+#endif
+constexpr int IDX_FIXK = SVTK_IDX_FIXK;
+static_assert(IDX_FIXK <= 32, "one lane per fixed slot");
 #ifndef SVTK_IDX_DEVCAP
 #define SVTK_IDX_DEVCAP 64
 #endif
@@ -584,6 +589,16 @@ __global__ void __launch_bounds__(IDX_WARPS * 32, SVTK_IDX_DMINB) k_index_reads_
     if (tclip) s.ev[nev + __popc(mt & below)] = make_uint4(rendv, EV_TCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
     if (lclip) s.ev[nev + __popc(mt) + __popc(ml & below)] = make_uint4(s.pos[lane], EV_LCLIP, (uint32_t)(r0 + lane), s.endp[lane]);
     nev += __popc(mt) + __popc(ml);
+#if SVTK_IDX_FIXK
+    // A chunk whose events all fit its own IDX_FIXK slots (behind the sub-pools) needs no allocation: no atomic round trip at
+    // the end of the warp's life, only a fire-and-forget count (second word of the sub-pool's control line) for the totals.
+    if (nev > 0 && nev <= IDX_FIXK && head.y == 0u) {
+        const uint32_t fb = (uint32_t)IDX_POOLS * X.pool_cap + (uint32_t)c * (uint32_t)IDX_FIXK;
+        if (lane == 0) atomicAdd(&X.ctrl[pool * CTRL_STRIDE + 1], (unsigned int)nev);
+        if (lane < nev) X.events[(size_t)fb + lane] = s.ev[lane];
+        head = make_uint4(fb, (uint32_t)nev, 0xffffffffu, head.w);
+    } else
+#endif
     if (nev > 0) index_flush_warp(s, X, pool, nev, head);
     if (lane == 0) X.chunks[c] = head;
 }
@@ -880,7 +895,10 @@ struct IndexCounters {                // instrumented instantiation only
 // ---------------------------------------------------------------------------------------------------------
 // One warp per window.  Windows with more than RW_CAP signatures go to the overflow list (window, exact count).
 template <bool STATS>
-__global__ void __launch_bounds__(RW_WARPS * 32) k_refine_warp(DevReads R, DevWindows W, DevIndex X, Tunables t, int32_t *__restrict__ result,
+#ifndef SVTK_RW_MINB
+#define SVTK_RW_MINB 12
+#endif
+__global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(DevReads R, DevWindows W, DevIndex X, Tunables t, int32_t *__restrict__ result,
                                                                OverflowList ov, int2 *__restrict__ range_out, IndexCounters *ic) {
     __shared__ RefineWarpShared sh[RW_WARPS];
     const int lane = lane_id(), warp = threadIdx.x >> 5;
@@ -1121,6 +1139,7 @@ constexpr int RB_NT = 1024;
 
 int index_reads_per_chunk() { return IDX_READS; }
 int index_pools() { return IDX_POOLS; }
+int index_fixed_slots() { return (SVTK_IDX_DEFER && !SVTK_IDX_LANE) ? SVTK_IDX_FIXK : 0; }
 int index_ctrl_words() { return CTRL_ERR + CTRL_STRIDE; }
 int index_ctrl_stride() { return CTRL_STRIDE; }
 int refine_block_segment_ints() { return 32768; }      // power of two: the bitonic sort pads a segment to next_pow2(n)

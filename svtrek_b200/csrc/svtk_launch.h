@@ -33,7 +33,7 @@ struct LaunchWindows {          // device pointers
 };
 
 struct LaunchIndex {            // the signature index built by k_index_reads (device pointers)
-    void *events;               // uint4 per event; index_pools() sub-pools of pool_cap events each
+    void *events;               // uint4 per event; index_pools() sub-pools of pool_cap events each, then index_fixed_slots() per chunk
     void *chunks;               // uint4 per chunk of index_reads_per_chunk() reads
     void *segs;                 // uint4 per extra segment
     uint32_t *rend;             // per read
@@ -44,6 +44,7 @@ struct LaunchIndex {            // the signature index built by k_index_reads (d
 
 int index_reads_per_chunk();
 int index_pools();
+int index_fixed_slots();      // event slots per chunk behind the sub-pools (0: none); their counts live in ctrl[p * stride + 1]
 int index_ctrl_words();
 int index_ctrl_stride();
 int refine_block_segment_ints();

@@ -489,7 +489,7 @@ def run_ours(args):
             out["e2e"]["file_to_file_records_per_s"] = out["bam_e2e"].get("value")
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_port_baseline(rs, w, n_records)
-        print(json.dumps(out), flush=True)
+        emit(out)
     a.close()
     if world > 1:
         dist.barrier()
@@ -629,11 +629,29 @@ def run_reference(args):
                      "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
                                       "sample": "oracle/_ref missing: oracle/svtk_oracle.c orc_refine_batch on decoded reads, 1 thread"},
                      "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-    print(json.dumps(base), flush=True)
+    emit(base)
+
+
+_JSON_FD = None
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
 
 
 def main():
+    global _JSON_FD
     args = parse_args()
+    # Libraries write banners to fd 1 (NCCL prints "NCCL version ..." there when NCCL_DEBUG=VERSION is set on the box, child
+    # processes of the reference arm inherit it): everything that is not the JSON line goes to stderr.
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

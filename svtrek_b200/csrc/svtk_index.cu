@@ -879,7 +879,10 @@ __device__ __forceinline__ void warp_sort_segment(int *a, int n) {
     __syncwarp();
 }
 
-constexpr int RW_WARPS = 4;            // windows per CTA of k_refine_warp
+#ifndef SVTK_RW_WARPS
+#define SVTK_RW_WARPS 4
+#endif
+constexpr int RW_WARPS = SVTK_RW_WARPS;            // windows per CTA of k_refine_warp
 constexpr int RW_CAP = 256;            // signatures a warp sorts in registers (8 per lane)
 constexpr int RW_DEFER = 8;
 

@@ -462,6 +462,8 @@ def run_ours(args):
                                        "k_refine_indexed: 16 B/event scanned + 16 B/segment + 28 B/window (DESIGN.md)",
                          "work": stats},
             "roofline_other": {"kernel": oth, "achieved": kern[oth][1] / (kern[oth][0] * 1e-3) / 1e9 if kern[oth][0] > 0 else 0.0, "unit": "GB/s",
+                               "peak": peak, "frac": (kern[oth][1] / (kern[oth][0] * 1e-3) / 1e9 / peak) if kern[oth][0] > 0 and peak else None,
+                               "note": "the step's two kernels take about the same time; `roofline` is whichever ran longer in this run",
                                "algorithmic_bytes_per_launch": kern[oth][1], "kernel_ms": kern[oth][0], "traffic": (tr or {}).get(oth)},
             "reference_equivalent": {"note": "bytes the reference's per-(window, read) walks touch (SURVEY.md 8d) / time of both kernels",
                                      "bytes_per_step": walker["algorithmic_bytes"], "GBps": walker["algorithmic_bytes"] / ((idx_ms + ref_ms) * 1e-3) / 1e9 if (idx_ms + ref_ms) > 0 else 0.0,

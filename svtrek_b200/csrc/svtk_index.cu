@@ -7,11 +7,12 @@
 //     - the clip rules compare the read's start / final cursor with [W.start, W.end]  (:147-159, :210-221)
 // so the walk itself is window independent.  This file splits the path accordingly:
 //
-//   k_index_reads     ONE coalesced pass over all CIGAR words (HBM-bound): a warp owns a chunk of 8 consecutive
-//                     reads, streams their packed CIGAR words with 128-bit loads, 256 words per step, keeps the
-//                     reference cursor with a warp scan, and emits the chunk's signature events
-//                     {cursor, len|type, read, endpos} -- D > 50, I >= 50, trailing / leading soft clip -- plus
-//                     every read's final cursor.  No block-level barrier anywhere.
+//   k_index_reads_defer  ONE coalesced pass over all CIGAR words (the product kernel): a warp owns a chunk of 8 consecutive
+//                     reads and streams their packed CIGAR words, 256 per step, through a cp.async ring; a step is decode +
+//                     warp scan and leaves only per-lane marks; one resolve pass per 8 steps turns the marks into the
+//                     chunk's signature events {cursor, len|type, read, endpos} -- D > 50, I >= 50, trailing / leading soft
+//                     clip -- plus every read's final cursor.  No block-level barrier anywhere.
+//   k_index_reads     the earlier form of the same pass (events resolved inside every step); SVTK_IDX_DEFER=0 builds.
 //   k_refine_warp     one WARP per window: 32-ary search of the read range the BAM iterator would yield
 //                     (hts.c:3049-3090, 3905-3921), gather of the covering chunks' events under the two rules
 //                     above, register bitonic sort (<= 256 signatures), consensus_pos (refinement.c:41-101).

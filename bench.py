@@ -362,7 +362,10 @@ def run_ours(args):
     sampler = NvmlSampler(local)
     barrier()
     sampler.start()
-    a.set_profiling(True)
+    # per-kernel CUDA events live inside the timed region, on every prof_stride-th step: an event pair serialises the stream
+    # around its kernel (B200, C2: a step is 92.8 us with both pairs on every step, 77.5 us without any -- tools/step_overhead.py)
+    prof_stride = max(1, min(4, K // 4))
+    a.set_profiling(prof_stride)
     launches0 = a.launch_count
     evs = []
     t_wall0 = time.perf_counter()
@@ -447,6 +450,10 @@ def run_ours(args):
                        "records_per_gpu": n_records, "windows_per_gpu": n_win, "reads_per_gpu": n_reads, "cigar_words_per_gpu": n_words,
                        "sharding": "one region shard (own contig) per GPU, no collective" if world > 1 else "single GPU",
                        "l2": "256 MB buffer written between timed steps (L2 flush); CIGAR array is %.0f MB" % (4 * n_words / 1e6),
+                       "kernel_timing": "CUDA event pairs around k_index_reads and k_refine_warp on every %d%s timed step (%d and %d launches timed); "
+                                        "all %d steps are inside the step events that give `value`" % (
+                                            prof_stride, "th" if prof_stride > 3 else ("st" if prof_stride == 1 else "nd" if prof_stride == 2 else "rd"),
+                                            tim["index_kernel_launches"], tim["refine_kernel_launches"], K),
                        "params": "wider 20000, median 10000, narrow 2000, range 500, interval 5, min-count 3 (params.h defaults)"},
             "clocks": clocks,
             "e2e": {"value": rec_all * K / (e2e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),

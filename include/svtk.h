@@ -207,8 +207,9 @@ int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t
 int svtk_sync(svtk_ctx *ctx);
 /* number of kernel launches this ctx has issued so far */
 uint64_t svtk_launch_count(const svtk_ctx *ctx);
-/* bracket every fused refinement kernel with CUDA events (on = 1) and read the running totals; switching
- * profiling on or off resets them.  No reference counterpart: measurement aid for bench.py's roofline. */
+/* bracket every index / refinement kernel launch with CUDA events (on = 1), or every on-th launch of each (on > 1:
+ * a timing event pair serialises the stream around the kernel, ~4 us each on B200), and read the running totals;
+ * switching profiling on or off resets them.  No reference counterpart: measurement aid for bench.py's roofline. */
 int svtk_set_profiling(svtk_ctx *ctx, int on);
 int svtk_get_timing(svtk_ctx *ctx, svtk_timing *timing);
 /* The product path walks every CIGAR once (the "signature index": one coalesced pass over the resident reads) and

@@ -240,7 +240,8 @@ class Auditor:
         return int(self.lib.svtk_launch_count(self.ctx))
 
     def set_profiling(self, on=True):
-        _check(self.lib.svtk_set_profiling(self.ctx, 1 if on else 0))
+        """True / 1: CUDA events around every index / refine kernel launch; n > 1: around every n-th launch of each; False: off."""
+        _check(self.lib.svtk_set_profiling(self.ctx, int(on)))
 
     def timing(self):
         t = Timing()

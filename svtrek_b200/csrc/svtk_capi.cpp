@@ -169,9 +169,10 @@ static int build_index(Ctx *c) {
         if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 32 + 1024, c->idx.seg_cap))) return rc;
     }
     CU(cudaMemsetAsync(c->idx_ctrl.p, 0, ctl_index_bytes() + 64, c->stream));     // the batch flags too
-    if (c->profile) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
+    const bool prof = c->profile && (c->prof_tick_idx++ % (unsigned long long)c->prof_stride) == 0;
+    if (prof) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
     CU(launch_index_reads(c->reads, c->idx, c->stream));
-    if (c->profile) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
+    if (prof) { CU(cudaEventRecord(c->prof_ev[3], c->stream)); c->prof_idx_pending = true; }
     c->launches += c->reads.n_reads > 0;
     c->index_valid = true;
     c->index_fresh = true;
@@ -209,14 +210,15 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
         c->launches += 2;
     } else {
         if (!c->index_valid) if (int rc = build_index(c)) return rc;
-        if (c->profile) {
+        const bool prof = c->profile && (c->prof_tick_ref++ % (unsigned long long)c->prof_stride) == 0;
+        if (prof) {
             if (int rc = collect_timing(c, 1)) return rc;
             CU(cudaEventRecord(c->prof_ev[0], c->stream));
         }
         CU(launch_refine_indexed(c->reads, w, c->idx, (int2 *)c->range.p, c->params.consensus_interval_range, c->params.consensus_interval,
                                  c->params.consensus_min_count, dev_result, ov_flags(c), (int2 *)c->ov_items.p, w.n_win, counters,
                                  c->stream));
-        if (c->profile) {
+        if (prof) {
             CU(cudaEventRecord(c->prof_ev[1], c->stream));
             c->prof_pending = true;
         }
@@ -463,6 +465,8 @@ int svtk_set_profiling(svtk_ctx *ctx, int on) {
         for (int i = 0; i < 4; ++i) CU(cudaEventCreate(&c->prof_ev[i]));
     if (int rc = collect_timing(c)) return rc;
     c->profile = on != 0;
+    c->prof_stride = on > 1 ? on : 1;
+    c->prof_tick_idx = c->prof_tick_ref = 0;
     c->refine_ms = c->index_ms = 0.0; c->refine_launches = c->index_launches = 0;
     return 0;
 }

@@ -92,6 +92,8 @@ struct Ctx {
 
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;
+    int prof_stride = 1;                       // bracket every prof_stride-th index build / refine launch (svtk_set_profiling(ctx, n))
+    unsigned long long prof_tick_idx = 0, prof_tick_ref = 0;
     cudaEvent_t prof_ev[4] = {nullptr, nullptr, nullptr, nullptr};     // [0,1] refine kernel, [2,3] index kernel
     double refine_ms = 0.0, index_ms = 0.0;
     uint64_t refine_launches = 0, index_launches = 0;

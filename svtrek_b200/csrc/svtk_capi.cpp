@@ -112,11 +112,17 @@ static int finish_reads(Ctx *c) {
 // ---- control block: the index counters followed by the batch flags, so that a step which builds the index clears both with
 // one memset and reads both back with one copy.  flags: [0] overflow count  [1] fail flag  [2..3] arena top (u64)
 static size_t ctl_index_bytes() { return 4 * (size_t)index_ctrl_words(); }
+// Two blocks on the device: an index build flips to the other one, and the index kernel itself clears the block the NEXT build
+// will use (index_zeroes_next_ctrl), so a steady stream of builds issues no memset.  ctl_clean[b]: block b is known to be zero.
+static size_t ctl_block_bytes() { return (ctl_index_bytes() + 64 + 255) & ~(size_t)255; }
 static int ensure_ctl(Ctx *c) {
-    if (int rc = c->idx_ctrl.reserve(ctl_index_bytes() + 64)) return rc;
+    const void *before = c->idx_ctrl.p;
+    if (int rc = c->idx_ctrl.reserve(2 * ctl_block_bytes())) return rc;
+    if (c->idx_ctrl.p != before) c->ctl_clean[0] = c->ctl_clean[1] = false;
     return c->h_idx.reserve(ctl_index_bytes() + 64);
 }
-static int *ov_flags(Ctx *c) { return (int *)((char *)c->idx_ctrl.p + ctl_index_bytes()); }
+static char *ctl_base(Ctx *c, int which) { return (char *)c->idx_ctrl.p + (size_t)which * ctl_block_bytes(); }
+static int *ov_flags(Ctx *c) { return (int *)(ctl_base(c, c->ctl_cur) + ctl_index_bytes()); }
 static int *host_flags(Ctx *c) { return (int *)((char *)c->h_idx.p + ctl_index_bytes()); }
 
 // ---- signature index (svtk_index.cu)
@@ -131,8 +137,8 @@ static int ensure_index_buffers(Ctx *c, uint64_t pool_cap, uint64_t seg_cap) {
     if (int rc = c->idx_segs.reserve(16 * (size_t)seg_cap)) return rc;
     if (int rc = c->idx_rend.reserve(4 * (size_t)std::max(nr, 1ll))) return rc;
     if (int rc = ensure_ctl(c)) return rc;
-    c->idx = LaunchIndex{c->idx_events.p, c->idx_chunks.p, c->idx_segs.p, (uint32_t *)c->idx_rend.p, (unsigned int *)c->idx_ctrl.p,
-                         (unsigned int)pool_cap, (unsigned int)seg_cap, (int)n_chunks};
+    c->idx = LaunchIndex{c->idx_events.p, c->idx_chunks.p, c->idx_segs.p, (uint32_t *)c->idx_rend.p, (unsigned int *)ctl_base(c, c->ctl_cur),
+                         (unsigned int)pool_cap, (unsigned int)seg_cap, (int)n_chunks, nullptr, 0};
     return 0;
 }
 
@@ -168,7 +174,17 @@ static int build_index(Ctx *c) {
         const uint64_t pool = ev / (uint64_t)index_pools() * 5 / 4 + 1024;
         if (int rc = ensure_index_buffers(c, std::max<uint64_t>(pool, c->idx.pool_cap), std::max<uint64_t>(ev / 32 + 1024, c->idx.seg_cap))) return rc;
     }
-    CU(cudaMemsetAsync(c->idx_ctrl.p, 0, ctl_index_bytes() + 64, c->stream));     // the batch flags too
+    // counters and batch flags of this build live in the other control block: already cleared by the previous build's kernel
+    // (steady state), else by a memset here
+    const bool kz = index_zeroes_next_ctrl() != 0 && c->reads.n_reads > 0;
+    c->ctl_cur ^= 1;
+    if (!c->ctl_clean[c->ctl_cur]) CU(cudaMemsetAsync(ctl_base(c, c->ctl_cur), 0, ctl_index_bytes() + 64, c->stream));
+    c->idx.ctrl = (unsigned int *)ctl_base(c, c->ctl_cur);
+    c->idx.next_ctrl = kz ? (unsigned int *)ctl_base(c, c->ctl_cur ^ 1) : nullptr;
+    c->idx.next_words = (int)((ctl_index_bytes() + 64) / 4);
+    c->ctl_clean[c->ctl_cur] = false;
+    c->ctl_clean[c->ctl_cur ^ 1] = kz;
+    c->flags_clean = true;
     const bool prof = c->profile && (c->prof_tick_idx++ % (unsigned long long)c->prof_stride) == 0;
     if (prof) { if (int rc = collect_timing(c, 2)) return rc; CU(cudaEventRecord(c->prof_ev[2], c->stream)); }
     CU(launch_index_reads(c->reads, c->idx, c->stream));
@@ -194,7 +210,8 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
     c->pending = false;
     if (w.n_win <= 0) return 0;
     const bool with_index = mode != MODE_WALKER_STATS && !c->index_valid;      // build_index clears the whole control block
-    if (!with_index) CU(cudaMemsetAsync(ov_flags(c), 0, 64, c->stream));
+    // an index built by an explicit svtk_index_reads since the last batch cleared the flags with its counters
+    if (!with_index && !c->flags_clean) CU(cudaMemsetAsync(ov_flags(c), 0, 64, c->stream));
     unsigned long long *counters = nullptr;
     if (mode != MODE_INDEXED) {
         if (int rc = c->counters.reserve(64)) return rc;
@@ -225,9 +242,10 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
         c->launches += 1;
     }
     if (mode != MODE_WALKER_STATS && c->index_fresh)
-        CU(cudaMemcpyAsync(c->h_idx.p, c->idx_ctrl.p, ctl_index_bytes() + 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_idx.p, ctl_base(c, c->ctl_cur), ctl_index_bytes() + 4, cudaMemcpyDeviceToHost, c->stream));
     else
         CU(cudaMemcpyAsync(host_flags(c), ov_flags(c), 4, cudaMemcpyDeviceToHost, c->stream));
+    c->flags_clean = false;                                   // this batch's kernels own the flags now (a build inside it set it)
     c->pending = true;
     c->pend_mode = mode;
     c->pend_win = w;
@@ -669,6 +687,7 @@ int svtk_window_signatures(svtk_ctx *ctx, int kind, int chrom, svtk_interval int
     LaunchWindows lw;
     if (int rc = upload_windows(c, &w, &lw)) return rc;
     if (int rc = ensure_batch(c, 1)) return rc;
+    c->flags_clean = false;                                  // this entry point uses the batch flags as its own counter
     CU(launch_plan(c->reads, lw, (int2 *)c->range.p, c->stream));
     c->launches += 1;
     long long buf_ints = 1 << 16;
@@ -721,6 +740,7 @@ int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int w
     LaunchWindows lw;
     if (int rc = upload_windows(c, &w, &lw)) return rc;
     if (int rc = ensure_batch(c, nt)) return rc;
+    c->flags_clean = false;                                  // this entry point uses the batch flags as its own counter
     if (int rc = c->tmp_b.reserve(sizeof(int2) * (size_t)nt)) return rc;
     CU(launch_plan(c->reads, lw, (int2 *)c->range.p, c->stream));
     c->launches += 1;

@@ -92,6 +92,9 @@ struct Ctx {
 
     // live kernel timing (svtk_set_profiling): CUDA events around the fused refinement kernel on the ctx stream
     bool profile = false, prof_pending = false, prof_idx_pending = false;
+    bool flags_clean = false;                  // the current block's batch flags are zero (a build cleared them, no batch ran since)
+    int ctl_cur = 0;                           // which of the two control blocks the current index / batch uses
+    bool ctl_clean[2] = {false, false};        // block is known to hold zeros (cleared by the index kernel of the previous build)
     int prof_stride = 1;                       // bracket every prof_stride-th index build / refine launch (svtk_set_profiling(ctx, n))
     unsigned long long prof_tick_idx = 0, prof_tick_ref = 0;
     cudaEvent_t prof_ev[4] = {nullptr, nullptr, nullptr, nullptr};     // [0,1] refine kernel, [2,3] index kernel

@@ -61,13 +61,15 @@ struct DevIndex {
     unsigned int *ctrl;  // [p * CTRL_STRIDE] top of sub-pool p, [CTRL_SEG] segment top, [CTRL_ERR] error bits (1 events, 2 segments)
     unsigned int pool_cap, seg_cap;
     int n_chunks;
+    unsigned int *next_ctrl;   // the next build's control block: cleared here, off the host's critical path
+    int next_words;
 };
 
 static DevIndex to_dev(const LaunchIndex &x) {
     DevIndex d;
     d.events = reinterpret_cast<uint4 *>(x.events); d.chunks = reinterpret_cast<uint4 *>(x.chunks);
     d.segs = reinterpret_cast<uint4 *>(x.segs); d.rend = x.rend; d.ctrl = x.ctrl; d.pool_cap = x.pool_cap; d.seg_cap = x.seg_cap;
-    d.n_chunks = x.n_chunks;
+    d.n_chunks = x.n_chunks; d.next_ctrl = x.next_ctrl; d.next_words = x.next_words;
     return d;
 }
 static DevReads to_dev(const LaunchReads &r) {
@@ -435,6 +437,8 @@ __global__ void __launch_bounds__(IDX_WARPS * 32, SVTK_IDX_DMINB) k_index_reads_
     __shared__ IndexDeferShared sh[IDX_WARPS];
     __shared__ __align__(128) uint2 optab[16];               // one per CTA: every warp writes the same 16 entries, then reads after its own __syncwarp
     const int lane = lane_id(), warp = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && X.next_ctrl)                      // nobody touches that block before the next build (stream order)
+        for (int i = threadIdx.x; i < X.next_words; i += IDX_WARPS * 32) X.next_ctrl[i] = 0u;
     const long long c = (long long)blockIdx.x * IDX_WARPS + warp;
     if (c >= X.n_chunks) return;
     IndexDeferShared &s = sh[warp];
@@ -1143,6 +1147,7 @@ constexpr int RB_NT = 1024;
 
 int index_reads_per_chunk() { return IDX_READS; }
 int index_pools() { return IDX_POOLS; }
+int index_zeroes_next_ctrl() { return (SVTK_IDX_DEFER && !SVTK_IDX_LANE) ? 1 : 0; }
 int index_fixed_slots() { return (SVTK_IDX_DEFER && !SVTK_IDX_LANE) ? SVTK_IDX_FIXK : 0; }
 int index_ctrl_words() { return CTRL_ERR + CTRL_STRIDE; }
 int index_ctrl_stride() { return CTRL_STRIDE; }

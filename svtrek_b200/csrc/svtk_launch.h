@@ -40,12 +40,15 @@ struct LaunchIndex {            // the signature index built by k_index_reads (d
     unsigned int *ctrl;         // index_ctrl_words() u32: [p * stride] sub-pool tops, [pools * stride] segment top, then error bits
     unsigned int pool_cap, seg_cap;
     int n_chunks;
+    unsigned int *next_ctrl;    // control block of the NEXT build, cleared by this build's kernel (nullptr: the host clears it)
+    int next_words;
 };
 
 int index_reads_per_chunk();
 int index_pools();
 int index_fixed_slots();      // event slots per chunk behind the sub-pools (0: none); their counts live in ctrl[p * stride + 1]
 int index_ctrl_words();
+int index_zeroes_next_ctrl();  // 1: launch_index_reads clears LaunchIndex::next_ctrl itself
 int index_ctrl_stride();
 int refine_block_segment_ints();
 cudaError_t launch_index_reads(const LaunchReads &r, const LaunchIndex &x, cudaStream_t s);

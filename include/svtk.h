@@ -204,6 +204,11 @@ int svtk_refine_windows_device(svtk_ctx *ctx, const svtk_windows *dev_windows, i
 /* same results through the reference-shaped walker (one CIGAR walk per (window, read) pair, like refinement.c) with
  * the work counters of SURVEY 8(d); slower -- an independent cross-check and the reference-equivalent byte count */
 int svtk_measure_windows(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result, svtk_stats *stats);
+/* One whole pass of the path -- rebuild the signature index of the resident reads, then refine every window -- queued on the
+ * ctx stream without waiting for anything: the caller may queue many passes back to back (bench.py's timed steps; a driver that
+ * audits several VCFs against one BAM).  svtk_sync waits for all of them and finishes, synchronously, the windows of any pass that
+ * left the fast path.  dev_windows / dev_result must stay valid until then. */
+int svtk_audit_device(svtk_ctx *ctx, const svtk_windows *dev_windows, int32_t *dev_result);
 int svtk_sync(svtk_ctx *ctx);
 /* number of kernel launches this ctx has issued so far */
 uint64_t svtk_launch_count(const svtk_ctx *ctx);
@@ -243,6 +248,23 @@ int svtk_sliding_window_ins(svtk_ctx *ctx, int chrom, svtk_interval inter, int w
  * reference's end-of-file tail drop, audit.c:35-41,342, is not reproduced).  *n_records (may be NULL)
  * receives the number of (INS)/(DEL)/(INV) lines written. */
 int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records);
+/* A region shard of process_vcf for multi-GPU runs (replaces the per-worker fan-out of audit.c:269-293): the whole
+ * VCF is parsed, but only the records on references tid_lo .. tid_hi (chrom - 1) are audited and written.  One ctx per GPU
+ * calls this with its own range (and the reads of that range loaded, svtk_load_bam_refs); the shard outputs concatenated in
+ * range order are the lines svtk_process_vcf writes for the whole file.  flags: SVTK_VCF_NO_INFO_LINES leaves out the two
+ * [INFO] lines (the merger writes them once); SVTK_VCF_OWNS_UNPLACED makes this shard the one that reports lines no shard
+ * can place (malformed lines, references outside the dictionary) -- give it to exactly one shard. */
+enum { SVTK_VCF_NO_INFO_LINES = 1, SVTK_VCF_OWNS_UNPLACED = 2 };
+int svtk_process_vcf_region(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int32_t tid_lo, int32_t tid_hi, uint32_t flags,
+                            int64_t *n_records);
+/* The front and back ends of process_vcf alone -- no ctx, no GPU: the windows process_vcf builds for a VCF (audit.c:65-193,
+ * in file order; call with cap 0 for the count), and the lines it writes for given per-window results (audit.c:182-229).
+ * n_ref: size of the BAM's reference dictionary (0: unknown), only used to place records of a sharded call.  tid_lo < 0: the
+ * whole file.  Parity aids: the host logic can be checked against the reference's captured stdout without a device. */
+int svtk_vcf_windows(const char *vcf_path, const svtk_params *params, int32_t n_ref, int32_t tid_lo, int32_t tid_hi, uint32_t flags,
+                     int64_t cap, int32_t *chrom, uint32_t *start, uint32_t *end, uint32_t *pos, uint8_t *kind, int64_t *n_win);
+int svtk_vcf_format(const char *vcf_path, const svtk_params *params, int32_t n_ref, int32_t tid_lo, int32_t tid_hi, uint32_t flags,
+                    const int32_t *results, int64_t n_results, const char *out_path, int64_t *n_records);
 /* The same, plus the side file the north star's "abPOA for insertion consensus" needs (the reference's stdout has no slot for a
  * sequence): for every INS record whose refinement gave a position and that has carrier reads, one FASTA entry
  *   >INS chr=<chrom> org_pos=<VCF pos> ref_pos=<refined> reads=<carriers> len=<bases>

@@ -82,7 +82,7 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format"]
 
 _lib = None
 
@@ -128,6 +128,10 @@ def load_library():
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
     L.svtk_process_vcf_ins.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.svtk_ins_sequences.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p, C.c_int32, C.c_int32, C.POINTER(InsSets)]
+    L.svtk_audit_device.argtypes = [C.c_void_p, C.POINTER(Windows), C.c_void_p]
+    L.svtk_process_vcf_region.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.c_uint32, C.POINTER(C.c_int64)]
+    L.svtk_vcf_windows.argtypes = [C.c_char_p, C.POINTER(Params), C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_int64] + [C.c_void_p] * 5 + [C.POINTER(C.c_int64)]
+    L.svtk_vcf_format.argtypes = [C.c_char_p, C.POINTER(Params), C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_void_p, C.c_int64, C.c_char_p, C.POINTER(C.c_int64)]
     L.svtk_copy_reads.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)] + [C.c_void_p] * 6
     _lib = L
     return L
@@ -140,6 +144,37 @@ def _check(rc):
 
 def _u32(a):
     return np.ascontiguousarray(np.asarray(a).astype(np.int64) & 0xFFFFFFFF, dtype=np.uint32)
+
+
+def vcf_windows(vcf_path, params=None, n_ref=0, refs=None, owns_unplaced=True):
+    """svtk_vcf_windows: the refine_* windows process_vcf builds for a VCF (no device needed).  refs=(tid_lo, tid_hi): a shard."""
+    L = load_library()
+    p = dict(DEFAULT_PARAMS); p.update(params or {})
+    P = Params(**p)
+    lo, hi = (-1, -1) if refs is None else (int(refs[0]), int(refs[1]))
+    flags = 2 if owns_unplaced else 0
+    n = C.c_int64(0)
+    _check(L.svtk_vcf_windows(os.fsencode(vcf_path), C.byref(P), int(n_ref), lo, hi, flags, 0, None, None, None, None, None, C.byref(n)))
+    k = int(n.value)
+    a = dict(chrom=np.zeros(k, np.int32), start=np.zeros(k, np.uint32), end=np.zeros(k, np.uint32), pos=np.zeros(k, np.uint32), kind=np.zeros(k, np.uint8))
+    if k:
+        _check(L.svtk_vcf_windows(os.fsencode(vcf_path), C.byref(P), int(n_ref), lo, hi, flags, k,
+                                  *[a[x].ctypes.data for x in ("chrom", "start", "end", "pos", "kind")], C.byref(n)))
+    return a
+
+
+def vcf_format(vcf_path, results, out_path, params=None, n_ref=0, refs=None, owns_unplaced=True, info_lines=True):
+    """svtk_vcf_format: the lines process_vcf writes for the given per-window results (no device needed); returns the record count."""
+    L = load_library()
+    p = dict(DEFAULT_PARAMS); p.update(params or {})
+    P = Params(**p)
+    lo, hi = (-1, -1) if refs is None else (int(refs[0]), int(refs[1]))
+    flags = (2 if owns_unplaced else 0) | (0 if info_lines else 1)
+    r = np.ascontiguousarray(results, dtype=np.int32)
+    n = C.c_int64(0)
+    _check(L.svtk_vcf_format(os.fsencode(vcf_path), C.byref(P), int(n_ref), lo, hi, flags, r.ctypes.data if r.size else None, int(r.size),
+                             os.fsencode(out_path), C.byref(n)))
+    return int(n.value)
 
 
 class Auditor:
@@ -215,6 +250,11 @@ class Auditor:
     def refine_windows_device(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
         w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
         _check(self.lib.svtk_refine_windows_device(self.ctx, C.byref(w), result_ptr))
+
+    def audit_device(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
+        """svtk_audit_device: index rebuild + every window, queued on the ctx stream; sync() finishes all queued passes."""
+        w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
+        _check(self.lib.svtk_audit_device(self.ctx, C.byref(w), result_ptr))
 
     def measure_windows(self, n, chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr, result_ptr):
         w = Windows(int(n), chrom_ptr, start_ptr, end_ptr, pos_ptr, kind_ptr)
@@ -402,6 +442,13 @@ class Auditor:
         _check(self.lib.svtk_process_vcf_ins(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, fasta_path.encode(), int(tol),
                                              C.byref(n), C.byref(k)))
         return n.value, k.value
+
+    def process_vcf_region(self, vcf_path, out_path, tid_lo, tid_hi, info_lines=False, owns_unplaced=False):
+        """svtk_process_vcf_region: the records on references tid_lo..tid_hi only (one GPU's region shard)."""
+        n = C.c_int64(0)
+        flags = (0 if info_lines else 1) | (2 if owns_unplaced else 0)
+        _check(self.lib.svtk_process_vcf_region(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, int(tid_lo), int(tid_hi), flags, C.byref(n)))
+        return n.value
 
     def process_vcf(self, vcf_path, out_path):
         n = C.c_int64(0)

@@ -203,7 +203,7 @@ static int ensure_batch(Ctx *c, int n_win) {
 
 enum { MODE_INDEXED = 0, MODE_WALKER_STATS = 1, MODE_INDEXED_STATS = 2 };
 
-static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int mode) {
+static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int mode, char *host_ctl = nullptr) {
     if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded (svtk_load_reads / svtk_attach_reads_device)");
     if (int rc = set_device(c)) return rc;
     if (int rc = ensure_batch(c, std::max(w.n_win, 1))) return rc;
@@ -241,7 +241,9 @@ static int launch_batch(Ctx *c, const LaunchWindows &w, int32_t *dev_result, int
         }
         c->launches += 1;
     }
-    if (mode != MODE_WALKER_STATS && c->index_fresh)
+    if (host_ctl)            // svtk_audit_device: the whole control block of this step goes to the step's own slot
+        CU(cudaMemcpyAsync(host_ctl, ctl_base(c, c->ctl_cur), ctl_index_bytes() + 4, cudaMemcpyDeviceToHost, c->stream));
+    else if (mode != MODE_WALKER_STATS && c->index_fresh)
         CU(cudaMemcpyAsync(c->h_idx.p, ctl_base(c, c->ctl_cur), ctl_index_bytes() + 4, cudaMemcpyDeviceToHost, c->stream));
     else
         CU(cudaMemcpyAsync(host_flags(c), ov_flags(c), 4, cudaMemcpyDeviceToHost, c->stream));
@@ -395,7 +397,7 @@ void svtk_destroy(svtk_ctx *ctx) {
                       &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl, &c->bam_comp, &c->bam_infl, &c->bam_blocks,
                       &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl})
         b->release();
-    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h}) b->release();
+    for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h, &c->h_audit}) b->release();
     for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
     c->bam_h.release();
@@ -464,12 +466,61 @@ int svtk_refine_windows_device(svtk_ctx *ctx, const svtk_windows *w, int32_t *de
     return launch_batch(c, as_launch(w), dev_result, MODE_INDEXED);
 }
 
+// ---- svtk_audit_device: one whole pass of the path (index build + every window), stream-ordered, no host wait.
+// Each step copies its control block (index counters, error bits, overflow count) to its own pinned slot; svtk_sync reads the
+// slots in order and redoes, through the synchronous path, any step whose index ran out of room or whose windows overflowed
+// the register sort.  Up to AUDIT_SLOTS steps may be in flight; one more waits for the stream.
+static const int AUDIT_SLOTS = 256;
+static size_t audit_slot_bytes() { return (ctl_index_bytes() + 64 + 63) & ~(size_t)63; }
+
+static int resolve_audit_steps(Ctx *c) {
+    // the stream has drained.  Steps are independent passes over the same resident reads: redo the ones that need it.
+    std::vector<Ctx::AuditStep> q;
+    q.swap(c->audit_q);
+    c->pending = false;
+    c->index_fresh = false;
+    const int st = index_ctrl_stride(), np = index_pools();
+    for (size_t i = 0; i < q.size(); ++i) {
+        const unsigned int *ctrl = (const unsigned int *)((const char *)c->h_audit.p + (size_t)q[i].slot * audit_slot_bytes());
+        const unsigned int err = ctrl[(np + 1) * st];
+        const int n_ov = *(const int *)((const char *)ctrl + ctl_index_bytes());
+        if (i + 1 == q.size()) {                             // totals of the newest index (svtk_measure_index reads them)
+            uint64_t ev = 0;
+            for (int p = 0; p < np; ++p) ev += ctrl[p * st];
+            if (index_fixed_slots()) for (int p = 0; p < np; ++p) ev += ctrl[p * st + 1];
+            c->idx_n_events = ev; c->idx_n_segs = ctrl[np * st];
+        }
+        if (!err && n_ov <= 0) continue;
+        c->index_valid = false;                              // rebuild (re-dimensioned if needed) and redo this step's windows
+        if (int rc = launch_batch(c, q[i].win, q[i].result, MODE_INDEXED)) return rc;
+        CU(cudaStreamSynchronize(c->stream));
+        if (int rc = resolve_overflow(c)) return rc;
+    }
+    return 0;
+}
+
+int svtk_audit_device(svtk_ctx *ctx, const svtk_windows *w, int32_t *dev_result) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !w || (w->n_win > 0 && !dev_result)) return fail(SVTK_ERR_ARG, "null argument");
+    if (!c->have_reads) return fail(SVTK_ERR_STATE, "no reads loaded");
+    if (int rc = set_device(c)) return rc;
+    if ((c->pending && c->audit_q.empty()) || (int)c->audit_q.size() >= AUDIT_SLOTS) if (int rc = svtk_sync(ctx)) return rc;
+    if (int rc = c->h_audit.reserve(audit_slot_bytes() * AUDIT_SLOTS)) return rc;
+    if (w->n_win <= 0) return build_index(c);
+    const int slot = (int)c->audit_q.size();
+    c->index_valid = false;                                  // a step always contains the whole job: rebuild the index
+    if (int rc = launch_batch(c, as_launch(w), dev_result, MODE_INDEXED, (char *)c->h_audit.p + (size_t)slot * audit_slot_bytes())) return rc;
+    c->audit_q.push_back(Ctx::AuditStep{as_launch(w), dev_result, slot});
+    return 0;
+}
+
 int svtk_sync(svtk_ctx *ctx) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c) return fail(SVTK_ERR_ARG, "null ctx");
     if (int rc = set_device(c)) return rc;
     CU(cudaStreamSynchronize(c->stream));
     if (c->profile) if (int rc = collect_timing(c)) return rc;
+    if (!c->audit_q.empty()) return resolve_audit_steps(c);
     return resolve_overflow(c);
 }
 

@@ -68,6 +68,11 @@ struct Ctx {
     uint64_t launches = 0;
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
 
+    // svtk_audit_device: steps launched and not yet checked by svtk_sync; each owns a slot of h_audit (its control block copy)
+    struct AuditStep { LaunchWindows win; int32_t *result; int slot; };
+    std::vector<AuditStep> audit_q;
+    PinBuf h_audit;
+
     // K3 (svtk_poa.cu): device copies of one batch of read sets, per-worker scratch, events
     DevBuf poa_in, poa_out, poa_scratch, poa_ctl;
     PinBuf poa_h;

@@ -530,3 +530,236 @@ def write_bam(path, rs: ReadSet, seed=7, flags=None, chr_prefix="chr", truth=Non
                 prev = lin[t].get(win, prev)                              # empty windows repeat the previous offset, like HTSlib
                 f.write(struct.pack("<Q", prev))
     return size
+
+
+# ------------------------------------------------------------------------------------------------------------
+# The same kind of file, written fast: record bytes and BGZF compression by tools/libbgzfpack.so (C, zlib, pthreads; an input
+# generator, not product code), block cutting and the index with numpy.  bench.py writes the FULL config-2 BAM (128 k reads,
+# ~2 GB) with it, identically on both arms.
+_QUERY_OPS = np.array([1, 1, 0, 0, 1, 0, 0, 1, 1, 0, 0, 0, 0, 0, 0, 0], dtype=np.int64)      # M I S = X consume the query
+
+
+def _reg2bin_vec(beg, end):
+    end = end - 1
+    out = np.zeros(beg.shape[0], dtype=np.int64)
+    done = np.zeros(beg.shape[0], dtype=bool)
+    for shift, base in ((14, 4681), (17, 585), (20, 73), (23, 9), (26, 1)):
+        hit = ~done & ((beg >> shift) == (end >> shift))
+        out[hit] = base + (beg[hit] >> shift)
+        done |= hit
+    return out
+
+
+def _packer():
+    import ctypes
+    import os as _os
+    lib = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "tools", "libbgzfpack.so")
+    if not _os.path.exists(lib):
+        return None
+    try:
+        L = ctypes.CDLL(lib)
+    except OSError:
+        return None
+    vp, i64, i32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+    L.bgzfpack.argtypes = [vp, vp, i32, i32, i32, vp, i64, vp]
+    L.bgzfpack.restype = i32
+    L.bam_records.argtypes = [i64, i64, vp, vp, vp, vp, vp, vp, vp, vp, ctypes.c_uint64, i32, vp]
+    L.bam_records.restype = i32
+    return L
+
+
+def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_err=0.02, threads=None, level=6, chunk_reads=8192):
+    """A BAM + BAI of the read set like write_bam's (same record fields, HTSlib's BGZF cutting rule, same index layout), fast
+    enough for the full configs: ~15 s for config 2 on 16 cores, most of it zlib level 6.  Read names are fixed width (r%09d);
+    SEQ / QUAL are uniform random, carriers of a planted insertion hold a mutated copy of its sequence (`truth`).
+    Falls back to write_bam when tools/libbgzfpack.so has not been built.  Returns the file size."""
+    import struct
+    import os as _os
+    L = _packer()
+    if L is None:
+        return write_bam(path, rs, seed=seed, chr_prefix=chr_prefix, truth=truth, ins_err=ins_err)
+    threads = threads or max(1, min(64, (_os.cpu_count() or 2)))
+    n = rs.n_reads
+    BLOCK = 0xff00
+    NAME = 11                                                  # "r%09d\0"
+    tid = np.ascontiguousarray(np.repeat(np.arange(rs.n_tid, dtype=np.int32), np.diff(rs.tid_off)))
+    cig_off = np.ascontiguousarray(rs.cigar_off.astype(np.int64))
+    ncig = rs.n_cigar.astype(np.int64)
+    if ncig.size and int(ncig.max()) > 65535:
+        raise ValueError("write_bam_fast: CIGARs beyond 65535 operations need the CG tag")
+    qcs = np.zeros(rs.cigar.shape[0] + 1, dtype=np.int64)
+    np.cumsum(_QUERY_OPS[rs.cigar & 15] * (rs.cigar >> 4).astype(np.int64), out=qcs[1:])
+    qlen = np.ascontiguousarray(qcs[cig_off[1:]] - qcs[cig_off[:-1]]) if n else np.zeros(0, np.int64)
+    del qcs
+    rec_len = 4 + 32 + NAME + 4 * ncig + (qlen + 1) // 2 + qlen
+    bins = _reg2bin_vec(rs.pos.astype(np.int64), rs.end.astype(np.int64)) if n else np.zeros(0, np.int64)
+    bins16 = np.ascontiguousarray(bins.astype(np.uint16))
+    ncig32 = np.ascontiguousarray(rs.n_cigar.astype(np.uint32))
+    pos32 = np.ascontiguousarray(rs.pos.astype(np.uint32))
+    cigar = np.ascontiguousarray(rs.cigar.astype(np.uint32))
+    templates = {}
+    has_big_ins = np.zeros(n, dtype=bool)
+    if truth is not None and n:
+        trng = np.random.default_rng(seed + 1)
+        for k in np.flatnonzero(~truth.is_del):
+            templates.setdefault(int(truth.tid[k]), []).append((int(truth.pos0[k]), int(truth.length[k]), trng.integers(0, 4, int(truth.length[k])).astype(np.uint8)))
+        big = ((rs.cigar & 15) == OP_I) & ((rs.cigar >> 4) >= 50)
+        bcs = np.zeros(rs.cigar.shape[0] + 1, dtype=np.int64)
+        np.cumsum(big, out=bcs[1:])
+        has_big_ins = (bcs[cig_off[1:]] - bcs[cig_off[:-1]]) > 0
+
+    text = "@HD\tVN:1.6\tSO:coordinate\n" + "".join(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L_}\n" for t, L_ in enumerate(rs.contig_len))
+    hdr = b"BAM\1" + struct.pack("<i", len(text)) + text.encode() + struct.pack("<i", rs.n_tid)
+    for t, L_ in enumerate(rs.contig_len):
+        nm = f"{chr_prefix}{t + 1}".encode() + b"\0"
+        hdr += struct.pack("<i", len(nm)) + nm + struct.pack("<i", int(L_))
+
+    # ---- pass 1 (sizes only): the block every record starts / ends in.  HTSlib: a record that does not fit the current block
+    # starts a new one; a record larger than a block fills blocks to the brim (bgzf.c: bgzf_flush_try, bgzf_write)
+    hdr_blocks = max(1, -(-len(hdr) // BLOCK))
+    b, fill = hdr_blocks, 0                                    # the header is flushed: records start a fresh block
+    bs_l, is_l, be_l, ie_l = [0] * n, [0] * n, [0] * n, [0] * n
+    starts = {}                                                # block -> stream offset of its first byte
+    off = 0
+    for r, Lr in enumerate(rec_len.tolist()):
+        if fill + Lr > BLOCK and fill > 0:
+            b += 1; fill = 0
+        if fill == 0:
+            starts[b] = off
+        bs_l[r] = b; is_l[r] = fill
+        rem, o2 = Lr, off
+        while fill + rem > BLOCK:
+            take = BLOCK - fill
+            rem -= take; o2 += take
+            b += 1; fill = 0
+            starts[b] = o2
+        fill += rem
+        be_l[r] = b; ie_l[r] = fill
+        off += Lr
+    n_blocks = (b + 1) if fill > 0 else b                       # blocks [hdr_blocks, n_blocks) hold records
+    if n and fill == 0:
+        starts.pop(b, None)
+    blk_start = np.array(bs_l, dtype=np.int64); in_start = np.array(is_l, dtype=np.int64)
+    blk_end = np.array(be_l, dtype=np.int64); in_end = np.array(ie_l, dtype=np.int64)
+    rec_off = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(rec_len, out=rec_off[1:])
+    blk_stream0 = np.zeros(n_blocks + 1, dtype=np.int64)
+    for k in range(hdr_blocks, n_blocks):
+        blk_stream0[k] = starts[k]
+    blk_stream0[n_blocks] = rec_off[n]
+
+    csize = np.zeros(n_blocks + 1, dtype=np.int64)
+    rng = np.random.default_rng(seed)
+    STR = 65536 + 64
+
+    def pack(f, data, boff, k0):
+        nb_out = boff.shape[0] - 1
+        outb = np.empty(nb_out * STR, dtype=np.uint8)
+        osz = np.zeros(nb_out, dtype=np.int64)
+        if L.bgzfpack(data.ctypes.data, boff.ctypes.data, nb_out, level, threads, outb.ctypes.data, STR, osz.ctypes.data) != 0:
+            raise RuntimeError("bgzfpack failed")
+        for i in range(nb_out):
+            f.write(outb[i * STR:i * STR + int(osz[i])].data)
+        csize[k0:k0 + nb_out] = osz
+
+    with open(path, "wb") as f:
+        hb = np.frombuffer(hdr, dtype=np.uint8).copy()
+        hoff = np.array([min(len(hdr), i * BLOCK) for i in range(hdr_blocks + 1)], dtype=np.int64)
+        pack(f, hb, hoff, 0)
+        carry = np.zeros(0, dtype=np.uint8)                    # bytes of the stream not yet written (tail of the last chunk)
+        next_blk = hdr_blocks
+        for c0 in range(0, n, chunk_reads):
+            c1 = min(n, c0 + chunk_reads)
+            base = int(rec_off[c0])
+            d_off = base - carry.size                          # stream offset of data[0]
+            data = np.empty(carry.size + int(rec_off[c1]) - base, dtype=np.uint8)
+            data[:carry.size] = carry
+            ro = np.ascontiguousarray(rec_off[c0:c1] - d_off)
+            L.bam_records(c1 - c0, c0, tid[c0:].ctypes.data, pos32[c0:].ctypes.data, bins16[c0:].ctypes.data, ncig32[c0:].ctypes.data,
+                          cig_off[c0:].ctypes.data, cigar.ctypes.data, qlen[c0:].ctypes.data, ro.ctypes.data, seed, threads, data.ctypes.data)
+            # planted insertions: carriers hold a mutated copy of the insertion's own sequence
+            for r in np.flatnonzero(has_big_ins[c0:c1]).tolist():
+                rr = c0 + r
+                t = int(tid[rr])
+                if t not in templates:
+                    continue
+                w = rs.cigar[int(cig_off[rr]):int(cig_off[rr + 1])]
+                cur, q = int(rs.pos[rr]), 0
+                s0 = int(ro[r]) + 36 + NAME + 4 * int(ncig[rr])
+                for cw in w.tolist():
+                    o, ln = cw & 15, cw >> 4
+                    if o == OP_I and ln >= 50:
+                        for p0, Lt, tpl in templates[t]:
+                            if Lt == ln and abs(p0 - cur) <= 3:
+                                copy = tpl.copy()
+                                mm = rng.random(ln) < ins_err
+                                copy[mm] = (copy[mm] + rng.integers(1, 4, int(mm.sum()))) & 3
+                                qi = q + np.arange(ln)
+                                byte = s0 + (qi >> 1)
+                                hi = (qi & 1) == 0
+                                nibv = (1 << copy).astype(np.uint8)
+                                data[byte[hi]] = (data[byte[hi]] & 0x0F) | (nibv[hi] << 4)       # two passes: a byte may take both nibbles
+                                data[byte[~hi]] = (data[byte[~hi]] & 0xF0) | nibv[~hi]
+                                break
+                    if o not in (OP_I, OP_S):
+                        cur += ln
+                    if o in (OP_M, OP_I, OP_S, OP_EQ, OP_X):
+                        q += ln
+            # every block that ends inside the bytes built so far goes out now
+            d_end = int(rec_off[c1])
+            last_blk = next_blk
+            while last_blk < n_blocks and int(blk_stream0[last_blk + 1]) <= d_end:
+                last_blk += 1
+            if last_blk > next_blk:
+                boff = np.ascontiguousarray(blk_stream0[next_blk:last_blk + 1] - d_off, dtype=np.int64)
+                pack(f, data, boff, next_blk)
+            done_to = int(blk_stream0[last_blk])
+            carry = data[done_to - d_off:].copy()
+            next_blk = last_blk
+        assert next_blk == n_blocks and carry.size == 0, (next_blk, n_blocks, carry.size)
+        e = np.zeros(1, dtype=np.uint8)
+        pack_eof = np.zeros(2, dtype=np.int64)                 # one empty block: the EOF marker
+        pack(f, e, pack_eof, n_blocks)
+    coff = np.zeros(n_blocks + 2, dtype=np.int64)
+    np.cumsum(csize[:n_blocks + 1], out=coff[1:])
+    size = int(coff[n_blocks + 1])
+    # ---- index (SAMv1 5.2)
+    v0 = (coff[blk_start] << 16) | in_start
+    v1 = (coff[blk_end] << 16) | in_end
+    with open(path + ".bai", "wb") as f:
+        f.write(b"BAI\1" + struct.pack("<i", rs.n_tid))
+        for t in range(rs.n_tid):
+            a, z = int(rs.tid_off[t]), int(rs.tid_off[t + 1])
+            if z == a:
+                f.write(struct.pack("<i", 0) + struct.pack("<i", 0))
+                continue
+            bt, s0, s1 = bins[a:z], v0[a:z], v1[a:z]
+            order = np.argsort(bt, kind="stable")
+            bo, so0, so1 = bt[order], s0[order], s1[order]
+            brk = np.ones(z - a, dtype=bool)
+            brk[1:] = (bo[1:] != bo[:-1]) | (so0[1:] != so1[:-1])
+            cs = np.flatnonzero(brk)
+            ce = np.concatenate([cs[1:], [z - a]]) - 1
+            ch_bin, ch_v0, ch_v1 = bo[cs], so0[cs], so1[ce]
+            ub, first = np.unique(ch_bin, return_index=True)
+            cnt = np.diff(np.concatenate([first, [ch_bin.shape[0]]]))
+            out = [struct.pack("<i", ub.shape[0])]
+            for bb, fi, cn in zip(ub.tolist(), first.tolist(), cnt.tolist()):
+                out.append(struct.pack("<Ii", bb, cn))
+                pair = np.empty(2 * cn, dtype="<u8")
+                pair[0::2] = ch_v0[fi:fi + cn]; pair[1::2] = ch_v1[fi:fi + cn]
+                out.append(pair.tobytes())
+            p = rs.pos[a:z].astype(np.int64); e_ = rs.end[a:z].astype(np.int64)
+            wlo, whi = p >> 14, ((e_ - 1) >> 14) + 1
+            n_intv = int(whi.max())
+            lin = np.full(n_intv, np.iinfo(np.int64).max, dtype=np.int64)
+            own, widx = _expand_ranges(wlo, whi)
+            np.minimum.at(lin, widx, s0[own])
+            empty = lin == np.iinfo(np.int64).max
+            last_filled = np.where(empty, -1, np.arange(n_intv))          # empty windows repeat the previous offset, like HTSlib
+            np.maximum.accumulate(last_filled, out=last_filled)
+            lin = np.where(last_filled < 0, 0, lin[np.maximum(last_filled, 0)])
+            out.append(struct.pack("<i", n_intv))
+            out.append(lin.astype("<u8").tobytes())
+            f.write(b"".join(out))
+    return size

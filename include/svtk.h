@@ -158,8 +158,13 @@ typedef struct {
     int32_t n_ref;
     uint32_t n_pieces;               /* pieces the record chain was cut into */
     uint32_t lanes_per_warp;         /* BGZF blocks decoded side by side in one warp (1..32, grows with the file) */
-    float host_scan_ms;              /* mmap + BGZF block table + header + .bai */
-    float upload_ms, inflate_ms, parse_ms, total_ms;
+    float host_scan_ms;              /* (unused since the block table is built chunk by chunk while the file uploads) */
+    float upload_ms;                 /* first to last host -> device copy of the file's bytes */
+    float inflate_ms;                /* first inflate launch to the end of the last one (overlaps the upload) */
+    float parse_ms, total_ms;        /* CRC + record kernels; wall clock of the whole call */
+    float load_span_ms;              /* first upload to the end of the last inflate: what upload + inflate cost together */
+    uint32_t n_spans;                /* disjoint byte ranges of the file that were shipped */
+    uint32_t inflate_launches;
 } svtk_bam_stats;
 int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats);
 /* The same for the reads of references tid_lo .. tid_hi only (region shard of a multi-GPU run, SURVEY 8e: one ctx per GPU, each
@@ -167,6 +172,12 @@ int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svt
  * the file, so only that byte range is shipped and inflated.  Read indices and tid_off are those of the shard (other
  * references are empty); windows on other references refine to NA. */
 int svtk_load_bam_refs(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int32_t tid_lo, int32_t tid_hi, svtk_bam_stats *stats);
+/* Only what a batch of windows can see (host arrays; chrom / start / end are read): for each window the region its iterator
+ * would query -- sam_itr_queryi(idx, chrom - 1, start - 1, end - 1), refinement.c:114 -- is looked up in the .bai the way
+ * hts_itr_query does (hts.c:3049-3090: the chunks of every overlapping bin, clipped by the linear index), the chunk lists are
+ * merged, and only those BGZF blocks are shipped and inflated.  Region shards of a single-reference job, and sparse VCFs against
+ * large BAMs, load a fraction of the file.  Reads beyond what the windows can see are simply not resident. */
+int svtk_load_bam_windows(svtk_ctx *ctx, const char *bam_path, const char *bai_path, const svtk_windows *host_windows, svtk_bam_stats *stats);
 /* the BAM header's reference dictionary (bam_hdr_t target_name / target_len) after svtk_load_bam */
 int svtk_bam_n_ref(const svtk_ctx *ctx);
 int svtk_bam_ref(const svtk_ctx *ctx, int tid, const char **name, uint32_t *len);

@@ -70,7 +70,7 @@ class PoaStats(C.Structure):
 class BamStats(C.Structure):
     _fields_ = [("file_bytes", C.c_uint64), ("n_blocks", C.c_uint64), ("inflated_bytes", C.c_uint64), ("n_reads", C.c_uint64), ("n_words", C.c_uint64), ("image_bytes", C.c_uint64),
                 ("n_ref", C.c_int32), ("n_pieces", C.c_uint32), ("lanes_per_warp", C.c_uint32), ("host_scan_ms", C.c_float), ("upload_ms", C.c_float), ("inflate_ms", C.c_float),
-                ("parse_ms", C.c_float), ("total_ms", C.c_float)]
+                ("parse_ms", C.c_float), ("total_ms", C.c_float), ("load_span_ms", C.c_float), ("n_spans", C.c_uint32), ("inflate_launches", C.c_uint32)]
 
 
 class InsSets(C.Structure):
@@ -82,7 +82,7 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format", "svtk_load_bam_windows"]
 
 _lib = None
 
@@ -124,6 +124,7 @@ def load_library():
                                      C.POINTER(PoaTrace), C.POINTER(PoaStats)]
     L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
     L.svtk_load_bam_refs.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(BamStats)]
+    L.svtk_load_bam_windows.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(Windows), C.POINTER(BamStats)]
     L.svtk_bam_n_ref.argtypes = [C.c_void_p]
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
     L.svtk_process_vcf_ins.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -298,6 +299,15 @@ class Auditor:
             _check(self.lib.svtk_load_bam(self.ctx, os.fsencode(bam_path), bai, C.byref(st)))
         else:
             _check(self.lib.svtk_load_bam_refs(self.ctx, os.fsencode(bam_path), bai, int(refs[0]), int(refs[1]), C.byref(st)))
+        return {k: getattr(st, k) for k, _ in BamStats._fields_}
+
+    def load_bam_windows(self, bam_path, chrom, start, end, bai_path=None):
+        """svtk_load_bam_windows: only the parts of the file the given windows' iterators could touch."""
+        chrom = np.ascontiguousarray(chrom, dtype=np.int32)
+        start, end = _u32(start), _u32(end)
+        w = Windows(int(chrom.shape[0]), chrom.ctypes.data, start.ctypes.data, end.ctypes.data, None, None)
+        st = BamStats()
+        _check(self.lib.svtk_load_bam_windows(self.ctx, os.fsencode(bam_path), os.fsencode(bai_path) if bai_path else None, C.byref(w), C.byref(st)))
         return {k: getattr(st, k) for k, _ in BamStats._fields_}
 
     def bam_refs(self):

@@ -55,20 +55,27 @@ constexpr unsigned FULLMASK = 0xffffffffu;
 #ifndef SVTK_BZ_MINB
 #define SVTK_BZ_MINB 16           // resident single-warp CTAs per SM the register allocation must allow
 #endif
-__global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned n_blocks,
-                                                     uint8_t *__restrict__ out, unsigned int *__restrict__ ctl, int lanes) {
+__global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned first_block,
+                                                     unsigned n_blocks, uint8_t *__restrict__ out, unsigned int *__restrict__ ctl, unsigned int *__restrict__ next,
+                                                     int lanes) {
     extern __shared__ uint32_t bz_sm[];
+    // length / distance bases (svtk_bgzf_core.cuh): one copy per CTA, behind the lanes' Huffman tables
+    uint32_t *lut = bz_sm + lanes * BZ_TABLE_WORDS;
+    if (threadIdx.x < 29u) lut[threadIdx.x] = bz_len_entry((int)threadIdx.x);
+    if (threadIdx.x < 30u) lut[32 + threadIdx.x] = bz_dist_entry((int)threadIdx.x);
+    __syncwarp();
+    const BzLut L{lut};
     BzTables T;
     T.lit = reinterpret_cast<uint16_t *>(bz_sm + (threadIdx.x < (unsigned)lanes ? threadIdx.x : 0u) * BZ_TABLE_WORDS);
     T.dist = T.lit + (1 << BZ_LBITS);
     BzLane z;
-    z.state = BZ_S_IDLE; z.err = BZ_OK;
+    z.state = BZ_S_IDLE; z.err = BZ_OK; z.pend_len = 0; z.pend_dist = 0;
     unsigned cur = 0xffffffffu;
     bool drained = threadIdx.x >= (unsigned)lanes;
     for (;;) {
         if (z.state == BZ_S_IDLE && !drained) {
             if (cur != 0xffffffffu && z.err) { if (atomicCAS(&ctl[BAM_CTL_ZERR], 0u, cur + 1u) == 0u) ctl[BAM_CTL_ZCODE] = (unsigned)z.err; }
-            cur = atomicAdd(&ctl[BAM_CTL_NEXT], 1u);
+            cur = first_block + atomicAdd(next, 1u);
             if (cur < n_blocks) {
                 const BgzfBlock b = blk[cur];
                 bz_begin(z, words, b.in_beg, b.in_beg + b.in_len, out + b.out_off, b.isize);
@@ -76,11 +83,11 @@ __global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_
         }
         if (__all_sync(FULLMASK, drained)) break;
         // every lane passes here once per round: block switches (header + table build) on the lanes that need one, then a
-        // burst of symbol steps that all lanes take together
+        // burst of symbol rounds that all lanes take together
         if (z.state == BZ_S_HEADER) bz_header(z, T);
 #pragma unroll 1
         for (int it = 0; it < BZ_BURST; ++it)
-            if (z.state == BZ_S_SYMBOLS) bz_step(z, T);
+            if (z.state == BZ_S_SYMBOLS) bz_step(z, T, L);
         bz_check_input(z);
     }
 }
@@ -161,7 +168,7 @@ __device__ int find_cg(const uint32_t *__restrict__ w, unsigned long long p, uns
     return p == end ? 0 : -1;
 }
 
-// One thread per piece [splits[s], splits[s+1]) of the record chain.  FILL == false: seg[s] = {reads, CIGAR words}.
+// One thread per piece [splits[2s], splits[2s+1]) of the record chain (pieces of different loaded ranges do not touch).  FILL == false: seg[s] = {reads, CIGAR words}.
 // FILL == true: seg[s] holds the exclusive prefix {first read index, first CIGAR word}; per read the record offset, the
 // CIGAR source offset, n_cigar and cigar_off are written.
 template <bool FILL>
@@ -172,8 +179,8 @@ __global__ void __launch_bounds__(128) k_bam_walk(const uint32_t *__restrict__ w
                                                   uint32_t *__restrict__ l_seq_out, unsigned int *__restrict__ ctl) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
-    unsigned long long off = splits[s];
-    const unsigned long long end = splits[s + 1];
+    unsigned long long off = splits[2 * s];
+    const unsigned long long end = splits[2 * s + 1];
     unsigned long long nr = 0, nw = 0;
     if (FILL) { const ulonglong2 b = seg[s]; nr = b.x; nw = b.y; }
     int err = BW_OK;
@@ -256,7 +263,7 @@ using namespace svtk;
 
 namespace {
 
-struct Mapped {                      // read-only mmap of a whole file
+struct Mapped {                      // read-only mmap of a whole file (the .bai)
     const uint8_t *p = nullptr;
     size_t n = 0;
     int fd = -1;
@@ -269,7 +276,6 @@ struct Mapped {                      // read-only mmap of a whole file
         if (n == 0) return 0;
         void *m = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0);
         if (m == MAP_FAILED) return -1;
-        madvise(m, n, MADV_SEQUENTIAL);
         p = (const uint8_t *)m;
         return 0;
     }
@@ -283,40 +289,57 @@ inline uint32_t le16(const uint8_t *p) { return (uint32_t)p[0] | (uint32_t)p[1] 
 inline uint32_t le32(const uint8_t *p) { return (uint32_t)p[0] | (uint32_t)p[1] << 8 | (uint32_t)p[2] << 16 | (uint32_t)p[3] << 24; }
 inline uint64_t le64(const uint8_t *p) { return (uint64_t)le32(p) | (uint64_t)le32(p + 4) << 32; }
 
-// BGZF block table (SAMv1 4.1): gzip member with the BC extra subfield carrying BSIZE
-// [from, to): `from` must be the start of a block; scanning stops at the first block starting at or after `to`.
-// in_beg is relative to `base` (the file offset the device image starts at).
-int scan_bgzf(const uint8_t *f, size_t n, size_t from, size_t to, size_t base, std::vector<BgzfBlock> &blk, std::vector<uint64_t> &coff) {
+bool pread_all(int fd, void *dst, size_t n, size_t off) {
+    char *d = (char *)dst;
+    while (n) {
+        const ssize_t k = pread(fd, d, n, (off_t)off);
+        if (k <= 0) return false;
+        d += k; n -= (size_t)k; off += (size_t)k;
+    }
+    return true;
+}
+
+// one BGZF block header (SAMv1 4.1: gzip member with the BC extra subfield carrying BSIZE) at h[0..avail): 0 = ok
+int parse_bgzf_header(const uint8_t *h, size_t avail, size_t file_off, uint32_t *bsize, uint32_t *xlen_out) {
+    if (avail < 18) return fail(SVTK_ERR_IO, "bam: truncated BGZF header at byte %zu", file_off);
+    if (h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) return fail(SVTK_ERR_IO, "bam: not a BGZF block at byte %zu", file_off);
+    const uint32_t xlen = le16(h + 10);
+    if (12 + (size_t)xlen > avail) return fail(SVTK_ERR_IO, "bam: truncated BGZF extra field at byte %zu", file_off);
+    uint32_t bs = 0;
+    for (uint32_t x = 0; x + 4 <= xlen;) {
+        const uint8_t *e = h + 12 + x;
+        const uint32_t slen = le16(e + 2);
+        if (e[0] == 'B' && e[1] == 'C' && slen == 2 && x + 6 <= xlen) bs = le16(e + 4) + 1;
+        x += 4 + slen;
+    }
+    if (bs < xlen + 20) return fail(SVTK_ERR_IO, "bam: bad BGZF block size at byte %zu", file_off);
+    *bsize = bs; *xlen_out = xlen;
+    return 0;
+}
+
+// BGZF block table of f[from, n) (used for the header's own blocks): scanning stops at the first block starting at or after `to`
+int scan_bgzf(const uint8_t *f, size_t n, size_t from, size_t to, std::vector<BgzfBlock> &blk) {
     size_t off = from;
-    unsigned long long out = 0;
+    unsigned long long out = blk.empty() ? 0ull : blk.back().out_off + blk.back().isize;
     while (off < n && off < to) {
-        if (off + 18 > n) return fail(SVTK_ERR_IO, "bam: truncated BGZF header at byte %zu", off);
-        const uint8_t *h = f + off;
-        if (h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) return fail(SVTK_ERR_IO, "bam: not a BGZF block at byte %zu", off);
-        const uint32_t xlen = le16(h + 10);
-        if (off + 12 + xlen > n) return fail(SVTK_ERR_IO, "bam: truncated BGZF extra field at byte %zu", off);
-        uint32_t bsize = 0;
-        for (uint32_t x = 0; x + 4 <= xlen;) {
-            const uint8_t *e = h + 12 + x;
-            const uint32_t slen = le16(e + 2);
-            if (e[0] == 'B' && e[1] == 'C' && slen == 2 && x + 6 <= xlen) bsize = le16(e + 4) + 1;
-            x += 4 + slen;
-        }
-        if (bsize < xlen + 20 || off + bsize > n) return fail(SVTK_ERR_IO, "bam: bad BGZF block size at byte %zu", off);
+        uint32_t bsize = 0, xlen = 0;
+        if (int rc = parse_bgzf_header(f + off, std::min<size_t>(n - off, 65536), off, &bsize, &xlen)) return rc;
+        if (off + bsize > n) return fail(SVTK_ERR_IO, "bam: bad BGZF block size at byte %zu", off);
         BgzfBlock b;
-        b.in_beg = off - base + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = le32(h + bsize - 4); b.out_off = out;
+        b.in_beg = off + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = le32(f + off + bsize - 4); b.out_off = out;
         if (b.isize > 65536u) return fail(SVTK_ERR_IO, "bam: BGZF block at byte %zu claims %u inflated bytes", off, b.isize);
-        blk.push_back(b); coff.push_back(off);
+        blk.push_back(b);
         out += b.isize;
         off += bsize;
     }
     return 0;
 }
 
-// the BAM header (magic, text, reference dictionary): inflated on the host with the same decoder, block by block, until complete
-int read_header(const uint8_t *f, size_t n, std::vector<std::string> &names, std::vector<uint32_t> &lens, unsigned long long *first_rec) {
+// the BAM header (magic, text, reference dictionary) out of the first bytes of the file: inflated on the host with the same
+// decoder, block by block, until complete.  *need_more: the buffer ended inside the header (the caller reads more and retries).
+int read_header(const uint8_t *f, size_t n, bool whole_file, std::vector<std::string> &names, std::vector<uint32_t> &lens,
+                unsigned long long *first_rec, bool *need_more) {
     std::vector<BgzfBlock> blk;                           // the header's own blocks, scanned lazily from the start of the file
-    std::vector<uint64_t> hcoff;
     size_t scanned = 0;
     std::vector<uint32_t> words;                          // the decoder reads aligned words: one block's payload at a time
     std::vector<uint8_t> hd;
@@ -324,14 +347,17 @@ int read_header(const uint8_t *f, size_t n, std::vector<std::string> &names, std
     std::vector<uint16_t> tabs((1 << BZ_LBITS) + (1 << BZ_DBITS));
     BzTables T;
     T.lit = tabs.data(); T.dist = tabs.data() + (1 << BZ_LBITS);
+    *need_more = false;
     auto more = [&](size_t need) -> int {
         while (hd.size() < need) {
             if (nb >= blk.size()) {
-                if (scanned >= n) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
-                const size_t before = blk.size();
-                if (int rc = scan_bgzf(f, n, scanned, std::min(n, scanned + (1u << 20)), 0, blk, hcoff)) return rc;
-                if (blk.size() == before) return fail(SVTK_ERR_IO, "bam: header runs past the end of the file");
-                scanned = (size_t)(blk.back().in_beg + blk.back().in_len + 8);      // base 0: in_beg is a file offset
+                // the next block must lie wholly inside the buffer
+                if (scanned + 18 > n) { *need_more = !whole_file; return fail(SVTK_ERR_IO, "bam: header runs past the end of the file"); }
+                uint32_t bsize = 0, xlen = 0;
+                if (int rc = parse_bgzf_header(f + scanned, n - scanned, scanned, &bsize, &xlen)) return rc;
+                if (scanned + bsize > n) { *need_more = !whole_file; return fail(SVTK_ERR_IO, "bam: header runs past the end of the file"); }
+                if (int rc = scan_bgzf(f, n, scanned, scanned + 1, blk)) return rc;
+                scanned += bsize;
             }
             const BgzfBlock &b = blk[nb++];
             words.assign((size_t)(b.in_len + BZ_OVERREAD) / 4 + 4, 0u);
@@ -368,10 +394,20 @@ int read_header(const uint8_t *f, size_t n, std::vector<std::string> &names, std
     return 0;
 }
 
-// record-aligned cut points from the .bai (SAMv1 5.2): linear-index offsets and the chunk starts of every real bin
-struct BaiRef { uint64_t beg = ~0ull, end = 0; };          // virtual offsets: first record / past the last record of one reference
+// ---- the .bai (SAMv1 5.2), parsed once per load
+struct BaiBin { uint32_t bin; uint32_t first, count; };    // chunks [first, first + count) of BaiRefIdx::chunks
+struct BaiRefIdx {
+    std::vector<BaiBin> bins;                              // sorted by bin number
+    std::vector<uint64_t> chunks;                          // pairs (begin, end) virtual offsets
+    std::vector<uint64_t> lin;                             // linear index, 16 kb tiles
+    uint64_t beg = ~0ull, end = 0;                         // first record / past the last record of the reference
+};
+struct Bai {
+    std::vector<BaiRefIdx> refs;
+    std::vector<uint64_t> voffs;                           // every record-aligned offset the index knows (sorted, unique): cut points
+};
 
-int read_bai(const char *path, int *n_ref_out, std::vector<uint64_t> &voffs, std::vector<BaiRef> &refs) {
+int read_bai(const char *path, Bai &bai) {
     Mapped m;
     if (m.open_file(path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open index %s (the reference needs it too: sam_index_load, audit.c:272)", path);
     const uint8_t *f = m.p;
@@ -379,10 +415,10 @@ int read_bai(const char *path, int *n_ref_out, std::vector<uint64_t> &voffs, std
     if (n < 8 || memcmp(f, "BAI\1", 4) != 0) return fail(SVTK_ERR_IO, "bam: %s is not a BAI index", path);
     const int32_t n_ref = (int32_t)le32(f + 4);
     if (n_ref < 0) return fail(SVTK_ERR_IO, "bam: bad index");
-    *n_ref_out = n_ref;
-    refs.assign((size_t)n_ref, BaiRef());
+    bai.refs.assign((size_t)n_ref, BaiRefIdx());
     size_t p = 8;
     for (int r = 0; r < n_ref; ++r) {
+        BaiRefIdx &R = bai.refs[(size_t)r];
         if (p + 4 > n) return fail(SVTK_ERR_IO, "bam: truncated index");
         const int32_t n_bin = (int32_t)le32(f + p);
         p += 4;
@@ -392,217 +428,410 @@ int read_bai(const char *path, int *n_ref_out, std::vector<uint64_t> &voffs, std
             const int32_t n_chunk = (int32_t)le32(f + p + 4);
             p += 8;
             if (n_chunk < 0 || p + 16ull * (size_t)n_chunk > n) return fail(SVTK_ERR_IO, "bam: truncated index");
-            if (bin != 37450u)                                      // the pseudo-bin holds file-level metadata, not record offsets
+            if (bin != 37450u) {                                    // the pseudo-bin holds file-level metadata, not record offsets
+                R.bins.push_back(BaiBin{bin, (uint32_t)(R.chunks.size() / 2), (uint32_t)n_chunk});
                 for (int k = 0; k < n_chunk; ++k) {
                     const uint64_t vb = le64(f + p + 16 * (size_t)k), ve = le64(f + p + 16 * (size_t)k + 8);
-                    voffs.push_back(vb);
-                    refs[(size_t)r].beg = std::min(refs[(size_t)r].beg, vb); refs[(size_t)r].end = std::max(refs[(size_t)r].end, ve);
+                    R.chunks.push_back(vb); R.chunks.push_back(ve);
+                    bai.voffs.push_back(vb);
+                    R.beg = std::min(R.beg, vb); R.end = std::max(R.end, ve);
                 }
+            }
             p += 16 * (size_t)n_chunk;
         }
+        std::sort(R.bins.begin(), R.bins.end(), [](const BaiBin &a, const BaiBin &b) { return a.bin < b.bin; });
         if (p + 4 > n) return fail(SVTK_ERR_IO, "bam: truncated index");
         const int32_t n_intv = (int32_t)le32(f + p);
         p += 4;
         if (n_intv < 0 || p + 8ull * (size_t)n_intv > n) return fail(SVTK_ERR_IO, "bam: truncated index");
-        for (int k = 0; k < n_intv; ++k) { const uint64_t v = le64(f + p + 8 * (size_t)k); if (v) voffs.push_back(v); }
+        R.lin.resize((size_t)n_intv);
+        for (int k = 0; k < n_intv; ++k) { const uint64_t v = le64(f + p + 8 * (size_t)k); R.lin[(size_t)k] = v; if (v) bai.voffs.push_back(v); }
         p += 8 * (size_t)n_intv;
     }
+    std::sort(bai.voffs.begin(), bai.voffs.end());
+    bai.voffs.erase(std::unique(bai.voffs.begin(), bai.voffs.end()), bai.voffs.end());
     return 0;
 }
 
-// host -> device copy of a (pageable, memory-mapped) file image: the ctx's two pinned staging buffers, each chunk copied into
-// staging by several threads at once (one thread faults pages in at ~10 GB/s, the DMA engine takes ~50 GB/s)
-int upload_file(Ctx *c, void *dst, const uint8_t *src, size_t bytes) {
-    const size_t CH = 32u << 20;
-    for (int i = 0; i < 2; ++i) {
-        if (int rc = c->stage[i].reserve(CH)) return rc;
-        if (!c->stage_ev[i]) CU(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+struct VRange { uint64_t vb, ve; };                        // records from virtual offset vb up to ve (both record aligned)
+
+// Which parts of the file can hold a read overlapping [beg, end) of reference tid: the chunks of every bin that overlaps the
+// region, clipped below by the linear index entry of the region's first 16 kb tile -- hts_itr_query's rule (hts.c:3049-3090;
+// reg2bins hts.c:2920, the linear-index lower bound hts.c:3099-3111).  A superset of what the iterator yields: it still
+// filters record by record (hts.c:3913-3916), and so does the device search.
+void bai_query(const BaiRefIdx &R, long long beg, long long end, std::vector<VRange> &out) {
+    if (end <= beg || R.bins.empty()) return;
+    if (beg < 0) beg = 0;
+    if (end > (1ll << 29)) end = 1ll << 29;                 // the BAI binning scheme covers 2^29 bases
+    if (beg >= end) return;
+    uint64_t min_off = 0;
+    if (!R.lin.empty()) {
+        const size_t t = (size_t)(beg >> 14);
+        min_off = t < R.lin.size() ? R.lin[t] : R.lin.back();
+        if (min_off == 0 && t < R.lin.size()) for (size_t k = t; k-- > 0;) if (R.lin[k]) { min_off = R.lin[k]; break; }   // hts.c: walk back over empty tiles
     }
-    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const int T = (int)std::min(8u, std::max(1u, hw / 2));
-    size_t done = 0;
-    int k = 0;
-    while (done < bytes) {
-        const size_t n = std::min(CH, bytes - done);
-        CU(cudaEventSynchronize(c->stage_ev[k]));
-        char *st = (char *)c->stage[k].p;
-        const size_t per = ((n + T - 1) / T + 4095) & ~(size_t)4095;
-        std::vector<std::thread> th;
-        for (int t = 1; t < T; ++t) {
-            const size_t a = per * t;
-            if (a < n) th.emplace_back([=]() { memcpy(st + a, src + done + a, std::min(per, n - a)); });
-        }
-        memcpy(st, src + done, std::min(per, n));
-        for (auto &x : th) x.join();
-        CU(cudaMemcpyAsync((char *)dst + done, st, n, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaEventRecord(c->stage_ev[k], c->stream));
-        done += n;
-        k ^= 1;
+    const long long e1 = end - 1;
+    int t = 0;
+    for (int level = 0; level <= 5; ++level) {
+        const int shift = 29 - 3 * level;                   // 26, 23, 20, 17, 14 for levels 1..5; level 0: the whole range
+        const uint32_t b0 = (uint32_t)t + (uint32_t)(level ? (beg >> shift) : 0), b1 = (uint32_t)t + (uint32_t)(level ? (e1 >> shift) : 0);
+        auto it = std::lower_bound(R.bins.begin(), R.bins.end(), b0, [](const BaiBin &a, uint32_t v) { return a.bin < v; });
+        for (; it != R.bins.end() && it->bin <= b1; ++it)
+            for (uint32_t k = 0; k < it->count; ++k) {
+                const uint64_t vb = R.chunks[2 * (size_t)(it->first + k)], ve = R.chunks[2 * (size_t)(it->first + k) + 1];
+                if (ve > min_off && ve > vb) out.push_back(VRange{std::max(vb, min_off), ve});
+            }
+        t += 1 << (3 * level);
     }
-    return 0;
+}
+
+// sort, then merge ranges that overlap, touch, or lie within one BGZF block of each other (the records in between come along:
+// extra reads are harmless, the per-window selection happens on the device)
+void merge_ranges(std::vector<VRange> &r) {
+    std::sort(r.begin(), r.end(), [](const VRange &a, const VRange &b) { return a.vb < b.vb; });
+    size_t w = 0;
+    for (size_t i = 0; i < r.size(); ++i) {
+        if (w && (r[i].vb >> 16) <= (r[w - 1].ve >> 16) + 0x10000ull) r[w - 1].ve = std::max(r[w - 1].ve, r[i].ve);
+        else r[w++] = r[i];
+    }
+    r.resize(w);
 }
 
 double ms_since(std::chrono::steady_clock::time_point t0) {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
+struct Span { size_t fb, fe; };                            // bytes [fb, fe) of the file: whole BGZF blocks
+
 }  // namespace
 
-static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int tid_lo, int tid_hi, svtk_bam_stats *stats) {
+// The loader proper.  ranges == nullptr: every record of the file.  Otherwise: the records of the given (sorted, merged) ranges.
+//
+// Pipeline (one pass over the needed bytes of the file):
+//   host   T copier threads pread() the next chunk (<= 32 MB) of the file into a pinned ring buffer;  this thread then walks the
+//          chunk's BGZF headers / footers (block table: payload offset, ISIZE -> each block's slice of the inflated image),
+//   DMA    ships the chunk and its block descriptors on the ctx stream,
+//   GPU    k_bgzf_inflate for the blocks that are complete so far, on one of a few side streams that waits for the chunk's event:
+//          chunk k inflates while chunk k+1 uploads and chunk k+2 is read.
+// then CRC, record chain, extraction as before.
+static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_path, const Bai *bai_in, const std::vector<VRange> *ranges,
+                           svtk_bam_stats *stats) {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
-    if (!c || !bam_path) return fail(SVTK_ERR_ARG, "null argument");
     if (stats) memset(stats, 0, sizeof(*stats));
     if (int rc = set_device(c)) return rc;
     const auto t_all = std::chrono::steady_clock::now();
     c->have_reads = false;
-    const bool ranged = tid_lo >= 0;
+    const bool whole = ranges == nullptr;
 
-    // ---- host: map the file; the index first (it says which bytes of the file a reference range needs)
-    Mapped bam;
-    if (bam.open_file(bam_path) != 0) return fail(SVTK_ERR_IO, "bam: cannot open %s", bam_path);
-    if (bam.n == 0) return fail(SVTK_ERR_IO, "bam: %s is empty", bam_path);
-    if (bam.n >= (1ull << 34) - 65536) return fail(SVTK_ERR_ARG, "bam: files of 16 GiB and more must be sharded by region (32-bit word index in the decoder)");
-    std::vector<uint64_t> voffs;
-    std::vector<BaiRef> bai_refs;
-    int bai_n_ref = 0;
-    {
-        std::string bai = bai_path ? std::string(bai_path) : std::string(bam_path) + ".bai";
-        if (!bai_path && access(bai.c_str(), R_OK) != 0) {
+    struct Fd { int fd = -1; ~Fd() { if (fd >= 0) ::close(fd); } } file;
+    file.fd = ::open(bam_path, O_RDONLY);
+    if (file.fd < 0) return fail(SVTK_ERR_IO, "bam: cannot open %s", bam_path);
+    struct stat fst;
+    if (fstat(file.fd, &fst) != 0) return fail(SVTK_ERR_IO, "bam: cannot stat %s", bam_path);
+    const size_t fsize = (size_t)fst.st_size;
+    if (fsize == 0) return fail(SVTK_ERR_IO, "bam: %s is empty", bam_path);
+
+    Bai bai_local;
+    const Bai *bai = bai_in;
+    if (!bai) {
+        std::string bp = bai_path ? std::string(bai_path) : std::string(bam_path) + ".bai";
+        if (!bai_path && access(bp.c_str(), R_OK) != 0) {
             std::string alt(bam_path);
-            if (alt.size() > 4 && alt.compare(alt.size() - 4, 4, ".bam") == 0) { alt.replace(alt.size() - 4, 4, ".bai"); if (access(alt.c_str(), R_OK) == 0) bai = alt; }
+            if (alt.size() > 4 && alt.compare(alt.size() - 4, 4, ".bam") == 0) { alt.replace(alt.size() - 4, 4, ".bai"); if (access(alt.c_str(), R_OK) == 0) bp = alt; }
         }
-        if (int rc = read_bai(bai.c_str(), &bai_n_ref, voffs, bai_refs)) return rc;
-    }
-    // byte range [fb, fe) of the file to ship and record range [v_beg, v_end) (virtual offsets) to walk; whole file: everything
-    size_t fb = 0, fe = bam.n;
-    uint64_t v_beg = 0, v_end = ~0ull;
-    bool nothing = false;
-    if (ranged) {
-        if (tid_hi < tid_lo || tid_hi >= bai_n_ref) return fail(SVTK_ERR_ARG, "bam: reference range [%d, %d] outside the index's %d references", tid_lo, tid_hi, bai_n_ref);
-        v_beg = ~0ull; v_end = 0;
-        for (int t = tid_lo; t <= tid_hi; ++t) { v_beg = std::min(v_beg, bai_refs[(size_t)t].beg); v_end = std::max(v_end, bai_refs[(size_t)t].end); }
-        if (v_beg >= v_end) nothing = true;                        // no reads on these references
-        else {
-            fb = (size_t)(v_beg >> 16);
-            fe = (size_t)(v_end >> 16) + 1;                        // the block holding v_end is the last one scanned (scan stops at the first block at or after fe)
-            if (fb >= bam.n) return fail(SVTK_ERR_IO, "bam: index offset beyond the end of the file (stale .bai?)");
-        }
+        if (int rc = read_bai(bp.c_str(), bai_local)) return rc;
+        bai = &bai_local;
     }
 
-    // the table work runs on a helper thread while this thread feeds the upload ring (both only read the mapping)
-    std::vector<BgzfBlock> blk;
-    std::vector<uint64_t> coff;
-    std::vector<unsigned long long> splits;
-    unsigned long long total = 0, first_rec = 0, last_rec = 0;
-    int n_ref = 0, n_seg = 0, prep_rc = 0;
-    std::string prep_msg;
-    double prep_ms = 0;
-    size_t image_bytes = 0;                                        // bytes of the file the device image holds, from fb
+    // ---- header (host): the first bytes of the file
+    unsigned long long hdr_end = 0;
+    {
+        size_t take = std::min<size_t>(fsize, 1u << 20);
+        for (;;) {
+            std::vector<uint8_t> hb(take);
+            if (!pread_all(file.fd, hb.data(), take, 0)) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+            bool need_more = false;
+            const int rc = read_header(hb.data(), take, take == fsize, c->bam_ref_names, c->bam_ref_lens, &hdr_end, &need_more);
+            if (rc == 0) break;
+            if (!need_more || take == fsize) return rc;
+            take = std::min<size_t>(fsize, take * 8);
+        }
+    }
+    const int n_ref = (int)c->bam_ref_names.size();
+    if (n_ref != (int)bai->refs.size()) return fail(SVTK_ERR_IO, "bam: index has %zu references, BAM header %d", bai->refs.size(), n_ref);
+
+    // ---- which bytes: whole BGZF blocks around every range
+    std::vector<Span> spans;
+    if (whole) spans.push_back(Span{0, fsize});
+    else
+        for (const VRange &r : *ranges) {
+            const size_t fb = (size_t)(r.vb >> 16);
+            size_t fe = (size_t)(r.ve >> 16);
+            if (fb >= fsize || fe > fsize) return fail(SVTK_ERR_IO, "bam: index offset beyond the end of the file (stale .bai?)");
+            if ((r.ve & 0xffffu) != 0) {                            // the range ends inside a block: that block comes along whole
+                uint8_t h[18 + 256];
+                const size_t av = std::min<size_t>(sizeof h, fsize - fe);
+                uint32_t bsize = 0, xlen = 0;
+                if (!pread_all(file.fd, h, av, fe)) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+                if (parse_bgzf_header(h, av, fe, &bsize, &xlen)) return fail(SVTK_ERR_IO, "bam: index offset %zu does not point at a BGZF block (stale .bai?)", fe);
+                fe = std::min(fsize, fe + bsize);
+            }
+            if (!spans.empty() && fb <= spans.back().fe) spans.back().fe = std::max(spans.back().fe, fe);
+            else if (fe > fb) spans.push_back(Span{fb, fe});
+        }
+    size_t image_bytes = 0;
+    for (const Span &sp : spans) image_bytes += sp.fe - sp.fb;
+    if (image_bytes >= (1ull << 34) - (1u << 20))
+        return fail(SVTK_ERR_ARG, "bam: %zu bytes to load at once; 16 GiB and more must be split by region (svtk_load_bam_refs / svtk_load_bam_windows; "
+                                  "the decoder indexes the shipped bytes with 32-bit words)", image_bytes);
+
+    // ---- device + pinned buffers
+    const size_t CH = std::min<size_t>(32u << 20, std::max<size_t>(1u << 20, (image_bytes + 3) / 4 + 65536));    // small files: small pinned buffers
+    constexpr int NSTAGE = 3, NSIDE = 4, NCHEV = 8;
+    for (int i = 0; i < NSTAGE; ++i) {
+        if (int rc = c->bam_stage[i].reserve(CH)) return rc;
+        if (!c->bam_stage_ev[i]) CU(cudaEventCreateWithFlags(&c->bam_stage_ev[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < NSIDE; ++i) {
+        if (!c->bam_side[i]) CU(cudaStreamCreateWithFlags(&c->bam_side[i], cudaStreamNonBlocking));
+        if (!c->bam_side_ev[i]) CU(cudaEventCreateWithFlags(&c->bam_side_ev[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < NCHEV; ++i) if (!c->bam_chunk_ev[i]) CU(cudaEventCreateWithFlags(&c->bam_chunk_ev[i], cudaEventDisableTiming));
+    for (int i = 0; i < 5; ++i) if (!c->bam_ev[i]) CU(cudaEventCreate(&c->bam_ev[i]));
+    if (int rc = c->bam_comp.reserve(image_bytes + BZ_OVERREAD + 64)) return rc;
+    // capacity guesses for what is only known after the scan; a file that outgrows them takes the unpipelined route below
+    size_t blk_cap = std::max<size_t>(c->bam_blocks.cap / sizeof(BgzfBlock), image_bytes / 8192 + 4096);
+    if (int rc = c->bam_blocks.reserve(sizeof(BgzfBlock) * blk_cap)) return rc;
+    if (int rc = c->bam_tab.reserve(sizeof(BgzfBlock) * blk_cap)) return rc;
+    size_t infl_cap = std::max<size_t>(c->bam_infl.cap, 2 * image_bytes + (16u << 20));
+    if (int rc = c->bam_infl.reserve(infl_cap)) return rc;
+    infl_cap = c->bam_infl.cap - 128;
+    constexpr int MAX_LAUNCH = 4096;
+    if (int rc = c->bam_ctl.reserve(256 + 4 * MAX_LAUNCH)) return rc;
+    if (int rc = c->bam_h.reserve(256 + 8 * (size_t)(n_ref + 1))) return rc;
+    CU(cudaMemsetAsync(c->bam_ctl.p, 0, 256 + 4 * MAX_LAUNCH, c->stream));
+    CU(cudaMemsetAsync((char *)c->bam_comp.p + (image_bytes & ~(size_t)3), 0, BZ_OVERREAD + 64 - (image_bytes & 3), c->stream));   // the decoder looks a few bytes past the end
+    unsigned int *ctl = (unsigned int *)c->bam_ctl.p;
+    int sms = 148;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    static unsigned long long attr_seen = 0;
+    if (first_use_on_device(attr_seen)) CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (32 * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4));
+
+    // lanes per warp of the inflate launches (see k_bgzf_inflate): thin warps finish a block sooner, wide warps fit more blocks
+    // on the machine.  The whole load should fit ~18 resident single-warp CTAs per SM (the kernel's register budget).
+    long long want_warps = (long long)sms * 18;
+    if (const char *e = getenv("SVTK_BZ_WARPS")) if (*e) want_warps = std::max(1ll, atoll(e));
+    const long long est_blocks = (long long)(image_bytes / 40000) + 1;
+    int lanes = 1;
+    while (lanes < 32 && (est_blocks + lanes - 1) / lanes > want_warps) lanes <<= 1;
+    if (const char *e = getenv("SVTK_BZ_LANES")) if (*e) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) lanes = v; }
+    bool pipelined = true;
+    if (const char *e = getenv("SVTK_BAM_PIPE")) if (*e == '0') pipelined = false;
+
+    std::vector<uint64_t> coff;                            // file offset of every loaded block (sorted)
+    std::vector<BgzfBlock> tab_overflow;                   // descriptors beyond the pinned table's first guess
+    BgzfBlock *tab = (BgzfBlock *)c->bam_tab.p;            // pinned: descriptors are DMA'd from here
+    size_t n_blk = 0, launched = 0, shipped_tab = 0;
+    unsigned long long total = 0;
+    int n_launch = 0;
+    bool first_launch = true;
+    auto launch_inflate = [&](size_t b0, size_t b1, cudaStream_t st) -> int {
+        if (b1 <= b0) return 0;
+        if (n_launch >= MAX_LAUNCH) return fail(SVTK_ERR_STATE, "bam: too many inflate launches");
+        const size_t nb = b1 - b0;
+        const int smem = (lanes * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4;
+        int per_sm = 1;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (nb + lanes - 1) / lanes);
+        k_bgzf_inflate<<<grid, 32, smem, st>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)b0, (unsigned)b1,
+                                               (uint8_t *)c->bam_infl.p, ctl, ctl + 64 + n_launch, lanes);
+        CU(cudaGetLastError());
+        ++n_launch;
+        c->launches += 1;
+        return 0;
+    };
+
+    // ---- the pipeline
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    int T = (int)std::min(12u, std::max(1u, hw / 2));
+    if (const char *e = getenv("SVTK_BAM_THREADS")) if (*e) T = std::max(1, std::min(64, atoi(e)));
+    bool fits = true;                                       // the capacity guesses still hold
+    CU(cudaEventRecord(c->bam_ev[0], c->stream));
+    size_t img_off = 0;                                     // bytes of the image shipped so far
+    int k = 0;                                              // chunk counter
+    // scanner state: the block whose header comes next
+    size_t scan_span = 0, scan_off = spans.empty() ? 0 : spans[0].fb;
+    size_t span_img0 = 0;                                   // image offset of the current scan span's first byte
+    uint8_t carry[65536 + 64];                              // head of a block that straddles two chunks
+    for (size_t si = 0; si < spans.size(); ++si) {
+        for (size_t done = spans[si].fb; done < spans[si].fe;) {
+            const size_t n = std::min(CH, spans[si].fe - done);
+            const int sb = k % NSTAGE;
+            CU(cudaEventSynchronize(c->bam_stage_ev[sb]));              // the DMA that last read this buffer is over
+            char *st = (char *)c->bam_stage[sb].p;
+            {
+                const int fd = file.fd;
+                const size_t per = ((n + T - 1) / T + 4095) & ~(size_t)4095;
+                std::vector<int> ok((size_t)T, 1);
+                std::vector<std::thread> th;
+                auto rd = [&, fd, st, done, n, per](int t) { const size_t a = per * (size_t)t; if (a < n) ok[(size_t)t] = pread_all(fd, st + a, std::min(per, n - a), done + a) ? 1 : 0; };
+                for (int t = 1; t < T; ++t) if (per * (size_t)t < n) th.emplace_back(rd, t);
+                rd(0);
+                for (auto &x : th) x.join();
+                for (int v : ok) if (!v) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+            }
+            CU(cudaMemcpyAsync((char *)c->bam_comp.p + img_off, st, n, cudaMemcpyHostToDevice, c->stream));
+            CU(cudaEventRecord(c->bam_stage_ev[sb], c->stream));
+            // ---- block table of the bytes staged so far (this chunk: file bytes [done, done + n) of span si)
+            const size_t have_to = done + n;
+            while (scan_span == si && scan_off < spans[si].fe) {
+                // header + footer of the block at scan_off: from the staged chunk when it lies inside, else through a small read
+                const uint8_t *h;
+                size_t av;
+                if (scan_off >= done && scan_off + 18 + 256 <= have_to) { h = (const uint8_t *)st + (scan_off - done); av = have_to - scan_off; }
+                else {
+                    av = std::min<size_t>(18 + 256, fsize - scan_off);
+                    if (scan_off + 18 > have_to) break;                 // header not staged yet
+                    if (!pread_all(file.fd, carry, av, scan_off)) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+                    h = carry;
+                }
+                uint32_t bsize = 0, xlen = 0;
+                if (int rc = parse_bgzf_header(h, std::min<size_t>(av, 65536), scan_off, &bsize, &xlen)) return rc;
+                if (scan_off + bsize > spans[si].fe) return fail(SVTK_ERR_IO, "bam: bad BGZF block size at byte %zu", scan_off);
+                if (scan_off + bsize > have_to) break;                  // the block ends in the next chunk
+                uint32_t isize;
+                if (scan_off >= done) isize = le32((const uint8_t *)st + (scan_off + bsize - 4 - done));
+                else {                                                  // straddler: its tail is in this chunk
+                    const size_t fo = scan_off + bsize - 4;
+                    if (fo >= done) isize = le32((const uint8_t *)st + (fo - done));
+                    else { uint8_t f4[4]; if (!pread_all(file.fd, f4, 4, fo)) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path); isize = le32(f4); }
+                }
+                if (isize > 65536u) return fail(SVTK_ERR_IO, "bam: BGZF block at byte %zu claims %u inflated bytes", scan_off, isize);
+                if (n_blk >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: split the load");
+                if (fits && (n_blk >= blk_cap || total + isize > infl_cap)) fits = false;
+                BgzfBlock b;
+                b.in_beg = span_img0 + (scan_off - spans[si].fb) + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = isize; b.out_off = total;
+                if (fits) tab[n_blk] = b; else tab_overflow.push_back(b);
+                coff.push_back(scan_off);
+                ++n_blk;
+                total += isize;
+                scan_off += bsize;
+            }
+            if (scan_span == si && scan_off >= spans[si].fe && si + 1 < spans.size()) {
+                span_img0 += spans[si].fe - spans[si].fb;
+                scan_span = si + 1; scan_off = spans[si + 1].fb;
+            }
+            img_off += n;
+            done += n;
+            // ---- ship the new descriptors, launch their inflate behind this chunk's bytes
+            if (fits && pipelined && n_blk > launched) {
+                CU(cudaMemcpyAsync((BgzfBlock *)c->bam_blocks.p + shipped_tab, tab + shipped_tab, sizeof(BgzfBlock) * (n_blk - shipped_tab), cudaMemcpyHostToDevice, c->stream));
+                shipped_tab = n_blk;
+                cudaEvent_t ev = c->bam_chunk_ev[k % NCHEV];
+                CU(cudaEventRecord(ev, c->stream));
+                cudaStream_t side = c->bam_side[k % NSIDE];
+                CU(cudaStreamWaitEvent(side, ev, 0));
+                if (first_launch) { CU(cudaEventRecord(c->bam_ev[1], side)); first_launch = false; }
+                if (int rc = launch_inflate(launched, n_blk, side)) return rc;
+                launched = n_blk;
+            }
+            ++k;
+        }
+    }
+    if (scan_span + 1 < spans.size() || (!spans.empty() && scan_off != spans.back().fe))
+        return fail(SVTK_ERR_IO, "bam: BGZF blocks do not tile the file (stopped at byte %zu)", scan_off);
+    CU(cudaEventRecord(c->bam_ev[2], c->stream));           // end of the upload
+    if (!fits) {
+        // the guesses were too small: exact buffers now, the whole inflate after the upload (everything is on the device already)
+        for (int i = 0; i < NSIDE; ++i) CU(cudaStreamSynchronize(c->bam_side[i]));
+        CU(cudaStreamSynchronize(c->stream));
+        std::vector<BgzfBlock> all(n_blk);
+        const size_t in_tab = n_blk - tab_overflow.size();
+        memcpy(all.data(), tab, sizeof(BgzfBlock) * in_tab);
+        if (!tab_overflow.empty()) memcpy(all.data() + in_tab, tab_overflow.data(), sizeof(BgzfBlock) * tab_overflow.size());
+        tab_overflow.clear();
+        if (int rc = c->bam_blocks.reserve(sizeof(BgzfBlock) * n_blk)) return rc;
+        if (int rc = c->bam_tab.reserve(sizeof(BgzfBlock) * n_blk)) return rc;
+        if (int rc = c->bam_infl.reserve((size_t)total + 256)) return rc;
+        tab = (BgzfBlock *)c->bam_tab.p;
+        memcpy(tab, all.data(), sizeof(BgzfBlock) * n_blk);
+        launched = 0; shipped_tab = 0;
+        CU(cudaMemsetAsync(c->bam_ctl.p, 0, 256 + 4 * MAX_LAUNCH, c->stream));
+        n_launch = 0;
+    }
+    if (n_blk > shipped_tab) {
+        CU(cudaMemcpyAsync((BgzfBlock *)c->bam_blocks.p + shipped_tab, tab + shipped_tab, sizeof(BgzfBlock) * (n_blk - shipped_tab), cudaMemcpyHostToDevice, c->stream));
+        shipped_tab = n_blk;
+    }
+    if (first_launch) { CU(cudaEventRecord(c->bam_ev[1], c->stream)); first_launch = false; }
+    if (n_blk > launched) { if (int rc = launch_inflate(launched, n_blk, c->stream)) return rc; launched = n_blk; }
+    for (int i = 0; i < NSIDE; ++i) {                       // join the side streams
+        CU(cudaEventRecord(c->bam_side_ev[i], c->bam_side[i]));
+        CU(cudaStreamWaitEvent(c->stream, c->bam_side_ev[i], 0));
+    }
+    CU(cudaMemsetAsync((char *)c->bam_infl.p + (total & ~3ull), 0, 64 - (total & 3), c->stream));
+    CU(cudaEventRecord(c->bam_ev[3], c->stream));           // end of the inflate
+    if (stats) stats->lanes_per_warp = (uint32_t)lanes;
+    const uint32_t *infl = (const uint32_t *)c->bam_infl.p;
+    if (n_blk) {
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * 8, (n_blk + 7) / 8);
+        k_bgzf_crc<<<grid, 256, 0, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)n_blk, (const uint8_t *)c->bam_infl.p, ctl);
+        CU(cudaGetLastError());
+        c->launches += 1;
+    }
+
+    // ---- pieces of the record chain: every range, cut at the record-aligned offsets the index holds
     auto to_linear = [&](uint64_t v, unsigned long long *lin) -> int {
         const uint64_t co = v >> 16, uo = v & 0xffffu;
         auto it = std::lower_bound(coff.begin(), coff.end(), co);
         if (it == coff.end() || *it != co) {
-            if (!coff.empty() && co == coff.back() + (blk.back().in_beg + fb - coff.back()) + blk.back().in_len + 8 && uo == 0) { *lin = total; return 0; }   // just past the last block
-            return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a BGZF block (stale .bai?)", (unsigned long long)co);
+            // just past the last loaded block of a span: the end of the previous block
+            if (uo == 0 && it != coff.begin()) {
+                const size_t j = (size_t)(it - coff.begin()) - 1;
+                const BgzfBlock &pb = tab[j];
+                *lin = pb.out_off + pb.isize;
+                return 0;
+            }
+            return fail(SVTK_ERR_IO, "bam: index offset %llu does not point at a loaded BGZF block (stale .bai?)", (unsigned long long)co);
         }
-        const BgzfBlock &b = blk[(size_t)(it - coff.begin())];
+        const BgzfBlock &b = tab[(size_t)(it - coff.begin())];
         if (uo > b.isize) return fail(SVTK_ERR_IO, "bam: index offset beyond its block (stale .bai?)");
         *lin = b.out_off + uo;
         return 0;
     };
-    auto prep = [&]() -> int {
-        unsigned long long hdr_end = 0;
-        if (int rc = read_header(bam.p, bam.n, c->bam_ref_names, c->bam_ref_lens, &hdr_end)) return rc;
-        n_ref = (int)c->bam_ref_names.size();
-        if (n_ref != bai_n_ref) return fail(SVTK_ERR_IO, "bam: index has %d references, BAM header %d", bai_n_ref, n_ref);
-        if (nothing) { splits.push_back(0); return 0; }
-        if (int rc = scan_bgzf(bam.p, bam.n, fb, fe, fb, blk, coff)) return rc;
-        if (blk.empty()) return fail(SVTK_ERR_IO, "bam: no BGZF block at index offset %zu (stale .bai?)", fb);
-        total = blk.back().out_off + blk.back().isize;
-        if (blk.size() >= 0xfffffff0ull) return fail(SVTK_ERR_ARG, "bam: more than 2^32 BGZF blocks: shard the file");
-        if (ranged) {
-            if (int rc = to_linear(v_beg, &first_rec)) return rc;
-            if (int rc = to_linear(v_end, &last_rec)) return rc;
-        } else { first_rec = hdr_end; last_rec = total; }
-        if (first_rec > last_rec || last_rec > total) return fail(SVTK_ERR_IO, "bam: header / index offsets beyond the file");
-        splits.reserve(voffs.size() + 2);
-        splits.push_back(first_rec);
-        for (uint64_t v : voffs) {
-            if (ranged && (v <= v_beg || v >= v_end)) continue;
+    std::vector<unsigned long long> splits;                 // (begin, end) pairs, linear offsets into the inflated image
+    auto add_range = [&](unsigned long long lb, unsigned long long le, uint64_t vb, uint64_t ve) -> int {
+        if (lb >= le) return 0;
+        unsigned long long prev = lb;
+        auto it = std::upper_bound(bai->voffs.begin(), bai->voffs.end(), vb);
+        for (; it != bai->voffs.end() && *it < ve; ++it) {
             unsigned long long lin = 0;
-            if (int rc = to_linear(v, &lin)) return rc;
-            if (lin > first_rec && lin < last_rec) splits.push_back(lin);
+            if (int rc = to_linear(*it, &lin)) return rc;
+            if (lin > prev && lin < le) { splits.push_back(prev); splits.push_back(lin); prev = lin; }
         }
-        std::sort(splits.begin(), splits.end());
-        splits.erase(std::unique(splits.begin(), splits.end()), splits.end());
-        n_seg = first_rec < last_rec ? (int)splits.size() : 0;
-        splits.push_back(last_rec);
+        splits.push_back(prev); splits.push_back(le);
         return 0;
     };
-    std::thread prep_thread([&]() {
-        prep_rc = prep();
-        if (prep_rc) prep_msg = svtk_last_error();            // the message lives in the helper thread's slot
-        prep_ms = ms_since(t_all);
-    });
-    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{prep_thread};
-
-    // ---- device: the compressed image (needs nothing from the tables).  A ranged load does not know yet where its last block
-    // ends: it ships up to the end of the block that holds v_end, which is at most 64 KiB past fe
-    for (int i = 0; i < 4; ++i) if (!c->bam_ev[i]) CU(cudaEventCreate(&c->bam_ev[i]));
-    image_bytes = nothing ? 0 : std::min(bam.n, ranged ? fe + 65536 : bam.n) - fb;
-    if (int rc = c->bam_comp.reserve(image_bytes + BZ_OVERREAD)) return rc;
-    CU(cudaMemsetAsync((char *)c->bam_comp.p + (image_bytes & ~(size_t)3), 0, BZ_OVERREAD - (image_bytes & 3), c->stream));   // the decoder looks a few bytes past the end
-    CU(cudaEventRecord(c->bam_ev[0], c->stream));
-    if (image_bytes) if (int rc = upload_file(c, c->bam_comp.p, bam.p + fb, image_bytes)) return rc;
-    prep_thread.join();
-    if (prep_rc) return fail(prep_rc, "%s", prep_msg.c_str());
-    const double host_ms = prep_ms;
-
-    // ---- device: tables, inflate
-    if (int rc = c->bam_infl.reserve((size_t)total + 64)) return rc;
-    if (int rc = c->bam_blocks.reserve(sizeof(BgzfBlock) * std::max<size_t>(blk.size(), 1))) return rc;
-    if (int rc = c->bam_splits.reserve(8 * splits.size())) return rc;
+    if (whole) {
+        if (hdr_end > total) return fail(SVTK_ERR_IO, "bam: header / index offsets beyond the file");
+        // virtual offset of the first record: the block holding inflated byte hdr_end
+        size_t j = 0;
+        while (j + 1 < n_blk && tab[j + 1].out_off <= hdr_end) ++j;
+        const uint64_t v_first = n_blk ? (coff[j] << 16 | (hdr_end - tab[j].out_off)) : 0;
+        if (int rc = add_range(hdr_end, total, v_first, ~0ull)) return rc;
+    } else
+        for (const VRange &r : *ranges) {
+            unsigned long long lb = 0, le = 0;
+            if (int rc = to_linear(r.vb, &lb)) return rc;
+            if (int rc = to_linear(r.ve, &le)) return rc;
+            if (lb > le || le > total) return fail(SVTK_ERR_IO, "bam: index offsets beyond the file (stale .bai?)");
+            if (int rc = add_range(lb, le, r.vb, r.ve)) return rc;
+        }
+    const int n_seg = (int)(splits.size() / 2);
+    if (int rc = c->bam_splits.reserve(8 * std::max<size_t>(splits.size(), 2))) return rc;
     if (int rc = c->bam_seg.reserve(16 * (size_t)std::max(n_seg, 1))) return rc;
-    if (int rc = c->bam_ctl.reserve(256)) return rc;
     if (int rc = c->bam_h.reserve(256 + 8 * (size_t)(n_ref + 1) + 16 * (size_t)std::max(n_seg, 1))) return rc;
-    CU(cudaMemsetAsync(c->bam_ctl.p, 0, 256, c->stream));
-    CU(cudaMemsetAsync((char *)c->bam_infl.p + (total & ~3ull), 0, 64 - (total & 3), c->stream));
-    if (int rc = upload(c, c->bam_blocks.p, blk.data(), sizeof(BgzfBlock) * blk.size())) return rc;
-    if (int rc = upload(c, c->bam_splits.p, splits.data(), 8 * splits.size())) return rc;
-    CU(cudaEventRecord(c->bam_ev[1], c->stream));
-    unsigned int *ctl = (unsigned int *)c->bam_ctl.p;
-    const uint32_t *infl = (const uint32_t *)c->bam_infl.p;
-    if (!blk.empty()) {
-        int sms = 148;
-        CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-        // thin warps while the blocks are few (see k_bgzf_inflate): measured best at 12-16 warps per SM (B200: 85 MB / 238 MB / 950 MB
-        // files 2.9x / 2.0x / 1.2x faster than with 32 lanes), then widen
-        long long want_warps = (long long)sms * 20;
-        if (const char *e = getenv("SVTK_BZ_WARPS")) if (*e) want_warps = std::max(1ll, atoll(e));
-        int lanes = 1;
-        while (lanes < 32 && (long long)((blk.size() + lanes - 1) / lanes) > want_warps) lanes <<= 1;
-        const int smem = lanes * BZ_TABLE_WORDS * 4;
-        static unsigned long long attr_seen = 0;
-        if (first_use_on_device(attr_seen)) CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * BZ_TABLE_WORDS * 4));
-        int per_sm = 1;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (blk.size() + lanes - 1) / lanes);
-        k_bgzf_inflate<<<grid, 32, smem, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)blk.size(),
-                                                     (uint8_t *)c->bam_infl.p, ctl, lanes);
-        if (stats) stats->lanes_per_warp = (uint32_t)lanes;
-        CU(cudaGetLastError());
-        c->launches += 1;
-    }
-    CU(cudaEventRecord(c->bam_ev[2], c->stream));
-    if (!blk.empty()) {
-        int sms = 148;
-        CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * 8, (blk.size() + 7) / 8);
-        k_bgzf_crc<<<grid, 256, 0, c->stream>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)blk.size(),
-                                              (const uint8_t *)c->bam_infl.p, ctl);
-        CU(cudaGetLastError());
-        c->launches += 1;
-    }
+    if (n_seg) if (int rc = upload(c, c->bam_splits.p, splits.data(), 8 * splits.size())) return rc;
 
     // ---- record chain: count, prefix (host: a few thousand pieces), fill
     unsigned int *hctl = (unsigned int *)c->bam_h.p;
@@ -625,7 +854,7 @@ static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_pa
         const unsigned long long *cnt = (const unsigned long long *)c->bam_h.p;
         for (int s = 0; s < n_seg; ++s) { base[2 * s] = (unsigned long long)n_reads; base[2 * s + 1] = (unsigned long long)n_words; n_reads += (long long)cnt[2 * s]; n_words += (long long)cnt[2 * s + 1]; }
     }
-    if (n_reads >= (1ll << 31) - 1024) return fail(SVTK_ERR_ARG, "bam: more than 2^31 reads per device: shard the file");
+    if (n_reads >= (1ll << 31) - 1024) return fail(SVTK_ERR_ARG, "bam: more than 2^31 reads per device: split the load");
     const size_t nr = (size_t)n_reads, nw = (size_t)n_words;
     if (int rc = c->r_pos.reserve(4 * std::max<size_t>(nr, 1))) return rc;
     if (int rc = c->r_end.reserve(4 * std::max<size_t>(nr, 1))) return rc;
@@ -653,7 +882,8 @@ static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_pa
                                                                                (long long *)c->tmp_b.p, ctl);
     CU(cudaGetLastError());
     c->launches += 1;
-    CU(cudaEventRecord(c->bam_ev[3], c->stream));
+    cudaEvent_t ev_done = c->bam_ev[4];
+    CU(cudaEventRecord(ev_done, c->stream));
     std::vector<int64_t> tid_off((size_t)n_ref + 1, 0);
     CU(cudaMemcpyAsync(hctl, ctl, 64, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(hctl + 16, c->tmp_b.p, 8 * (size_t)(n_ref + 1), cudaMemcpyDeviceToHost, c->stream));
@@ -661,7 +891,7 @@ static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_pa
     if (hctl[BAM_CTL_ORDER]) return fail(SVTK_ERR_IO, "bam: records are not in coordinate order (or a refID is outside the header's dictionary)");
     memcpy(tid_off.data(), hctl + 16, 8 * (size_t)(n_ref + 1));
     c->bam_infl_bytes = total; c->bam_n_rec = n_reads;
-    c->h2d_bytes += image_bytes + sizeof(BgzfBlock) * blk.size() + 8 * splits.size();
+    c->h2d_bytes += image_bytes + sizeof(BgzfBlock) * n_blk + 8 * splits.size();
 
     svtk_reads d{};
     d.n_tid = n_ref; d.n_reads = n_reads; d.n_words = n_words; d.tid_off = tid_off.data();
@@ -670,22 +900,76 @@ static int load_bam_impl(svtk_ctx *ctx, const char *bam_path, const char *bai_pa
     if (int rc = adopt_device_reads(c, &d)) return rc;
     c->reads_from_bam = true;
     if (stats) {
-        float up = 0, inf = 0, par = 0;
-        cudaEventElapsedTime(&up, c->bam_ev[0], c->bam_ev[1]); cudaEventElapsedTime(&inf, c->bam_ev[1], c->bam_ev[2]); cudaEventElapsedTime(&par, c->bam_ev[2], c->bam_ev[3]);
-        stats->file_bytes = bam.n; stats->image_bytes = image_bytes; stats->n_blocks = blk.size(); stats->inflated_bytes = total; stats->n_reads = (uint64_t)n_reads;
-        stats->n_words = (uint64_t)n_words; stats->n_ref = n_ref; stats->n_pieces = (uint32_t)n_seg; stats->host_scan_ms = (float)host_ms;
-        stats->upload_ms = up; stats->inflate_ms = inf; stats->parse_ms = par; stats->total_ms = (float)ms_since(t_all);
+        float up = 0, inf = 0, span = 0;
+        cudaEventElapsedTime(&up, c->bam_ev[0], c->bam_ev[2]); cudaEventElapsedTime(&inf, c->bam_ev[1], c->bam_ev[3]); cudaEventElapsedTime(&span, c->bam_ev[0], c->bam_ev[3]);
+        stats->file_bytes = fsize; stats->image_bytes = image_bytes; stats->n_blocks = n_blk; stats->inflated_bytes = total; stats->n_reads = (uint64_t)n_reads;
+        stats->n_words = (uint64_t)n_words; stats->n_ref = n_ref; stats->n_pieces = (uint32_t)n_seg; stats->host_scan_ms = 0.f;
+        stats->upload_ms = up; stats->inflate_ms = inf; stats->load_span_ms = span; stats->n_spans = (uint32_t)spans.size(); stats->inflate_launches = (uint32_t)n_launch;
+        float par = 0;
+        cudaEventElapsedTime(&par, c->bam_ev[3], ev_done);
+        stats->parse_ms = par; stats->total_ms = (float)ms_since(t_all);
     }
     return 0;
 }
 
 extern "C" int svtk_load_bam(svtk_ctx *ctx, const char *bam_path, const char *bai_path, svtk_bam_stats *stats) {
-    return load_bam_impl(ctx, bam_path, bai_path, -1, -1, stats);
+    if (!ctx || !bam_path) return fail(SVTK_ERR_ARG, "null argument");
+    return load_bam_ranges(ctx, bam_path, bai_path, nullptr, nullptr, stats);
+}
+
+static int open_bai(const char *bam_path, const char *bai_path, Bai &bai) {
+    std::string bp = bai_path ? std::string(bai_path) : std::string(bam_path) + ".bai";
+    if (!bai_path && access(bp.c_str(), R_OK) != 0) {
+        std::string alt(bam_path);
+        if (alt.size() > 4 && alt.compare(alt.size() - 4, 4, ".bam") == 0) { alt.replace(alt.size() - 4, 4, ".bai"); if (access(alt.c_str(), R_OK) == 0) bp = alt; }
+    }
+    return read_bai(bp.c_str(), bai);
 }
 
 extern "C" int svtk_load_bam_refs(svtk_ctx *ctx, const char *bam_path, const char *bai_path, int32_t tid_lo, int32_t tid_hi, svtk_bam_stats *stats) {
+    if (!ctx || !bam_path) return fail(SVTK_ERR_ARG, "null argument");
     if (tid_lo < 0) return fail(SVTK_ERR_ARG, "bad reference range");
-    return load_bam_impl(ctx, bam_path, bai_path, tid_lo, tid_hi, stats);
+    Bai bai;
+    if (int rc = open_bai(bam_path, bai_path, bai)) return rc;
+    if (tid_hi < tid_lo || tid_hi >= (int)bai.refs.size()) return fail(SVTK_ERR_ARG, "bam: reference range [%d, %d] outside the index's %zu references", tid_lo, tid_hi, bai.refs.size());
+    std::vector<VRange> r;
+    uint64_t vb = ~0ull, ve = 0;
+    for (int t = tid_lo; t <= tid_hi; ++t) { vb = std::min(vb, bai.refs[(size_t)t].beg); ve = std::max(ve, bai.refs[(size_t)t].end); }
+    if (vb < ve) r.push_back(VRange{vb, ve});
+    return load_bam_ranges(ctx, bam_path, bai_path, &bai, &r, stats);
+}
+
+// Only what the given windows can see: per window the region sam_itr_queryi(idx, chrom - 1, start - 1, end - 1) would query
+// (refinement.c:114), widened to the bin chunks that can hold an overlapping read.  A region shard of a single-contig job, or a
+// sparse VCF against a whole-genome BAM, ships and inflates only those parts of the file.
+extern "C" int svtk_load_bam_windows(svtk_ctx *ctx, const char *bam_path, const char *bai_path, const svtk_windows *w, svtk_bam_stats *stats) {
+    if (!ctx || !bam_path || !w || w->n_win < 0) return fail(SVTK_ERR_ARG, "null argument");
+    if (w->n_win > 0 && (!w->chrom || !w->start || !w->end)) return fail(SVTK_ERR_ARG, "null window array");
+    Bai bai;
+    if (int rc = open_bai(bam_path, bai_path, bai)) return rc;
+    // union of the windows' regions per reference first (windows overlap heavily), then one index query per merged region
+    std::vector<std::vector<std::pair<long long, long long>>> reg(bai.refs.size());
+    for (int i = 0; i < w->n_win; ++i) {
+        const long long tid = (long long)w->chrom[i] - 1;
+        if (tid < 0 || tid >= (long long)bai.refs.size()) continue;
+        const long long beg = (long long)(uint32_t)(w->start[i] - 1u), end = (long long)(uint32_t)(w->end[i] - 1u);   // uint32 arithmetic, then widened
+        if (end < beg) continue;                               // hts_itr_query: NULL iterator
+        reg[(size_t)tid].push_back({beg, std::max(end, beg + 1)});
+    }
+    std::vector<VRange> r;
+    for (size_t t = 0; t < reg.size(); ++t) {
+        auto &v = reg[t];
+        if (v.empty()) continue;
+        std::sort(v.begin(), v.end());
+        long long b = v[0].first, e = v[0].second;
+        for (size_t i = 1; i <= v.size(); ++i) {
+            if (i < v.size() && v[i].first <= e + 16384) { e = std::max(e, v[i].second); continue; }
+            bai_query(bai.refs[t], b, e, r);
+            if (i < v.size()) { b = v[i].first; e = v[i].second; }
+        }
+    }
+    merge_ranges(r);
+    return load_bam_ranges(ctx, bam_path, bai_path, &bai, &r, stats);
 }
 
 extern "C" int svtk_bam_n_ref(const svtk_ctx *ctx) { return ctx ? (int)reinterpret_cast<const Ctx *>(ctx)->bam_ref_names.size() : 0; }

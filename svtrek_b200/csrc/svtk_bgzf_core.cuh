@@ -150,13 +150,14 @@ struct BzLane {
     BzBits b;
     uint8_t *out;
     uint32_t op, out_len;                 // bytes produced so far / expected (ISIZE)
+    uint32_t pend_len, pend_dist;         // rest of a match still to copy (bz_step copies BZ_CHUNK bytes per call)
     int state, last, err;
 };
 
 BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len) {
     z.b.w = words; z.b.end = in_end;
     bz_prime(z.b, in_beg);
-    z.out = out; z.op = 0; z.out_len = out_len; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
+    z.out = out; z.op = 0; z.out_len = out_len; z.pend_len = 0; z.pend_dist = 0; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
 }
 
 BZ_HD void bz_fail(BzLane &z, int e) { z.err = e; z.state = BZ_S_IDLE; }
@@ -228,86 +229,107 @@ BZ_HD void bz_header(BzLane &z, BzTables &T) {
     z.state = BZ_S_SYMBOLS;
 }
 
-// LZ77 copy of len bytes from dist bytes back (bounds checked by the caller).  The window is the block's own output in
-// global memory, so a byte-by-byte loop pays one memory round trip per byte (each load may alias the previous store).
-// dist >= 8: groups of up to 8 loads issued together, then their stores.  dist < 8 (runs): the period is read once into a
-// register and replayed.  (Collecting the output in a 64-bit register and storing aligned words was measured slower on
-// B200: the decoder is bound by instruction latency of the few resident warps, not by cache accesses -- DESIGN.md 9.)
-BZ_HD void bz_copy(uint8_t *o, uint32_t dist, uint32_t len) {
-    const uint8_t *src = o - dist;
-    if (dist >= 8u) {
-#ifndef SVTK_BZ_NOSHORT
-        if (len <= 4u) {                                    // the common short match: one group of 4
-            uint8_t t[4];
+// ---- length / distance symbol -> {base, extra bits}.  On the GPU two small tables in shared memory (lanes of a warp index them
+// divergently: 29 / 30 words, one bank each, so no conflicts); arithmetic on the host.  RFC 1951 3.2.5.
+BZ_HD uint32_t bz_len_entry(int k) {      // k = symbol - 257 in 0..28 -> base | extra bits << 16
+    if (k < 8) return (uint32_t)(k + 3);
+    if (k == 28) return 258u;
+    const int eb = (k - 4) >> 2;
+    return (3u + ((4u + (uint32_t)(k & 3)) << eb)) | (uint32_t)eb << 16;
+}
+BZ_HD uint32_t bz_dist_entry(int d) {     // d in 0..29 -> base | extra bits << 16
+    if (d < 4) return (uint32_t)d + 1u;
+    const int eb = (d >> 1) - 1;
+    return (1u + ((2u + (uint32_t)(d & 1)) << eb)) | (uint32_t)eb << 16;
+}
+constexpr int BZ_LUT_WORDS = 64;          // [0..28] lengths, [32..61] distances
+struct BzLut { const uint32_t *w; };      // nullptr: compute (host)
+BZ_HD uint32_t bz_len_lookup(const BzLut &L, int k) { return L.w ? L.w[k] : bz_len_entry(k); }
+BZ_HD uint32_t bz_dist_lookup(const BzLut &L, int d) { return L.w ? L.w[32 + d] : bz_dist_entry(d); }
+
+// ---- LZ77 copy, BZ_CHUNK bytes per call.  The window is the block's own output in global memory.  A match is copied in chunks so
+// that every lane of a warp runs the SAME short code whatever its match length (a long match just takes more rounds): the warp
+// pays for the union of its lanes' paths, and loops with lane-dependent trip counts were most of that union.
+// dist >= BZ_CHUNK: the source lies wholly behind the chunk.  dist < BZ_CHUNK (a run): the first chunk replicates the period from
+// a register; after it the distance is raised to the smallest multiple of the period >= BZ_CHUNK (same bytes: the data is
+// periodic), so later chunks are plain copies again.
+constexpr uint32_t BZ_CHUNK = 8;
+BZ_HD void bz_copy_chunk(BzLane &z) {
+    uint8_t *o = z.out + z.op;
+    const uint32_t n = z.pend_len < BZ_CHUNK ? z.pend_len : BZ_CHUNK;
+    uint32_t dist = z.pend_dist;
+    unsigned long long v;                 // the chunk's bytes, first byte in the low bits
 #if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (uint32_t i = 0; i < 4u; ++i) if (i < len) t[i] = src[i];
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (uint32_t i = 0; i < 4u; ++i) if (i < len) o[i] = t[i];
-            return;
-        }
-#endif
-        for (uint32_t k = 0; k < len; k += 8u) {
-            const uint32_t n = len - k < 8u ? len - k : 8u;
-            uint8_t t[8];
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (uint32_t i = 0; i < 8u; ++i) if (i < n) t[i] = src[k + i];
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-            for (uint32_t i = 0; i < 8u; ++i) if (i < n) o[k + i] = t[i];
-        }
-    } else {
-        unsigned long long pat = 0;
-        for (uint32_t i = 0; i < dist; ++i) pat |= (unsigned long long)src[i] << (8u * i);
-        uint32_t ph = 0;
-        for (uint32_t k = 0; k < len; ++k) { o[k] = (uint8_t)(pat >> (8u * ph)); ph = ph + 1u == dist ? 0u : ph + 1u; }
+    {   // three aligned words cover the 8 source bytes wherever they start (bytes past the source are ignored; the buffers are
+        // readable 16 bytes past their end)
+        const uintptr_t a = (uintptr_t)(o - dist);
+        const uint32_t *aw = (const uint32_t *)(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 3) * 8u, w0 = aw[0], w1 = aw[1], w2 = aw[2];
+        v = (unsigned long long)__funnelshift_r(w0, w1, sh) | (unsigned long long)__funnelshift_r(w1, w2, sh) << 32;
     }
+#else
+    v = 0;
+    for (uint32_t i = 0; i < BZ_CHUNK && i < dist; ++i) v |= (unsigned long long)o[(long long)i - (long long)dist] << (8u * i);
+#endif
+    if (dist < BZ_CHUNK) {                // run: bytes [0, dist) of v are the period; replicate it over the chunk
+        const unsigned long long per = v & ((1ull << (8u * dist)) - 1ull);
+        v = per;
+        uint32_t have = dist;
+        while (have < BZ_CHUNK) { v |= v << (8u * have); have <<= 1; }      // doubling keeps the phase: have stays a multiple of dist
+        // later chunks: plain copies from the smallest multiple of the period >= BZ_CHUNK back (1..7 -> 8 8 9 8 10 12 14)
+        z.pend_dist = (uint32_t)(0x0E0C0A0809080800ull >> (8u * dist)) & 255u;
+    }
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (uint32_t i = 0; i < BZ_CHUNK; ++i) if (i < n) o[i] = (uint8_t)(v >> (8u * i));
+    z.op += n; z.pend_len -= n;
 }
 
 // A corrupt stream can keep decoding "symbols" out of whatever follows its payload; the bound is checked once per burst of
-// BZ_BURST steps (a step consumes at most 48 bits), so the compressed buffer must be readable BZ_OVERREAD bytes past its end.
+// BZ_BURST steps (a step consumes at most 2 x 48 bits), so the compressed buffer must be readable BZ_OVERREAD bytes past its end.
 constexpr int BZ_BURST = 64;
-constexpr int BZ_OVERREAD = 8 * BZ_BURST + 64;
+constexpr int BZ_OVERREAD = 16 * BZ_BURST + 64;
 BZ_HD void bz_check_input(BzLane &z) {
     if (z.state != BZ_S_IDLE && bz_ip(z.b) > z.b.end + 8) bz_fail(z, BZ_ERR_IN);
 }
 
-// one literal/length symbol (and its distance + copy).  Only called in state BZ_S_SYMBOLS.
-BZ_HD void bz_step(BzLane &z, const BzTables &T) {
+// One round of a lane in state BZ_S_SYMBOLS: the next chunk of a pending match, or up to two literal/length symbols (the second
+// only after a literal: a refill leaves >= 32 bits, a literal takes <= 15) and, for a match, its distance and first chunk.
+BZ_HD void bz_step(BzLane &z, const BzTables &T, const BzLut &L) {
     BzBits &b = z.b;
-    bz_refill(b);
-    const int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
-    if (s < 256) {
+    if (z.pend_len == 0u) {
+        bz_refill(b);
+        int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
+        if (s < 256 && s >= 0) {
+            if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
+            z.out[z.op++] = (uint8_t)s;
+            s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
+            if (s < 256 && s >= 0) {
+                if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
+                z.out[z.op++] = (uint8_t)s;
+                return;
+            }
+        }
         if (s < 0) return bz_fail(z, BZ_ERR_CODE);
-        if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
-        z.out[z.op++] = (uint8_t)s;
-        return;
+        if (s == 256) {
+            if (z.last) bz_finish(z); else z.state = BZ_S_HEADER;
+            return;
+        }
+        if (s > 285) return bz_fail(z, BZ_ERR_CODE);
+        bz_refill(b);
+        const uint32_t le = bz_len_lookup(L, s - 257);
+        const uint32_t len = (le & 0xffffu) + bz_take(b, (int)(le >> 16));
+        const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
+        if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
+        bz_refill(b);
+        const uint32_t de = bz_dist_lookup(L, d);
+        const uint32_t dist = (de & 0xffffu) + bz_take(b, (int)(de >> 16));
+        if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
+        if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
+        z.pend_len = len; z.pend_dist = dist;
     }
-    if (s == 256) {
-        if (z.last) bz_finish(z); else z.state = BZ_S_HEADER;
-        return;
-    }
-    if (s > 285) return bz_fail(z, BZ_ERR_CODE);
-    uint32_t len;
-    if (s < 265) len = (uint32_t)(s - 254);
-    else if (s == 285) len = 258;
-    else { const int k = s - 261, eb = k >> 2; len = 3u + ((4u + (uint32_t)(k & 3)) << eb) + bz_take(b, eb); }
-    bz_refill(b);
-    const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
-    if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
-    uint32_t dist;
-    if (d < 4) dist = (uint32_t)d + 1u;
-    else { const int eb = (d >> 1) - 1; dist = 1u + ((2u + (uint32_t)(d & 1)) << eb) + bz_take(b, eb); }
-    if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
-    if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
-    bz_copy(z.out + z.op, dist, len);
-    z.op += len;
+    bz_copy_chunk(z);
 }
 
 // Inflate one raw DEFLATE stream (the payload of one BGZF block): words/in_beg/in_end locate it inside the compressed
@@ -317,9 +339,10 @@ BZ_HD int bz_inflate(const uint32_t *words, unsigned long long in_beg, unsigned 
                      BzTables &T) {
     BzLane z;
     bz_begin(z, words, in_beg, in_end, out, out_len);
+    const BzLut L{nullptr};
     while (z.state != BZ_S_IDLE) {
         if (z.state == BZ_S_HEADER) bz_header(z, T);
-        else bz_step(z, T);
+        else bz_step(z, T, L);
         bz_check_input(z);
     }
     return z.err;

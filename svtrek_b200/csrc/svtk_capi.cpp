@@ -93,17 +93,47 @@ int set_device(Ctx *c) {
 
 static int finish_reads(Ctx *c) {
     c->reads_from_bam = false;            // svtk_load_bam sets it again after adopting its own arrays
-    // planner look-back bound: max(end - pos) over the read set; and the packed-CIGAR contract of svtk_reads
-    if (int rc = c->scratch4.reserve(64)) return rc;
+    c->reads.tiles = nullptr; c->reads.tile_off = nullptr;
+    // the svtk_reads contract, checked on the host where it is cheap: tid_off monotone inside [0, n_reads]
+    for (size_t t = 0; t + 1 < c->h_tid_off.size(); ++t)
+        if (c->h_tid_off[t] < 0 || c->h_tid_off[t] > c->h_tid_off[t + 1] || c->h_tid_off[t + 1] > c->reads.n_reads)
+            return fail(SVTK_ERR_ARG, "svtk_reads: tid_off must be non-decreasing within [0, n_reads] (reference %zu)", t);
+    if (!c->h_tid_off.empty() && c->h_tid_off[0] != 0) return fail(SVTK_ERR_ARG, "svtk_reads: tid_off[0] must be 0");
+    // planner look-back bound: max(end - pos) over the read set; the packed-CIGAR / coordinate-order contract; the last read
+    // position of every reference (sizes the position tiles)
+    const int n_tid = c->reads.n_tid;
+    if (int rc = c->scratch4.reserve(64 + 4 * (size_t)std::max(n_tid, 1))) return rc;
     CU(cudaMemsetAsync(c->scratch4.p, 0, 8, c->stream));
     CU(launch_max_span(c->reads.pos, c->reads.end, c->reads.n_reads, (uint32_t *)c->scratch4.p, c->stream));
     CU(launch_check_layout(c->reads, (unsigned long long)c->n_words, (unsigned int *)c->scratch4.p + 1, c->stream));
-    c->launches += 2 * (c->reads.n_reads > 0);
-    uint32_t ms[2] = {1, 0};
-    CU(cudaMemcpyAsync(ms, c->scratch4.p, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(launch_last_pos(c->reads, (uint32_t *)c->scratch4.p + 16, c->stream));
+    c->launches += 3 * (c->reads.n_reads > 0);
+    std::vector<uint32_t> back(16 + (size_t)std::max(n_tid, 1), 0u);
+    back[0] = 1;
+    CU(cudaMemcpyAsync(back.data(), c->scratch4.p, 64 + 4 * (size_t)n_tid, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    if (ms[1]) return fail(SVTK_ERR_ARG, "svtk_reads: CIGARs must be packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1], cigar_off[0] == 0, last end == n_words)");
-    c->reads.max_span = std::max(ms[0], 1u);
+    if (c->reads.n_reads > 0) {
+        if (back[1] & 1u) return fail(SVTK_ERR_ARG, "svtk_reads: CIGARs must be packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1], cigar_off[0] == 0, last end == n_words)");
+        if (back[1] & 2u) return fail(SVTK_ERR_ARG, "svtk_reads: reads must be sorted by pos within each reference (BAM coordinate order)");
+        if (back[1] & 4u) return fail(SVTK_ERR_ARG, "svtk_reads: end must be >= pos (bam_endpos)");
+    }
+    c->reads.max_span = std::max(back[0], 1u);
+    // position tiles: per reference, the first read at or right of every 4 096-base boundary -- what the .bai's linear index is to
+    // the reference's iterator (hts.c:3099-3111).  Built once per load; k_refine_warp starts its two read-range searches there.
+    if (c->reads.n_reads > 0 && n_tid > 0) {
+        std::vector<long long> toff((size_t)n_tid + 1, 0);
+        for (int t = 0; t < n_tid; ++t) {
+            const bool has = c->h_tid_off[(size_t)t + 1] > c->h_tid_off[(size_t)t];
+            toff[(size_t)t + 1] = toff[(size_t)t] + (has ? (long long)(back[16 + (size_t)t] >> pos_tile_shift()) + 2 : 0);
+        }
+        if (int rc = c->pos_tiles.reserve(4 * (size_t)std::max(toff.back(), 1ll))) return rc;
+        if (int rc = c->pos_tile_off.reserve(8 * ((size_t)n_tid + 1))) return rc;
+        if (int rc = upload(c, c->pos_tile_off.p, toff.data(), 8 * ((size_t)n_tid + 1))) return rc;
+        CU(launch_pos_tiles(c->reads, (uint32_t *)c->pos_tiles.p, (const long long *)c->pos_tile_off.p, c->stream));
+        c->launches += 1;
+        CU(cudaStreamSynchronize(c->stream));               // `toff` is pageable: the upload above staged it, but keep the contract simple
+        c->reads.tiles = (const uint32_t *)c->pos_tiles.p; c->reads.tile_off = (const long long *)c->pos_tile_off.p;
+    }
     c->have_reads = true;
     c->index_valid = false;
     return 0;
@@ -343,7 +373,7 @@ int adopt_device_reads(Ctx *c, const svtk_reads *d) {
     if (c->h_tid_off.back() != d->n_reads) return fail(SVTK_ERR_ARG, "tid_off[n_tid] != n_reads");
     if (int rc = upload(c, c->r_tid_off.p, c->h_tid_off.data(), sizeof(long long) * (size_t)(d->n_tid + 1))) return rc;
     c->reads = LaunchReads{d->n_tid, d->n_reads, (const long long *)c->r_tid_off.p, d->pos, d->end, d->n_cigar,
-                           (const unsigned long long *)d->cigar_off, d->cigar, 1};
+                           (const unsigned long long *)d->cigar_off, d->cigar, 1, nullptr, nullptr};
     c->n_words = d->n_words;
     return finish_reads(c);
 }
@@ -393,14 +423,17 @@ void svtk_destroy(svtk_ctx *ctx) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items,
-                      &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
+                      &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->pos_tiles, &c->pos_tile_off, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
                       &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl, &c->bam_comp, &c->bam_infl, &c->bam_blocks,
                       &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h, &c->h_audit}) b->release();
     for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
-    for (int i = 0; i < 4; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
-    c->bam_h.release();
+    for (int i = 0; i < 5; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
+    c->bam_h.release(); c->bam_tab.release();
+    for (int i = 0; i < 3; ++i) { c->bam_stage[i].release(); if (c->bam_stage_ev[i]) cudaEventDestroy(c->bam_stage_ev[i]); }
+    for (int i = 0; i < 4; ++i) { if (c->bam_side_ev[i]) cudaEventDestroy(c->bam_side_ev[i]); if (c->bam_side[i]) cudaStreamDestroy(c->bam_side[i]); }
+    for (int i = 0; i < 8; ++i) if (c->bam_chunk_ev[i]) cudaEventDestroy(c->bam_chunk_ev[i]);
     if (c->poa_side) cudaStreamDestroy(c->poa_side);
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
@@ -443,7 +476,7 @@ int svtk_load_reads(svtk_ctx *ctx, const svtk_reads *h) {
     if (int rc = upload(c, c->r_cigar.p, h->cigar, 4 * nw)) return rc;
     c->reads = LaunchReads{h->n_tid, h->n_reads, (const long long *)c->r_tid_off.p, (const uint32_t *)c->r_pos.p,
                            (const uint32_t *)c->r_end.p, (const uint32_t *)c->r_ncig.p, (const unsigned long long *)c->r_off.p,
-                           (const uint32_t *)c->r_cigar.p, 1};
+                           (const uint32_t *)c->r_cigar.p, 1, nullptr, nullptr};
     c->h2d_bytes += sizeof(long long) * (size_t)(h->n_tid + 1) + 20 * nr + 4 * nw;
     c->n_words = h->n_words;
     return finish_reads(c);

@@ -37,6 +37,7 @@ struct Ctx {
     LaunchReads reads{};
     std::vector<int64_t> h_tid_off;
     DevBuf r_tid_off, r_pos, r_end, r_ncig, r_off, r_cigar;
+    DevBuf pos_tiles, pos_tile_off;       // position tiles of the resident reads (svtk_capi.cpp finish_reads)
 
     // signature index over the resident reads (svtk_index.cu): rebuilt by the first refine after a load
     long long n_words = 0;
@@ -83,7 +84,12 @@ struct Ctx {
     // reads SEQ from them); reference names / lengths of the BAM header for the host front end
     DevBuf bam_comp, bam_infl, bam_blocks, bam_splits, bam_seg, bam_rec, bam_ctl;
     PinBuf bam_h;
-    cudaEvent_t bam_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t bam_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // the loader's pipeline: pinned ring the file is read into, side streams the inflate launches run on, the pinned block table
+    PinBuf bam_stage[3], bam_tab;
+    cudaEvent_t bam_stage_ev[3] = {nullptr, nullptr, nullptr}, bam_side_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t bam_chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t bam_side[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<std::string> bam_ref_names;
     std::vector<uint32_t> bam_ref_lens;
     unsigned long long bam_infl_bytes = 0;

@@ -31,7 +31,10 @@ struct DevReads {
     const unsigned long long *cigar_off;
     const uint32_t *cigar;       // 16-byte aligned, readable up to the next 16-byte boundary past the last word
     uint32_t max_span;           // max over reads of end - pos
+    const uint32_t *tiles;       // position tiles (svtk_index.cu k_pos_tiles): first read with pos >= tile start, per reference; nullptr: none
+    const long long *tile_off;   // [n_tid + 1] first tile of each reference
 };
+constexpr int POS_TILE_SHIFT = 12;          // 4 096-base tiles: ~8 reads per tile at 30x / 15 kb
 
 struct DevWindows {
     int n_win;

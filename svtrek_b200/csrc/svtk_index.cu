@@ -75,7 +75,7 @@ static DevIndex to_dev(const LaunchIndex &x) {
 static DevReads to_dev(const LaunchReads &r) {
     DevReads d;
     d.n_tid = r.n_tid; d.n_reads = r.n_reads; d.tid_off = r.tid_off; d.pos = r.pos; d.end = r.end; d.n_cigar = r.n_cigar;
-    d.cigar_off = r.cigar_off; d.cigar = r.cigar; d.max_span = r.max_span;
+    d.cigar_off = r.cigar_off; d.cigar = r.cigar; d.max_span = r.max_span; d.tiles = r.tiles; d.tile_off = r.tile_off;
     return d;
 }
 static DevWindows to_dev(const LaunchWindows &w) {
@@ -797,6 +797,35 @@ __device__ __forceinline__ void warp_lower_bound_pos2(const uint32_t *__restrict
     resA = A.res; resB = B.res;
 }
 
+// The same two lower bounds through the position tiles (k_pos_tiles): the tile of each key gives the first read at or right of
+// the tile's boundary, a warp-wide probe of the next 32 positions finishes the job (a 4 096-base tile holds ~8 reads at 30x).
+// Two dependent memory round trips instead of the 32-ary search's four.
+__device__ __forceinline__ void warp_lower_bound_tiles2(const DevReads &R, int tid, long long t0, long long t1, long long keyA, long long keyB,
+                                                        long long &resA, long long &resB) {
+    const int lane = lane_id();
+    const long long tb = R.tile_off[tid], nt = R.tile_off[tid + 1] - tb;
+    long long a = -1, b = -1;                                   // probe starts (-1: resolved without probing)
+    resA = keyA <= 0 ? t0 : t1; resB = keyB <= 0 ? t0 : t1;
+    if (keyA > 0 && keyA <= 0xffffffffll && (keyA >> POS_TILE_SHIFT) < nt) a = tb + (keyA >> POS_TILE_SHIFT);
+    if (keyB > 0 && keyB <= 0xffffffffll && (keyB >> POS_TILE_SHIFT) < nt) b = tb + (keyB >> POS_TILE_SHIFT);
+    const uint32_t sa = a >= 0 ? __ldg(R.tiles + a) : 0u, sb = b >= 0 ? __ldg(R.tiles + b) : 0u;
+    long long ia = sa, ib = sb;
+    bool needA = a >= 0, needB = b >= 0;
+    while (needA || needB) {
+        const long long pa = ia + lane, pb = ib + lane;
+        const uint32_t va = (needA && pa < t1) ? __ldg(R.pos + pa) : 0xffffffffu;
+        const uint32_t vb = (needB && pb < t1) ? __ldg(R.pos + pb) : 0xffffffffu;
+        if (needA) {
+            const unsigned m = __ballot_sync(FULL, pa >= t1 || (long long)va >= keyA);
+            if (m) { resA = min(ia + (__ffs(m) - 1), t1); needA = false; } else ia += 32;
+        }
+        if (needB) {
+            const unsigned m = __ballot_sync(FULL, pb >= t1 || (long long)vb >= keyB);
+            if (m) { resB = min(ib + (__ffs(m) - 1), t1); needB = false; } else ib += 32;
+        }
+    }
+}
+
 // cursor right after the op that first pushes it past w_end (refinement.c:141-144); the caller knows it exists
 __device__ __forceinline__ uint32_t warp_stop_cursor(const uint32_t *__restrict__ cigar, unsigned long long off, uint32_t n,
                                                      uint32_t rpos, uint32_t w_end) {
@@ -921,7 +950,8 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
     long long lo = 0, hi = 0;
     if (tid >= 0 && tid < R.n_tid && endq >= begq && kind != KIND_POINT) {
         // yielded reads have pos < endq (hts.c:3913) and pos + span > beg; span <= max_span bounds the look-back
-        warp_lower_bound_pos2(R.pos, R.tid_off[tid], R.tid_off[tid + 1], endq, begq - (long long)R.max_span + 1, hi, lo);
+        if (R.tiles) warp_lower_bound_tiles2(R, tid, R.tid_off[tid], R.tid_off[tid + 1], endq, begq - (long long)R.max_span + 1, hi, lo);
+        else warp_lower_bound_pos2(R.pos, R.tid_off[tid], R.tid_off[tid + 1], endq, begq - (long long)R.max_span + 1, hi, lo);
         if (lo > hi) lo = hi;
     }
     if (lane == 0) range_out[w] = make_int2((int)lo, (int)hi);
@@ -930,7 +960,28 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
         return;
     }
     const unsigned below = (1u << lane) - 1u;
-    int n = 0, nd = 0;                                           // signatures, deferred leading-clip reads (uniform)
+    // consensus_pos only ever looks at signatures within `range` of pos (plus `interval` for the cluster behind an anchor), at
+    // the array's two ends and at its size (refinement.c:43,56-98).  With the values further away replaced by their nearest
+    // representative on either side -- the largest one below pos - reach, the smallest one above pos + reach -- every loop of
+    // consensus_pos visits the same elements and stops at the same place, so only the near ones are kept and sorted (a window
+    // drags in every D/I of every read that overlaps it, SURVEY Q7: ~65 signatures at config 2, ~20 of them near pos).
+    // Off when pos +- reach could wrap in the reference's int arithmetic: then everything is kept, as before.
+    const int pos = (int)W.pos[w];
+    const long long reach = (long long)t.range + (long long)t.interval + 1ll;
+    const bool filt = t.range >= 0 && t.interval >= 0 && reach < (1ll << 30) && pos >= 0 && (long long)pos <= 0x7fffffffll - reach - 1ll;
+    const long long keep_lo = filt ? (long long)pos - reach : -(1ll << 40), keep_hi = filt ? (long long)pos + reach : (1ll << 40);
+    int far_lo = (int)0x80000000, far_hi = 0x7fffffff;           // per lane: largest value below keep_lo, smallest above keep_hi
+    int n = 0, nk = 0, nd = 0;                                   // all signatures, the kept ones, deferred leading-clip reads (uniform)
+    unsigned any_lo = 0, any_hi = 0;
+    auto take = [&](bool emit, int val) {                        // called by all lanes together
+        const bool lo_side = emit && (long long)val < keep_lo, hi_side = emit && (long long)val > keep_hi;
+        const unsigned m = __ballot_sync(FULL, emit), mk = __ballot_sync(FULL, emit && !lo_side && !hi_side);
+        if (emit && !lo_side && !hi_side) { const int slot = nk + __popc(mk & below); if (slot < RW_CAP) s.sig[slot] = val; }
+        if (lo_side) far_lo = max(far_lo, val);
+        if (hi_side) far_hi = min(far_hi, val);
+        any_lo |= __ballot_sync(FULL, lo_side); any_hi |= __ballot_sync(FULL, hi_side);
+        n += __popc(m); nk += __popc(mk);
+    };
     unsigned long long n_scan = 0, n_seg = 0;
     const long long c0 = lo / IDX_READS, c1 = (hi - 1) / IDX_READS;
     for (long long cb = c0; cb <= c1; cb += 32) {
@@ -952,9 +1003,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
             int code = 0, val = 0;
             if (e < total)
                 code = event_for_window(__ldg(X.events + (size_t)jbase + (e - (jincl - jcnt))), kind, w_start, w_end, beg, lo, hi, X.rend, val);
-            const unsigned m = __ballot_sync(FULL, code == 1);
-            if (code == 1) { const int slot = n + __popc(m & below); if (slot < RW_CAP) s.sig[slot] = val; }
-            n += __popc(m);
+            take(code == 1, val);
             const unsigned md = __ballot_sync(FULL, code == 2);
             if (md) {
                 if (code == 2) { const int slot = nd + __popc(md & below); if (slot < RW_DEFER) s.defer[slot] = val; }
@@ -973,9 +1022,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
                 for (uint32_t e0 = 0; e0 < seg.y; e0 += 32) {
                     int code = 0, val = 0;
                     if (e0 + lane < seg.y) code = event_for_window(__ldg(X.events + (size_t)seg.x + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);
-                    const unsigned m = __ballot_sync(FULL, code == 1);
-                    if (code == 1) { const int slot = n + __popc(m & below); if (slot < RW_CAP) s.sig[slot] = val; }
-                    n += __popc(m);
+                    take(code == 1, val);
                     const unsigned md = __ballot_sync(FULL, code == 2);
                     if (md) {
                         if (code == 2) { const int slot = nd + __popc(md & below); if (slot < RW_DEFER) s.defer[slot] = val; }
@@ -993,8 +1040,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
             for (int k = 0; k < nd; ++k) {
                 const long long ri = s.defer[k];
                 const uint32_t sr = warp_stop_cursor(R.cigar, __ldg(R.cigar_off + ri), __ldg(R.n_cigar + ri), __ldg(R.pos + ri), w_end);
-                if (lane == 0 && n < RW_CAP) s.sig[n] = (int)(sr + 1u);
-                ++n;
+                take(lane == 0, (int)(sr + 1u));
             }
         } else {
             for (long long ri = lo; ri < hi; ++ri) {             // more than the defer list holds: rescan the read range (rare)
@@ -1003,8 +1049,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
                 const unsigned long long off = __ldg(R.cigar_off + ri);
                 if ((__ldg(R.cigar + off) & 15u) != (uint32_t)OP_SOFT || __ldg(X.rend + ri) <= w_end) continue;
                 const uint32_t sr = warp_stop_cursor(R.cigar, off, nc, rp, w_end);
-                if (lane == 0 && n < RW_CAP) s.sig[n] = (int)(sr + 1u);
-                ++n;
+                take(lane == 0, (int)(sr + 1u));
             }
         }
         __syncwarp();
@@ -1013,11 +1058,13 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
         atomicAdd(&ic->events_scanned, n_scan); atomicAdd(&ic->segments, n_seg);
         atomicAdd(&ic->pairs_range, (unsigned long long)(hi - lo)); atomicAdd(&ic->signatures, (unsigned long long)n);
     }
-    if (n < t.min_count || n <= 0) {                             // refinement.c:43
+    if (n < t.min_count || n <= 0) {                             // refinement.c:43: the size test counts every signature
         if (lane == 0) result[w] = -1;
         return;
     }
-    if (n > RW_CAP) {
+    // the far values' representatives join the kept ones: [largest below] kept... [smallest above]
+    const int nf = nk + (any_lo ? 1 : 0) + (any_hi ? 1 : 0);
+    if (nf > RW_CAP) {
         if (lane == 0) {
             const int slot = atomicAdd(ov.count, 1);
             if (slot < ov.capacity) ov.items[slot] = make_int2(w, n);
@@ -1026,16 +1073,18 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
         }
         return;
     }
-    if (n <= 32) warp_sort_segment<1>(s.sig, n);
-    else if (n <= 64) warp_sort_segment<2>(s.sig, n);
-    else if (n <= 128) warp_sort_segment<4>(s.sig, n);
-    else warp_sort_segment<8>(s.sig, n);
-    const int pos = (int)W.pos[w];
+    if (any_lo) { const int v = __reduce_max_sync(FULL, far_lo); if (lane == 0) s.sig[nk] = v; }
+    if (any_hi) { const int v = __reduce_min_sync(FULL, far_hi); if (lane == 0) s.sig[nk + (any_lo ? 1 : 0)] = v; }
+    __syncwarp();
+    if (nf <= 32) warp_sort_segment<1>(s.sig, nf);
+    else if (nf <= 64) warp_sort_segment<2>(s.sig, nf);
+    else if (nf <= 128) warp_sort_segment<4>(s.sig, nf);
+    else warp_sort_segment<8>(s.sig, nf);
     int res;
-    const ScanResult L = consensus_scan_warp(s.sig, n, pos, t, true);
+    const ScanResult L = consensus_scan_warp(s.sig, nf, pos, t, true);
     if (L.early) res = L.value;
     else {
-        const ScanResult Rr = consensus_scan_warp(s.sig, n, pos, t, false);
+        const ScanResult Rr = consensus_scan_warp(s.sig, nf, pos, t, false);
         res = Rr.early ? Rr.value : (L.dist < Rr.dist ? L.best : Rr.best);
     }
     if (lane == 0) result[w] = res;
@@ -1133,13 +1182,45 @@ __global__ void __launch_bounds__(NT) k_refine_block(DevReads R, DevWindows W, D
     }
 }
 
-// svtk_reads contract check: CIGARs packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1])
-__global__ void k_check_layout(const unsigned long long *__restrict__ off, const uint32_t *__restrict__ n, long long n_reads,
-                               unsigned long long n_words, unsigned int *flag) {
-    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n_reads; r += (long long)gridDim.x * blockDim.x) {
-        const unsigned long long next = (r + 1 < n_reads) ? off[r + 1] : n_words;
-        if (off[r] + n[r] != next || (r == 0 && off[0] != 0ull)) atomicOr(flag, 1u);
+// svtk_reads contract check: CIGARs packed back to back in read order (cigar_off[r] + n_cigar[r] == cigar_off[r+1]) -> bit 0;
+// reads sorted by pos inside every reference -> bit 1; end >= pos -> bit 2
+__global__ void k_check_layout(DevReads R, unsigned long long n_words, unsigned int *flag) {
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < R.n_reads; r += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long next = (r + 1 < R.n_reads) ? R.cigar_off[r + 1] : n_words;
+        unsigned bad = 0;
+        if (R.cigar_off[r] + R.n_cigar[r] != next || (r == 0 && R.cigar_off[0] != 0ull)) bad |= 1u;
+        if (R.end[r] < R.pos[r]) bad |= 4u;
+        if (r > 0 && R.pos[r] < R.pos[r - 1]) {               // allowed only across a reference boundary
+            int lo = 0, hi = R.n_tid;                          // first t with tid_off[t] > r - 1
+            while (lo < hi) { const int m = (lo + hi) >> 1; if (R.tid_off[m] > r - 1) hi = m; else lo = m + 1; }
+            if (lo >= R.n_tid + 1 || R.tid_off[lo] != r) bad |= 2u;
+        }
+        if (bad) atomicOr(flag, bad);
     }
+}
+
+// position of the last read of every reference (0xffffffff: the reference has no reads)
+__global__ void k_last_pos(DevReads R, uint32_t *__restrict__ out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= R.n_tid) return;
+    const long long a = R.tid_off[t], z = R.tid_off[t + 1];
+    out[t] = z > a ? R.pos[z - 1] : 0xffffffffu;
+}
+
+// position tiles: tiles[tile_off[t] + k] = first read of reference t with pos >= k << POS_TILE_SHIFT (reference end if none);
+// one thread per read writes the tiles whose boundary falls in (pos[r-1], pos[r]], the reference's last read also the tail
+__global__ void k_pos_tiles(DevReads R, uint32_t *__restrict__ tiles, const long long *__restrict__ tile_off) {
+    const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= R.n_reads) return;
+    int lo = 0, hi = R.n_tid;                                  // reference of read r: last t with tid_off[t] <= r
+    while (lo < hi) { const int m = (lo + hi) >> 1; if (R.tid_off[m + 1] > r) hi = m; else lo = m + 1; }
+    const int t = lo;
+    const long long t0 = R.tid_off[t], t1 = R.tid_off[t + 1], tb = tile_off[t], nt = tile_off[t + 1] - tb;
+    // tiles k with (k << SHIFT) in (pos[r-1], pos[r]]: k from floor(pos[r-1] / T) + 1 (a boundary AT pos[r-1] belongs to read r-1 or earlier)
+    const long long first = (r == t0) ? 0 : (long long)(R.pos[r - 1] >> POS_TILE_SHIFT) + 1;
+    const long long mine = (long long)(R.pos[r] >> POS_TILE_SHIFT);
+    for (long long k = first; k <= mine && k < nt; ++k) tiles[tb + k] = (uint32_t)r;
+    if (r + 1 == t1) for (long long k = mine + 1; k < nt; ++k) tiles[tb + k] = (uint32_t)t1;
 }
 
 // =========================================================================================================
@@ -1157,7 +1238,21 @@ cudaError_t launch_check_layout(const LaunchReads &r, unsigned long long n_words
     if (r.n_reads <= 0) return cudaSuccess;
     const long long want = (r.n_reads + 255) / 256;
     const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
-    k_check_layout<<<blocks, 256, 0, s>>>(r.cigar_off, r.n_cigar, r.n_reads, n_words, flag);
+    k_check_layout<<<blocks, 256, 0, s>>>(to_dev(r), n_words, flag);
+    return cudaGetLastError();
+}
+
+int pos_tile_shift() { return POS_TILE_SHIFT; }
+
+cudaError_t launch_last_pos(const LaunchReads &r, uint32_t *out, cudaStream_t s) {
+    if (r.n_tid <= 0) return cudaSuccess;
+    k_last_pos<<<(r.n_tid + 127) / 128, 128, 0, s>>>(to_dev(r), out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pos_tiles(const LaunchReads &r, uint32_t *tiles, const long long *tile_off, cudaStream_t s) {
+    if (r.n_reads <= 0) return cudaSuccess;
+    k_pos_tiles<<<(unsigned)((r.n_reads + 255) / 256), 256, 0, s>>>(to_dev(r), tiles, tile_off);
     return cudaGetLastError();
 }
 

@@ -269,7 +269,7 @@ constexpr int BIG_NT = 1024;
 static DevReads to_dev(const LaunchReads &r) {
     DevReads d;
     d.n_tid = r.n_tid; d.n_reads = r.n_reads; d.tid_off = r.tid_off; d.pos = r.pos; d.end = r.end; d.n_cigar = r.n_cigar;
-    d.cigar_off = r.cigar_off; d.cigar = r.cigar; d.max_span = r.max_span;
+    d.cigar_off = r.cigar_off; d.cigar = r.cigar; d.max_span = r.max_span; d.tiles = r.tiles; d.tile_off = r.tile_off;
     return d;
 }
 static DevWindows to_dev(const LaunchWindows &w) {

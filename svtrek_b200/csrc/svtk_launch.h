@@ -23,6 +23,8 @@ struct LaunchReads {            // device pointers
     const unsigned long long *cigar_off;
     const uint32_t *cigar;
     uint32_t max_span;
+    const uint32_t *tiles;          // position tiles built by launch_pos_tiles (nullptr: the kernels fall back to a search over pos)
+    const long long *tile_off;
 };
 
 struct LaunchWindows {          // device pointers
@@ -59,6 +61,9 @@ cudaError_t launch_refine_block(const LaunchReads &r, const LaunchWindows &w, co
                                 int interval, int min_count, int32_t *result, int *ov_count, int2 *ov_items, int ov_capacity, int n_items,
                                 int *arena, unsigned long long arena_ints, unsigned long long *arena_top, int *fail_flag, cudaStream_t s);
 cudaError_t launch_check_layout(const LaunchReads &r, unsigned long long n_words, unsigned int *flag, cudaStream_t s);
+int pos_tile_shift();
+cudaError_t launch_last_pos(const LaunchReads &r, uint32_t *out, cudaStream_t s);      // out[t] = pos of reference t's last read (0xffffffff: none)
+cudaError_t launch_pos_tiles(const LaunchReads &r, uint32_t *tiles, const long long *tile_off, cudaStream_t s);
 
 int big_segment_ints();
 int consensus_segment_smem_ints();

@@ -56,8 +56,9 @@ constexpr unsigned FULLMASK = 0xffffffffu;
 #define SVTK_BZ_MINB 16           // resident single-warp CTAs per SM the register allocation must allow
 #endif
 __global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_t *__restrict__ words, const BgzfBlock *__restrict__ blk, unsigned first_block,
-                                                     unsigned n_blocks, uint8_t *__restrict__ out, unsigned int *__restrict__ ctl, unsigned int *__restrict__ next,
-                                                     int lanes) {
+                                                     unsigned end_block, uint8_t *__restrict__ out, unsigned long long *__restrict__ tok,
+                                                     unsigned long long tok_sub, uint32_t *__restrict__ n_tok, unsigned int *__restrict__ ctl,
+                                                     unsigned int *__restrict__ next, int lanes) {
     extern __shared__ uint32_t bz_sm[];
     // length / distance bases (svtk_bgzf_core.cuh): one copy per CTA, behind the lanes' Huffman tables
     uint32_t *lut = bz_sm + lanes * BZ_TABLE_WORDS;
@@ -69,17 +70,20 @@ __global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_
     T.lit = reinterpret_cast<uint16_t *>(bz_sm + (threadIdx.x < (unsigned)lanes ? threadIdx.x : 0u) * BZ_TABLE_WORDS);
     T.dist = T.lit + (1 << BZ_LBITS);
     BzLane z;
-    z.state = BZ_S_IDLE; z.err = BZ_OK; z.pend_len = 0; z.pend_dist = 0;
+    z.state = BZ_S_IDLE; z.err = BZ_OK; z.n_tok = 0; z.tok = nullptr;
     unsigned cur = 0xffffffffu;
     bool drained = threadIdx.x >= (unsigned)lanes;
     for (;;) {
         if (z.state == BZ_S_IDLE && !drained) {
-            if (cur != 0xffffffffu && z.err) { if (atomicCAS(&ctl[BAM_CTL_ZERR], 0u, cur + 1u) == 0u) ctl[BAM_CTL_ZCODE] = (unsigned)z.err; }
+            if (cur != 0xffffffffu) {
+                n_tok[cur] = z.err ? 0u : z.n_tok;              // a failed block has nothing to resolve
+                if (z.err) { if (atomicCAS(&ctl[BAM_CTL_ZERR], 0u, cur + 1u) == 0u) ctl[BAM_CTL_ZCODE] = (unsigned)z.err; }
+            }
             cur = first_block + atomicAdd(next, 1u);
-            if (cur < n_blocks) {
+            if (cur < end_block) {
                 const BgzfBlock b = blk[cur];
-                bz_begin(z, words, b.in_beg, b.in_beg + b.in_len, out + b.out_off, b.isize);
-            } else { drained = true; z.err = BZ_OK; }
+                bz_begin(z, words, b.in_beg, b.in_beg + b.in_len, out + b.out_off, b.isize, tok + (bz_tok_offset(b.out_off, cur) - tok_sub));
+            } else { drained = true; z.err = BZ_OK; cur = 0xffffffffu; }
         }
         if (__all_sync(FULLMASK, drained)) break;
         // every lane passes here once per round: block switches (header + table build) on the lanes that need one, then a
@@ -89,6 +93,40 @@ __global__ void __launch_bounds__(32, SVTK_BZ_MINB) k_bgzf_inflate(const uint32_
         for (int it = 0; it < BZ_BURST; ++it)
             if (z.state == BZ_S_SYMBOLS) bz_step(z, T, L);
         bz_check_input(z);
+    }
+}
+
+// Second phase: the matches of every block, in stream order, one WARP per block, 32 tokens at a time.  A match may be copied
+// once every byte of its source is final: always true for the lowest pending match of the batch (everything before its
+// destination is final), and for any other whose source ends below that match's write position (the "frontier").  Each round
+// every ready lane copies one chunk of BZ_CHUNK bytes; the lowest pending lane always progresses, so the loop ends.
+__global__ void __launch_bounds__(256) k_bgzf_resolve(const BgzfBlock *__restrict__ blk, unsigned first_block, unsigned end_block, uint8_t *__restrict__ out,
+                                                      const unsigned long long *__restrict__ tok, unsigned long long tok_sub, const uint32_t *__restrict__ n_tok) {
+    const unsigned lane = threadIdx.x & 31u, warps = gridDim.x * (blockDim.x >> 5);
+    for (unsigned b = first_block + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < end_block; b += warps) {
+        const uint32_t n = n_tok[b];
+        if (n == 0u) continue;
+        const unsigned long long ob = blk[b].out_off;
+        uint8_t *base = out + ob;
+        const unsigned long long *tq = tok + (bz_tok_offset(ob, b) - tok_sub);
+        for (uint32_t k0 = 0; k0 < n; k0 += 32u) {
+            const bool have = k0 + lane < n;
+            const unsigned long long t = have ? tq[k0 + lane] : 0ull;
+            uint32_t wr = bz_tok_pos(t), left = have ? bz_tok_len(t) : 0u, dist = bz_tok_dist(t);    // wr: next byte this lane writes
+            const uint32_t src_end = wr - dist + left;                                               // one past the last source byte
+            unsigned pm = __ballot_sync(FULLMASK, left != 0u);
+            while (pm) {
+                const int low = __ffs(pm) - 1;
+                const uint32_t frontier = __shfl_sync(FULLMASK, wr, low);
+                if (left != 0u && ((int)lane == low || src_end <= frontier)) {
+                    const uint32_t c = left < BZ_CHUNK ? left : BZ_CHUNK;
+                    bz_copy_chunk(base + wr, &dist, c);
+                    wr += c; left -= c;
+                }
+                __syncwarp();                                      // this round's stores are visible to the next round's loads
+                pm = __ballot_sync(FULLMASK, left != 0u);
+            }
+        }
     }
 }
 
@@ -365,7 +403,8 @@ int read_header(const uint8_t *f, size_t n, bool whole_file, std::vector<std::st
             const size_t at = hd.size();
             hd.resize(at + b.isize);
             uint8_t dummy = 0;
-            const int rc = bz_inflate(words.data(), 0, b.in_len, b.isize ? hd.data() + at : &dummy, b.isize, T);
+            std::vector<unsigned long long> tok((size_t)b.isize / 3 + 2);
+            const int rc = bz_inflate(words.data(), 0, b.in_len, b.isize ? hd.data() + at : &dummy, b.isize, T, tok.data());
             if (rc) return fail(SVTK_ERR_IO, "bam: BGZF block %zu does not inflate (code %d)", nb - 1, rc);
         }
         return 0;
@@ -625,29 +664,48 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     int lanes = 1;
     while (lanes < 32 && (est_blocks + lanes - 1) / lanes > want_warps) lanes <<= 1;
     if (const char *e = getenv("SVTK_BZ_LANES")) if (*e) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) lanes = v; }
-    bool pipelined = true;
-    if (const char *e = getenv("SVTK_BAM_PIPE")) if (*e == '0') pipelined = false;
+    // Inflate launches per uploaded chunk (SVTK_BAM_PIPE=1) measured SLOWER than one launch after the upload on B200: a launch
+    // lasts as long as its slowest block (8 - 35 ms, whatever its size), so 57 chunk launches on 4 streams took 450 ms against
+    // 71 ms for the one launch (profiles/r02a_bam_sweep.jsonl).  Default: one launch.
+    const bool pipelined = false;
 
-    std::vector<uint64_t> coff;                            // file offset of every loaded block (sorted)
+    std::vector<uint64_t> coff, cend;                      // file offset of every loaded block (sorted), and of its end
     std::vector<BgzfBlock> tab_overflow;                   // descriptors beyond the pinned table's first guess
     BgzfBlock *tab = (BgzfBlock *)c->bam_tab.p;            // pinned: descriptors are DMA'd from here
     size_t n_blk = 0, launched = 0, shipped_tab = 0;
+    auto tab_at = [&](size_t i) -> const BgzfBlock & { return tab[i]; };
     unsigned long long total = 0;
     int n_launch = 0;
     bool first_launch = true;
+    // both phases for blocks [b0, b1): in waves of <= ~3 GB of inflated bytes, so that the match-token buffer (8 bytes per 3
+    // inflated bytes at worst) stays bounded whatever the file size
     auto launch_inflate = [&](size_t b0, size_t b1, cudaStream_t st) -> int {
-        if (b1 <= b0) return 0;
-        if (n_launch >= MAX_LAUNCH) return fail(SVTK_ERR_STATE, "bam: too many inflate launches");
-        const size_t nb = b1 - b0;
-        const int smem = (lanes * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4;
-        int per_sm = 1;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (nb + lanes - 1) / lanes);
-        k_bgzf_inflate<<<grid, 32, smem, st>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)b0, (unsigned)b1,
-                                               (uint8_t *)c->bam_infl.p, ctl, ctl + 64 + n_launch, lanes);
-        CU(cudaGetLastError());
-        ++n_launch;
-        c->launches += 1;
+        if (int rc = c->bam_ntok.reserve(4 * std::max<size_t>(std::max(n_blk, blk_cap), 1))) return rc;
+        const unsigned long long WAVE = 3ull << 30;
+        while (b0 < b1) {
+            if (n_launch >= MAX_LAUNCH) return fail(SVTK_ERR_STATE, "bam: too many inflate launches");
+            size_t be = b0 + 1;
+            while (be < b1 && tab_at(be).out_off + tab_at(be).isize - tab_at(b0).out_off <= WAVE) ++be;
+            const size_t nb = be - b0;
+            const unsigned long long wave_bytes = tab_at(be - 1).out_off + tab_at(be - 1).isize - tab_at(b0).out_off;
+            const unsigned long long tok_sub = bz_tok_offset(tab_at(b0).out_off, b0);
+            if (int rc = c->bam_tok.reserve(8 * (size_t)(bz_tok_capacity(wave_bytes, nb) + 4))) return rc;
+            const int smem = (lanes * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4;
+            int per_sm = 1;
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
+            const unsigned grid = (unsigned)std::min<size_t>((size_t)sms * std::max(per_sm, 1), (nb + lanes - 1) / lanes);
+            k_bgzf_inflate<<<grid, 32, smem, st>>>((const uint32_t *)c->bam_comp.p, (const BgzfBlock *)c->bam_blocks.p, (unsigned)b0, (unsigned)be,
+                                                   (uint8_t *)c->bam_infl.p, (unsigned long long *)c->bam_tok.p, tok_sub, (uint32_t *)c->bam_ntok.p, ctl,
+                                                   ctl + 64 + n_launch, lanes);
+            CU(cudaGetLastError());
+            const unsigned rgrid = (unsigned)std::min<size_t>((size_t)sms * 8, (nb + 7) / 8);
+            k_bgzf_resolve<<<rgrid, 256, 0, st>>>((const BgzfBlock *)c->bam_blocks.p, (unsigned)b0, (unsigned)be, (uint8_t *)c->bam_infl.p,
+                                                  (const unsigned long long *)c->bam_tok.p, tok_sub, (const uint32_t *)c->bam_ntok.p);
+            CU(cudaGetLastError());
+            ++n_launch;
+            c->launches += 2;
+            b0 = be;
+        }
         return 0;
     };
 
@@ -712,7 +770,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
                 BgzfBlock b;
                 b.in_beg = span_img0 + (scan_off - spans[si].fb) + 12 + xlen; b.in_len = bsize - xlen - 20; b.isize = isize; b.out_off = total;
                 if (fits) tab[n_blk] = b; else tab_overflow.push_back(b);
-                coff.push_back(scan_off);
+                coff.push_back(scan_off); cend.push_back(scan_off + bsize);
                 ++n_blk;
                 total += isize;
                 scan_off += bsize;
@@ -769,7 +827,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
         CU(cudaEventRecord(c->bam_side_ev[i], c->bam_side[i]));
         CU(cudaStreamWaitEvent(c->stream, c->bam_side_ev[i], 0));
     }
-    CU(cudaMemsetAsync((char *)c->bam_infl.p + (total & ~3ull), 0, 64 - (total & 3), c->stream));
+    CU(cudaMemsetAsync((char *)c->bam_infl.p + total, 0, 64, c->stream));     // the record kernels read whole words: zeros behind the last byte
     CU(cudaEventRecord(c->bam_ev[3], c->stream));           // end of the inflate
     if (stats) stats->lanes_per_warp = (uint32_t)lanes;
     const uint32_t *infl = (const uint32_t *)c->bam_infl.p;
@@ -786,9 +844,8 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
         auto it = std::lower_bound(coff.begin(), coff.end(), co);
         if (it == coff.end() || *it != co) {
             // just past the last loaded block of a span: the end of the previous block
-            if (uo == 0 && it != coff.begin()) {
-                const size_t j = (size_t)(it - coff.begin()) - 1;
-                const BgzfBlock &pb = tab[j];
+            if (uo == 0 && it != coff.begin() && cend[(size_t)(it - coff.begin()) - 1] == co) {
+                const BgzfBlock &pb = tab[(size_t)(it - coff.begin()) - 1];
                 *lin = pb.out_off + pb.isize;
                 return 0;
             }

@@ -150,14 +150,16 @@ struct BzLane {
     BzBits b;
     uint8_t *out;
     uint32_t op, out_len;                 // bytes produced so far / expected (ISIZE)
-    uint32_t pend_len, pend_dist;         // rest of a match still to copy (bz_step copies BZ_CHUNK bytes per call)
+    unsigned long long *tok;              // match tokens of this block (bz_step queues, bz_resolve_* copies): pos | len << 16 | (dist - 1) << 25
+    uint32_t n_tok;
     int state, last, err;
 };
 
-BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len) {
+BZ_HD void bz_begin(BzLane &z, const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len,
+                     unsigned long long *tok) {
     z.b.w = words; z.b.end = in_end;
     bz_prime(z.b, in_beg);
-    z.out = out; z.op = 0; z.out_len = out_len; z.pend_len = 0; z.pend_dist = 0; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
+    z.out = out; z.op = 0; z.out_len = out_len; z.tok = tok; z.n_tok = 0; z.state = BZ_S_HEADER; z.last = 0; z.err = BZ_OK;
 }
 
 BZ_HD void bz_fail(BzLane &z, int e) { z.err = e; z.state = BZ_S_IDLE; }
@@ -247,23 +249,33 @@ struct BzLut { const uint32_t *w; };      // nullptr: compute (host)
 BZ_HD uint32_t bz_len_lookup(const BzLut &L, int k) { return L.w ? L.w[k] : bz_len_entry(k); }
 BZ_HD uint32_t bz_dist_lookup(const BzLut &L, int d) { return L.w ? L.w[32 + d] : bz_dist_entry(d); }
 
-// ---- LZ77 copy, BZ_CHUNK bytes per call.  The window is the block's own output in global memory.  A match is copied in chunks so
-// that every lane of a warp runs the SAME short code whatever its match length (a long match just takes more rounds): the warp
-// pays for the union of its lanes' paths, and loops with lane-dependent trip counts were most of that union.
-// dist >= BZ_CHUNK: the source lies wholly behind the chunk.  dist < BZ_CHUNK (a run): the first chunk replicates the period from
-// a register; after it the distance is raised to the smallest multiple of the period >= BZ_CHUNK (same bytes: the data is
-// periodic), so later chunks are plain copies again.
+// ---- LZ77 in two phases.  A lane that copied its matches as it met them waited a DRAM round trip per match (the window of
+// every block in flight does not fit L2: 27 % of the kernel's stall samples sat on the first use of the source bytes, B200,
+// profiles/r02b) and dragged its warp through copy loops of lane-dependent length.  So the decoding lane only QUEUES a match --
+// destination offset, length, distance: one 8-byte token -- and skips the bytes; literals are stored directly.  A second pass
+// (k_bgzf_resolve: one WARP per block, 32 matches in flight at a time, full occupancy) fills the holes in stream order.
+// A block of n inflated bytes holds at most n / 3 matches.
+BZ_HD unsigned long long bz_token(uint32_t pos, uint32_t len, uint32_t dist) {
+    return (unsigned long long)pos | (unsigned long long)len << 16 | (unsigned long long)(dist - 1u) << 25;
+}
+BZ_HD uint32_t bz_tok_pos(unsigned long long t) { return (uint32_t)(t & 0xffffull); }
+BZ_HD uint32_t bz_tok_len(unsigned long long t) { return (uint32_t)(t >> 16) & 511u; }
+BZ_HD uint32_t bz_tok_dist(unsigned long long t) { return ((uint32_t)(t >> 25) & 0xffffu) + 1u; }
+BZ_HD unsigned long long bz_tok_capacity(unsigned long long inflated_bytes, unsigned long long n_blocks) { return inflated_bytes / 3ull + n_blocks; }
+BZ_HD unsigned long long bz_tok_offset(unsigned long long out_off, unsigned long long block_index) { return out_off / 3ull + block_index; }
+
+// up to BZ_CHUNK bytes of one match: o[0 .. n) = o[-dist ..], n <= BZ_CHUNK.  dist >= BZ_CHUNK: the source lies wholly behind the
+// chunk.  dist < BZ_CHUNK (a run): the period is replicated from a register; *dist is then raised to the smallest multiple of
+// the period >= BZ_CHUNK (same bytes: the data is periodic), so the match's later chunks are plain copies again.
 constexpr uint32_t BZ_CHUNK = 8;
-BZ_HD void bz_copy_chunk(BzLane &z) {
-    uint8_t *o = z.out + z.op;
-    const uint32_t n = z.pend_len < BZ_CHUNK ? z.pend_len : BZ_CHUNK;
-    uint32_t dist = z.pend_dist;
+BZ_HD void bz_copy_chunk(uint8_t *o, uint32_t *dist_io, uint32_t n) {
+    const uint32_t dist = *dist_io;
     unsigned long long v;                 // the chunk's bytes, first byte in the low bits
 #if defined(__CUDA_ARCH__)
     {   // three aligned words cover the 8 source bytes wherever they start (bytes past the source are ignored; the buffers are
         // readable 16 bytes past their end)
         const uintptr_t a = (uintptr_t)(o - dist);
-        const uint32_t *aw = (const uint32_t *)(a & ~(uintptr_t)3);
+        const volatile uint32_t *aw = (const volatile uint32_t *)(a & ~(uintptr_t)3);
         const uint32_t sh = (uint32_t)(a & 3) * 8u, w0 = aw[0], w1 = aw[1], w2 = aw[2];
         v = (unsigned long long)__funnelshift_r(w0, w1, sh) | (unsigned long long)__funnelshift_r(w1, w2, sh) << 32;
     }
@@ -272,18 +284,25 @@ BZ_HD void bz_copy_chunk(BzLane &z) {
     for (uint32_t i = 0; i < BZ_CHUNK && i < dist; ++i) v |= (unsigned long long)o[(long long)i - (long long)dist] << (8u * i);
 #endif
     if (dist < BZ_CHUNK) {                // run: bytes [0, dist) of v are the period; replicate it over the chunk
-        const unsigned long long per = v & ((1ull << (8u * dist)) - 1ull);
-        v = per;
+        v &= (1ull << (8u * dist)) - 1ull;
         uint32_t have = dist;
         while (have < BZ_CHUNK) { v |= v << (8u * have); have <<= 1; }      // doubling keeps the phase: have stays a multiple of dist
-        // later chunks: plain copies from the smallest multiple of the period >= BZ_CHUNK back (1..7 -> 8 8 9 8 10 12 14)
-        z.pend_dist = (uint32_t)(0x0E0C0A0809080800ull >> (8u * dist)) & 255u;
+        *dist_io = (uint32_t)(0x0E0C0A0809080800ull >> (8u * dist)) & 255u;  // 1..7 -> 8 8 9 8 10 12 14
     }
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (uint32_t i = 0; i < BZ_CHUNK; ++i) if (i < n) o[i] = (uint8_t)(v >> (8u * i));
-    z.op += n; z.pend_len -= n;
+}
+
+// the whole second phase for one block, by one thread (host driver, CPU tests)
+BZ_HD void bz_resolve_serial(uint8_t *out, const unsigned long long *tok, uint32_t n_tok) {
+    for (uint32_t k = 0; k < n_tok; ++k) {
+        const unsigned long long t = tok[k];
+        uint32_t dist = bz_tok_dist(t), left = bz_tok_len(t);
+        uint8_t *o = out + bz_tok_pos(t);
+        while (left) { const uint32_t n = left < BZ_CHUNK ? left : BZ_CHUNK; bz_copy_chunk(o, &dist, n); o += n; left -= n; }
+    }
 }
 
 // A corrupt stream can keep decoding "symbols" out of whatever follows its payload; the bound is checked once per burst of
@@ -294,57 +313,56 @@ BZ_HD void bz_check_input(BzLane &z) {
     if (z.state != BZ_S_IDLE && bz_ip(z.b) > z.b.end + 8) bz_fail(z, BZ_ERR_IN);
 }
 
-// One round of a lane in state BZ_S_SYMBOLS: the next chunk of a pending match, or up to two literal/length symbols (the second
-// only after a literal: a refill leaves >= 32 bits, a literal takes <= 15) and, for a match, its distance and first chunk.
+// One round of a lane in state BZ_S_SYMBOLS: up to two literal/length symbols (the second only after a literal: a refill leaves
+// >= 32 bits, a literal takes <= 15); literals are stored, a match is range-checked and queued.
 BZ_HD void bz_step(BzLane &z, const BzTables &T, const BzLut &L) {
     BzBits &b = z.b;
-    if (z.pend_len == 0u) {
-        bz_refill(b);
-        int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
+    bz_refill(b);
+    int s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
+    if (s < 256 && s >= 0) {
+        if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
+        z.out[z.op++] = (uint8_t)s;
+        s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
         if (s < 256 && s >= 0) {
             if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
             z.out[z.op++] = (uint8_t)s;
-            s = bz_symbol(b, T.lit, BZ_LBITS, T.lcnt, T.lsym, T.lresume);
-            if (s < 256 && s >= 0) {
-                if (z.op >= z.out_len) return bz_fail(z, BZ_ERR_OUT);
-                z.out[z.op++] = (uint8_t)s;
-                return;
-            }
-        }
-        if (s < 0) return bz_fail(z, BZ_ERR_CODE);
-        if (s == 256) {
-            if (z.last) bz_finish(z); else z.state = BZ_S_HEADER;
             return;
         }
-        if (s > 285) return bz_fail(z, BZ_ERR_CODE);
-        bz_refill(b);
-        const uint32_t le = bz_len_lookup(L, s - 257);
-        const uint32_t len = (le & 0xffffu) + bz_take(b, (int)(le >> 16));
-        const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
-        if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
-        bz_refill(b);
-        const uint32_t de = bz_dist_lookup(L, d);
-        const uint32_t dist = (de & 0xffffu) + bz_take(b, (int)(de >> 16));
-        if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
-        if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
-        z.pend_len = len; z.pend_dist = dist;
     }
-    bz_copy_chunk(z);
+    if (s < 0) return bz_fail(z, BZ_ERR_CODE);
+    if (s == 256) {
+        if (z.last) bz_finish(z); else z.state = BZ_S_HEADER;
+        return;
+    }
+    if (s > 285) return bz_fail(z, BZ_ERR_CODE);
+    bz_refill(b);
+    const uint32_t le = bz_len_lookup(L, s - 257);
+    const uint32_t len = (le & 0xffffu) + bz_take(b, (int)(le >> 16));
+    const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
+    if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
+    bz_refill(b);
+    const uint32_t de = bz_dist_lookup(L, d);
+    const uint32_t dist = (de & 0xffffu) + bz_take(b, (int)(de >> 16));
+    if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
+    if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);
+    z.tok[z.n_tok++] = bz_token(z.op, len, dist);            // n_tok <= out_len / 3: every match is >= 3 bytes and fits the block
+    z.op += len;
 }
 
 // Inflate one raw DEFLATE stream (the payload of one BGZF block): words/in_beg/in_end locate it inside the compressed
 // buffer, out/out_len is the block's slice of the inflated buffer (out_len == the block's ISIZE footer).  Returns BZ_OK
 // when the final block ended with exactly out_len bytes written.  (Single-lane driver; the kernel has its own.)
 BZ_HD int bz_inflate(const uint32_t *words, unsigned long long in_beg, unsigned long long in_end, uint8_t *out, uint32_t out_len,
-                     BzTables &T) {
+                     BzTables &T, unsigned long long *tok) {          // tok: room for out_len / 3 + 1 tokens
     BzLane z;
-    bz_begin(z, words, in_beg, in_end, out, out_len);
+    bz_begin(z, words, in_beg, in_end, out, out_len, tok);
     const BzLut L{nullptr};
     while (z.state != BZ_S_IDLE) {
         if (z.state == BZ_S_HEADER) bz_header(z, T);
         else bz_step(z, T, L);
         bz_check_input(z);
     }
+    if (z.err == BZ_OK) bz_resolve_serial(out, tok, z.n_tok);
     return z.err;
 }
 

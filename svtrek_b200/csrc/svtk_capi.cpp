@@ -425,7 +425,7 @@ void svtk_destroy(svtk_ctx *ctx) {
     for (DevBuf *b : {&c->r_tid_off, &c->r_pos, &c->r_end, &c->r_ncig, &c->r_off, &c->r_cigar, &c->range, &c->ov_items,
                       &c->arena, &c->counters, &c->scratch4, &c->idx_events, &c->idx_chunks, &c->idx_segs, &c->idx_rend, &c->idx_ctrl, &c->pos_tiles, &c->pos_tile_off, &c->win_blob, &c->result, &c->tmp_a, &c->tmp_b, &c->tmp_c,
                       &c->poa_in, &c->poa_out, &c->poa_scratch, &c->poa_ctl, &c->bam_comp, &c->bam_infl, &c->bam_blocks,
-                      &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl})
+                      &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl, &c->bam_tok, &c->bam_ntok})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h, &c->h_audit}) b->release();
     for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);

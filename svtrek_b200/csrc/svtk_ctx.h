@@ -87,6 +87,7 @@ struct Ctx {
     cudaEvent_t bam_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // the loader's pipeline: pinned ring the file is read into, side streams the inflate launches run on, the pinned block table
     PinBuf bam_stage[3], bam_tab;
+    DevBuf bam_tok, bam_ntok;             // match tokens between the two inflate phases, and their count per block
     cudaEvent_t bam_stage_ev[3] = {nullptr, nullptr, nullptr}, bam_side_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t bam_chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaStream_t bam_side[4] = {nullptr, nullptr, nullptr, nullptr};

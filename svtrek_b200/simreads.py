@@ -388,7 +388,7 @@ def windows_from_truth(truth: SVTruth, seed=1, *, pos_noise=40, wider=20000, med
     pos = (truth.pos0 + noise).astype(np.int64)
     end = np.where(truth.is_del, truth.pos0 + truth.length + noise_e, pos + 1).astype(np.int64)
     chrom = truth.tid.astype(np.int64) + 1
-    is_del = truth.is_del & (end - pos > 50)
+    is_del = truth.is_del & (((end - pos) & 0xFFFFFFFF) > 50)      # uint32 arithmetic like audit.c:168,190: a noisy END < POS still prints
     nwin = np.where(truth.is_del, np.where(is_del, 2, 0), 1)
     first = np.cumsum(nwin) - nwin
     tot = int(nwin.sum())
@@ -568,10 +568,14 @@ def _packer():
     return L
 
 
-def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_err=0.02, threads=None, level=6, chunk_reads=8192):
+def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_err=0.02, threads=None, level=6, chunk_reads=8192,
+                   header_contigs=None, tid_shift=0, want_meta=False):
     """A BAM + BAI of the read set like write_bam's (same record fields, HTSlib's BGZF cutting rule, same index layout), fast
     enough for the full configs: ~15 s for config 2 on 16 cores, most of it zlib level 6.  Read names are fixed width (r%09d);
     SEQ / QUAL are uniform random, carriers of a planted insertion hold a mutated copy of its sequence (`truth`).
+    header_contigs / tid_shift: the file is one PART of a larger job -- its header lists all of header_contigs, its records carry
+    reference id tid + tid_shift -- so that parts written by different processes can be concatenated block-wise into one BAM
+    (assemble_bam_parts).  want_meta: return what that needs instead of the size.
     Falls back to write_bam when tools/libbgzfpack.so has not been built.  Returns the file size."""
     import struct
     import os as _os
@@ -582,7 +586,9 @@ def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_
     n = rs.n_reads
     BLOCK = 0xff00
     NAME = 11                                                  # "r%09d\0"
-    tid = np.ascontiguousarray(np.repeat(np.arange(rs.n_tid, dtype=np.int32), np.diff(rs.tid_off)))
+    tid = np.ascontiguousarray(np.repeat(np.arange(rs.n_tid, dtype=np.int32), np.diff(rs.tid_off)) + np.int32(tid_shift))
+    hdr_contigs = list(header_contigs) if header_contigs is not None else list(rs.contig_len)
+    n_ref_all = len(hdr_contigs)
     cig_off = np.ascontiguousarray(rs.cigar_off.astype(np.int64))
     ncig = rs.n_cigar.astype(np.int64)
     if ncig.size and int(ncig.max()) > 65535:
@@ -608,9 +614,9 @@ def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_
         np.cumsum(big, out=bcs[1:])
         has_big_ins = (bcs[cig_off[1:]] - bcs[cig_off[:-1]]) > 0
 
-    text = "@HD\tVN:1.6\tSO:coordinate\n" + "".join(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L_}\n" for t, L_ in enumerate(rs.contig_len))
-    hdr = b"BAM\1" + struct.pack("<i", len(text)) + text.encode() + struct.pack("<i", rs.n_tid)
-    for t, L_ in enumerate(rs.contig_len):
+    text = "@HD\tVN:1.6\tSO:coordinate\n" + "".join(f"@SQ\tSN:{chr_prefix}{t + 1}\tLN:{L_}\n" for t, L_ in enumerate(hdr_contigs))
+    hdr = b"BAM\1" + struct.pack("<i", len(text)) + text.encode() + struct.pack("<i", n_ref_all)
+    for t, L_ in enumerate(hdr_contigs):
         nm = f"{chr_prefix}{t + 1}".encode() + b"\0"
         hdr += struct.pack("<i", len(nm)) + nm + struct.pack("<i", int(L_))
 
@@ -680,7 +686,7 @@ def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_
             # planted insertions: carriers hold a mutated copy of the insertion's own sequence
             for r in np.flatnonzero(has_big_ins[c0:c1]).tolist():
                 rr = c0 + r
-                t = int(tid[rr])
+                t = int(tid[rr]) - int(tid_shift)
                 if t not in templates:
                     continue
                 w = rs.cigar[int(cig_off[rr]):int(cig_off[rr + 1])]
@@ -726,40 +732,80 @@ def write_bam_fast(path, rs: ReadSet, seed=7, chr_prefix="chr", truth=None, ins_
     # ---- index (SAMv1 5.2)
     v0 = (coff[blk_start] << 16) | in_start
     v1 = (coff[blk_end] << 16) | in_end
+    sections = {}
+    for t in range(rs.n_tid):
+        a, z = int(rs.tid_off[t]), int(rs.tid_off[t + 1])
+        sections[t + int(tid_shift)] = bai_section(bins[a:z], v0[a:z], v1[a:z], rs.pos[a:z], rs.end[a:z])
     with open(path + ".bai", "wb") as f:
-        f.write(b"BAI\1" + struct.pack("<i", rs.n_tid))
-        for t in range(rs.n_tid):
-            a, z = int(rs.tid_off[t]), int(rs.tid_off[t + 1])
-            if z == a:
-                f.write(struct.pack("<i", 0) + struct.pack("<i", 0))
-                continue
-            bt, s0, s1 = bins[a:z], v0[a:z], v1[a:z]
-            order = np.argsort(bt, kind="stable")
-            bo, so0, so1 = bt[order], s0[order], s1[order]
-            brk = np.ones(z - a, dtype=bool)
-            brk[1:] = (bo[1:] != bo[:-1]) | (so0[1:] != so1[:-1])
-            cs = np.flatnonzero(brk)
-            ce = np.concatenate([cs[1:], [z - a]]) - 1
-            ch_bin, ch_v0, ch_v1 = bo[cs], so0[cs], so1[ce]
-            ub, first = np.unique(ch_bin, return_index=True)
-            cnt = np.diff(np.concatenate([first, [ch_bin.shape[0]]]))
-            out = [struct.pack("<i", ub.shape[0])]
-            for bb, fi, cn in zip(ub.tolist(), first.tolist(), cnt.tolist()):
-                out.append(struct.pack("<Ii", bb, cn))
-                pair = np.empty(2 * cn, dtype="<u8")
-                pair[0::2] = ch_v0[fi:fi + cn]; pair[1::2] = ch_v1[fi:fi + cn]
-                out.append(pair.tobytes())
-            p = rs.pos[a:z].astype(np.int64); e_ = rs.end[a:z].astype(np.int64)
-            wlo, whi = p >> 14, ((e_ - 1) >> 14) + 1
-            n_intv = int(whi.max())
-            lin = np.full(n_intv, np.iinfo(np.int64).max, dtype=np.int64)
-            own, widx = _expand_ranges(wlo, whi)
-            np.minimum.at(lin, widx, s0[own])
-            empty = lin == np.iinfo(np.int64).max
-            last_filled = np.where(empty, -1, np.arange(n_intv))          # empty windows repeat the previous offset, like HTSlib
-            np.maximum.accumulate(last_filled, out=last_filled)
-            lin = np.where(last_filled < 0, 0, lin[np.maximum(last_filled, 0)])
-            out.append(struct.pack("<i", n_intv))
-            out.append(lin.astype("<u8").tobytes())
-            f.write(b"".join(out))
+        f.write(b"BAI\1" + struct.pack("<i", n_ref_all))
+        for t in range(n_ref_all):
+            f.write(sections.get(t, struct.pack("<ii", 0, 0)))
+    if want_meta:
+        return dict(size=size, hdr_bytes=int(coff[hdr_blocks]), v0=v0, v1=v1, bins=bins, n_ref_all=n_ref_all)
     return size
+
+
+def bai_section(bins, v0, v1, pos, end, shift=0):
+    """One reference's part of a .bai (SAMv1 5.2): bins with their chunk lists, then the 16 kb linear index.  bins / v0 / v1 / pos /
+    end: per record, in file order.  shift: added to the compressed-offset half of every virtual offset (a part that moved)."""
+    import struct
+    n = int(bins.shape[0])
+    if n == 0:
+        return struct.pack("<ii", 0, 0)
+    s0 = v0 + (int(shift) << 16)
+    s1 = v1 + (int(shift) << 16)
+    order = np.argsort(bins, kind="stable")
+    bo, so0, so1 = bins[order], s0[order], s1[order]
+    brk = np.ones(n, dtype=bool)
+    brk[1:] = (bo[1:] != bo[:-1]) | (so0[1:] != so1[:-1])
+    cs = np.flatnonzero(brk)
+    ce = np.concatenate([cs[1:], [n]]) - 1
+    ch_bin, ch_v0, ch_v1 = bo[cs], so0[cs], so1[ce]
+    ub, first = np.unique(ch_bin, return_index=True)
+    cnt = np.diff(np.concatenate([first, [ch_bin.shape[0]]]))
+    out = [struct.pack("<i", ub.shape[0])]
+    for bb, fi, cn in zip(ub.tolist(), first.tolist(), cnt.tolist()):
+        out.append(struct.pack("<Ii", bb, cn))
+        pair = np.empty(2 * cn, dtype="<u8")
+        pair[0::2] = ch_v0[fi:fi + cn]; pair[1::2] = ch_v1[fi:fi + cn]
+        out.append(pair.tobytes())
+    p = np.asarray(pos).astype(np.int64); e_ = np.asarray(end).astype(np.int64)
+    wlo, whi = p >> 14, ((e_ - 1) >> 14) + 1
+    n_intv = int(whi.max())
+    lin = np.full(n_intv, np.iinfo(np.int64).max, dtype=np.int64)
+    own, widx = _expand_ranges(wlo, whi)
+    np.minimum.at(lin, widx, s0[own])
+    empty = lin == np.iinfo(np.int64).max
+    last_filled = np.where(empty, -1, np.arange(n_intv))          # empty windows repeat the previous offset, like HTSlib
+    np.maximum.accumulate(last_filled, out=last_filled)
+    lin = np.where(last_filled < 0, 0, lin[np.maximum(last_filled, 0)])
+    out.append(struct.pack("<i", n_intv))
+    out.append(lin.astype("<u8").tobytes())
+    return b"".join(out)
+
+
+def assemble_bam_parts(out_path, part_paths, hdr_bytes, sizes):
+    """One BAM out of parts written with the same header (write_bam_fast(..., header_contigs=, tid_shift=)): the header blocks of
+    part 0, every part's record blocks, one EOF block.  BGZF blocks are independent, so this is a byte-level concatenation.
+    Returns [offset of part k's record blocks in the new file minus their offset in the part] -- the shift of its virtual offsets."""
+    import os as _os
+    shifts, at = [], hdr_bytes
+    with open(out_path, "wb") as f:
+        with open(part_paths[0], "rb") as p0:
+            f.write(p0.read(hdr_bytes))
+        for pth, sz in zip(part_paths, sizes):
+            n = sz - hdr_bytes - 28                          # the part minus its header blocks and its EOF block
+            shifts.append(at - hdr_bytes)
+            with open(pth, "rb") as src:
+                src.seek(hdr_bytes)
+                left = n
+                while left > 0:
+                    buf = src.read(min(left, 64 << 20))
+                    if not buf:
+                        raise IOError("short part file " + pth)
+                    f.write(buf); left -= len(buf)
+            at += n
+        with open(part_paths[0], "rb") as p0:
+            p0.seek(sizes[0] - 28)
+            f.write(p0.read(28))
+    return shifts

@@ -9,7 +9,8 @@ extern "C" int hostsim_inflate(const uint8_t *comp, long long n, long long in_be
     static uint16_t lit[1 << svtk::BZ_LBITS], dist[1 << svtk::BZ_DBITS];
     svtk::BzTables T;
     T.lit = lit; T.dist = dist;
-    return svtk::bz_inflate(w.data(), (unsigned long long)in_beg, (unsigned long long)in_end, out, out_len, T);
+    std::vector<unsigned long long> tok((size_t)out_len / 3 + 2);
+    return svtk::bz_inflate(w.data(), (unsigned long long)in_beg, (unsigned long long)in_end, out, out_len, T, tok.data());
 }
 
 // CRC-32 of data[0..n) computed the way the kernel does: `slices` slice CRCs merged with the x^(8n) identity

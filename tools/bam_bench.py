@@ -38,7 +38,7 @@ def main():
         checked = False
         settings = [dict(SVTK_BZ_LANES=str(l)) for l in args.lanes.split(",")]
         if not args.no_unpiped:
-            settings += [dict(SVTK_BZ_LANES="0", SVTK_BAM_PIPE="0"), dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="4"), dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="16")]
+            settings += [dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="4"), dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="16")]
         for env in settings:
             for k in ("SVTK_BZ_LANES", "SVTK_BAM_PIPE", "SVTK_BAM_THREADS"):
                 os.environ.pop(k, None)

@@ -260,3 +260,34 @@ def ref_poa_steps(seqs):
     ln = abpoa().ref_poa_steps(n, off.ctypes.data, b.ctypes.data, bs.ctypes.data, nn.ctypes.data, no.ctypes.data, hh.ctypes.data,
                                cc.ctypes.data, cons.ctypes.data, cap, cov.ctypes.data, -1, None, 0)
     return dict(cons=cons[:ln].copy(), cov=cov[:ln].copy(), best_score=bs, node_n=nn, n_ops=no, ops_hash=hh, cells=cc)
+
+
+# ---- inserted sequences through the reference's HTSlib (oracle/ins_harness.c -> oracle/_ref/libins_ref.so)
+def have_ins_ref():
+    return os.path.exists(os.path.join(REF_DIR, "libins_ref.so"))
+
+
+def ref_ins_sequences(bam_path, chrom, start, end, kind, refined, tol=5, min_len=50):
+    """Per INS window with a refined position: the bases of every `I >= min_len` op refine_ins' loop meets within tol of it, read
+    with sam_itr_queryi / sam_itr_next / bam_seqi of the reference's HTSlib.  Returns dict(window, read_pos, ref_pos, seq_off, bases)."""
+    L = C.CDLL(os.path.join(REF_DIR, "libins_ref.so"))
+    L.ref_ins_sequences.argtypes = [C.c_char_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [C.POINTER(C.c_int64)] * 2
+    chrom = np.ascontiguousarray(chrom, dtype=np.int32)
+    start = np.ascontiguousarray(np.asarray(start).astype(np.int64) & 0xFFFFFFFF, dtype=np.uint32)
+    end = np.ascontiguousarray(np.asarray(end).astype(np.int64) & 0xFFFFFFFF, dtype=np.uint32)
+    kind = np.ascontiguousarray(kind, dtype=np.uint8)
+    refined = np.ascontiguousarray(refined, dtype=np.int32)
+    cap_s, cap_b = 1 << 12, 1 << 20
+    while True:
+        win = np.zeros(cap_s, np.int32); rp = np.zeros(cap_s, np.uint32); xp = np.zeros(cap_s, np.uint32)
+        off = np.zeros(cap_s + 1, np.int64); bases = np.zeros(cap_b, np.uint8)
+        ns, nb = C.c_int64(0), C.c_int64(0)
+        rc = L.ref_ins_sequences(os.fsencode(bam_path), int(len(chrom)), chrom.ctypes.data, start.ctypes.data, end.ctypes.data, kind.ctypes.data,
+                                 refined.ctypes.data, int(tol), int(min_len), cap_s, cap_b, win.ctypes.data, rp.ctypes.data, xp.ctypes.data,
+                                 off.ctypes.data, bases.ctypes.data, C.byref(ns), C.byref(nb))
+        if rc == -2:
+            raise IOError("ref_ins_sequences: cannot open " + str(bam_path))
+        if rc == 0:
+            n = int(ns.value)
+            return dict(window=win[:n].copy(), read_pos=rp[:n].copy(), ref_pos=xp[:n].copy(), seq_off=off[:n + 1].copy(), bases=bases[:int(nb.value)].copy())
+        cap_s, cap_b = max(cap_s, int(ns.value) + 1), max(cap_b, int(nb.value) + 1)

@@ -656,18 +656,30 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     static unsigned long long attr_seen = 0;
     if (first_use_on_device(attr_seen)) CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (32 * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4));
 
-    // lanes per warp of the inflate launches (see k_bgzf_inflate): thin warps finish a block sooner, wide warps fit more blocks
-    // on the machine.  The whole load should fit ~18 resident single-warp CTAs per SM (the kernel's register budget).
+    // lanes per warp of an inflate launch (see k_bgzf_inflate): thin warps finish a block sooner, wide warps fit more blocks on
+    // the machine.  A launch should fit ~18 resident single-warp CTAs per SM (the kernel's register budget).
     long long want_warps = (long long)sms * 18;
     if (const char *e = getenv("SVTK_BZ_WARPS")) if (*e) want_warps = std::max(1ll, atoll(e));
-    const long long est_blocks = (long long)(image_bytes / 40000) + 1;
-    int lanes = 1;
-    while (lanes < 32 && (est_blocks + lanes - 1) / lanes > want_warps) lanes <<= 1;
-    if (const char *e = getenv("SVTK_BZ_LANES")) if (*e) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) lanes = v; }
-    // Inflate launches per uploaded chunk (SVTK_BAM_PIPE=1) measured SLOWER than one launch after the upload on B200: a launch
-    // lasts as long as its slowest block (8 - 35 ms, whatever its size), so 57 chunk launches on 4 streams took 450 ms against
-    // 71 ms for the one launch (profiles/r02a_bam_sweep.jsonl).  Default: one launch.
-    const bool pipelined = false;
+    int forced_lanes = 0;
+    if (const char *e = getenv("SVTK_BZ_LANES")) if (*e) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) forced_lanes = v; }
+    auto lanes_for = [&](size_t blocks) {
+        int l = 1;
+        while (l < 32 && (long long)((blocks + l - 1) / l) > want_warps) l <<= 1;
+        return forced_lanes ? forced_lanes : l;
+    };
+    int lanes = lanes_for(image_bytes / 40000 + 1);
+    // Upload and inflate overlap in a FEW big pieces: a launch lasts as long as its slowest block (10 - 30 ms whatever its size:
+    // 57 launches of 32 MB each took 450 ms against 71 ms for one launch of everything, profiles/r02a_bam_sweep.jsonl), so a
+    // piece must upload for about as long as it inflates.  Files below 256 MB: one launch after the upload.
+    size_t pipe_bytes = std::max<size_t>(128u << 20, image_bytes / 4 + 1);
+    if (const char *e = getenv("SVTK_BAM_PIPE_MB")) if (*e) pipe_bytes = (size_t)std::max(1ll, atoll(e)) << 20;
+    bool pipelined = image_bytes >= (256u << 20);
+    if (const char *e = getenv("SVTK_BAM_PIPE")) if (*e) pipelined = (*e == '1');
+    if (pipelined) {      // concurrent launches need their own token slices: room for the whole load, by the capacity guesses
+        if (int rc = c->bam_tok.reserve(8 * (size_t)(bz_tok_capacity(infl_cap, blk_cap) + 4))) return rc;
+        if (int rc = c->bam_ntok.reserve(4 * std::max<size_t>(blk_cap, 1))) return rc;
+    }
+    size_t last_launch_off = 0;
 
     std::vector<uint64_t> coff, cend;                      // file offset of every loaded block (sorted), and of its end
     std::vector<BgzfBlock> tab_overflow;                   // descriptors beyond the pinned table's first guess
@@ -679,17 +691,19 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     bool first_launch = true;
     // both phases for blocks [b0, b1): in waves of <= ~3 GB of inflated bytes, so that the match-token buffer (8 bytes per 3
     // inflated bytes at worst) stays bounded whatever the file size
-    auto launch_inflate = [&](size_t b0, size_t b1, cudaStream_t st) -> int {
-        if (int rc = c->bam_ntok.reserve(4 * std::max<size_t>(std::max(n_blk, blk_cap), 1))) return rc;
-        const unsigned long long WAVE = 3ull << 30;
+    auto launch_inflate = [&](size_t b0, size_t b1, cudaStream_t st, bool whole_buffer) -> int {
+        if (!whole_buffer) if (int rc = c->bam_ntok.reserve(4 * std::max<size_t>(std::max(n_blk, blk_cap), 1))) return rc;
+        const unsigned long long WAVE = whole_buffer ? ~0ull : (3ull << 30);
         while (b0 < b1) {
             if (n_launch >= MAX_LAUNCH) return fail(SVTK_ERR_STATE, "bam: too many inflate launches");
             size_t be = b0 + 1;
             while (be < b1 && tab_at(be).out_off + tab_at(be).isize - tab_at(b0).out_off <= WAVE) ++be;
             const size_t nb = be - b0;
             const unsigned long long wave_bytes = tab_at(be - 1).out_off + tab_at(be - 1).isize - tab_at(b0).out_off;
-            const unsigned long long tok_sub = bz_tok_offset(tab_at(b0).out_off, b0);
-            if (int rc = c->bam_tok.reserve(8 * (size_t)(bz_tok_capacity(wave_bytes, nb) + 4))) return rc;
+            // whole_buffer: the token buffer was sized for the whole load up front (launches run side by side, each in its own slice)
+            const unsigned long long tok_sub = whole_buffer ? 0ull : bz_tok_offset(tab_at(b0).out_off, b0);
+            if (!whole_buffer) if (int rc = c->bam_tok.reserve(8 * (size_t)(bz_tok_capacity(wave_bytes, nb) + 4))) return rc;
+            lanes = lanes_for(nb);
             const int smem = (lanes * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4;
             int per_sm = 1;
             CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_bgzf_inflate, 32, smem));
@@ -782,7 +796,8 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
             img_off += n;
             done += n;
             // ---- ship the new descriptors, launch their inflate behind this chunk's bytes
-            if (fits && pipelined && n_blk > launched) {
+            if (fits && pipelined && n_blk > launched && (img_off - last_launch_off >= pipe_bytes || img_off == image_bytes)) {
+                last_launch_off = img_off;
                 CU(cudaMemcpyAsync((BgzfBlock *)c->bam_blocks.p + shipped_tab, tab + shipped_tab, sizeof(BgzfBlock) * (n_blk - shipped_tab), cudaMemcpyHostToDevice, c->stream));
                 shipped_tab = n_blk;
                 cudaEvent_t ev = c->bam_chunk_ev[k % NCHEV];
@@ -790,7 +805,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
                 cudaStream_t side = c->bam_side[k % NSIDE];
                 CU(cudaStreamWaitEvent(side, ev, 0));
                 if (first_launch) { CU(cudaEventRecord(c->bam_ev[1], side)); first_launch = false; }
-                if (int rc = launch_inflate(launched, n_blk, side)) return rc;
+                if (int rc = launch_inflate(launched, n_blk, side, true)) return rc;
                 launched = n_blk;
             }
             ++k;
@@ -822,7 +837,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
         shipped_tab = n_blk;
     }
     if (first_launch) { CU(cudaEventRecord(c->bam_ev[1], c->stream)); first_launch = false; }
-    if (n_blk > launched) { if (int rc = launch_inflate(launched, n_blk, c->stream)) return rc; launched = n_blk; }
+    if (n_blk > launched) { if (int rc = launch_inflate(launched, n_blk, c->stream, pipelined && fits)) return rc; launched = n_blk; }
     for (int i = 0; i < NSIDE; ++i) {                       // join the side streams
         CU(cudaEventRecord(c->bam_side_ev[i], c->bam_side[i]));
         CU(cudaStreamWaitEvent(c->stream, c->bam_side_ev[i], 0));

@@ -38,9 +38,11 @@ def main():
         checked = False
         settings = [dict(SVTK_BZ_LANES=str(l)) for l in args.lanes.split(",")]
         if not args.no_unpiped:
-            settings += [dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="4"), dict(SVTK_BZ_LANES="0", SVTK_BAM_THREADS="16")]
+            settings += [dict(SVTK_BAM_PIPE="0"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="128"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256"),
+                         dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="640"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256", SVTK_BZ_LANES="8"),
+                         dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256", SVTK_BAM_THREADS="16")]
         for env in settings:
-            for k in ("SVTK_BZ_LANES", "SVTK_BAM_PIPE", "SVTK_BAM_THREADS"):
+            for k in ("SVTK_BZ_LANES", "SVTK_BAM_PIPE", "SVTK_BAM_THREADS", "SVTK_BAM_PIPE_MB"):
                 os.environ.pop(k, None)
             for k, v in env.items():
                 if v != "0" or k != "SVTK_BZ_LANES":

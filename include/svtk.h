@@ -265,9 +265,21 @@ int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, 
  * range order are the lines svtk_process_vcf writes for the whole file.  flags: SVTK_VCF_NO_INFO_LINES leaves out the two
  * [INFO] lines (the merger writes them once); SVTK_VCF_OWNS_UNPLACED makes this shard the one that reports lines no shard
  * can place (malformed lines, references outside the dictionary) -- give it to exactly one shard. */
-enum { SVTK_VCF_NO_INFO_LINES = 1, SVTK_VCF_OWNS_UNPLACED = 2 };
+enum { SVTK_VCF_NO_INFO_LINES = 1, SVTK_VCF_OWNS_UNPLACED = 2, SVTK_VCF_TEE_STDOUT = 4 /* lines go to out_path AND stdout */,
+       SVTK_VCF_QUIET = 8 /* do not repeat the reference's stderr messages */ };
 int svtk_process_vcf_region(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int32_t tid_lo, int32_t tid_hi, uint32_t flags,
                             int64_t *n_records);
+/* svtk_process_vcf with flags (SVTK_VCF_TEE_STDOUT: the reference accepts -o and never writes it; the C driver treats
+ * it as an additional sink) and the optional consensus side file of svtk_process_vcf_ins (fasta_path NULL: none). */
+int svtk_process_vcf_flags(svtk_ctx *ctx, const char *vcf_path, const char *out_path, const char *fasta_path, int32_t tol, uint32_t flags,
+                           int64_t *n_records, int64_t *n_consensus);
+/* One region shard of a whole job, file to file (multi-GPU runs; replaces the worker fan-out of audit.c:269-293): the VCF's records
+ * are cut into n_shards contiguous runs (VCF order == genomic order, cuts may fall inside a reference) of equal estimated work --
+ * the compressed BAM bytes under each record's windows, read off the .bai's linear index -- and this call handles run `shard`:
+ * it loads only what those windows can see (svtk_load_bam_windows), refines them and writes their lines to out_path.  Every
+ * shard computes the same cuts; the outputs concatenated in shard order are svtk_process_vcf's output.  One ctx (GPU) per shard. */
+int svtk_audit_shard(svtk_ctx *ctx, const char *bam_path, const char *bai_path, const char *vcf_path, const char *out_path, int32_t shard,
+                     int32_t n_shards, uint32_t flags, int64_t *n_records, svtk_bam_stats *stats);
 /* The front and back ends of process_vcf alone -- no ctx, no GPU: the windows process_vcf builds for a VCF (audit.c:65-193,
  * in file order; call with cap 0 for the count), and the lines it writes for given per-window results (audit.c:182-229).
  * n_ref: size of the BAM's reference dictionary (0: unknown), only used to place records of a sharded call.  tid_lo < 0: the

@@ -82,7 +82,7 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format", "svtk_load_bam_windows"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format", "svtk_load_bam_windows", "svtk_process_vcf_flags", "svtk_audit_shard"]
 
 _lib = None
 
@@ -125,6 +125,8 @@ def load_library():
     L.svtk_load_bam.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(BamStats)]
     L.svtk_load_bam_refs.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(BamStats)]
     L.svtk_load_bam_windows.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(Windows), C.POINTER(BamStats)]
+    L.svtk_audit_shard.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.c_uint32, C.POINTER(C.c_int64), C.POINTER(BamStats)]
+    L.svtk_process_vcf_flags.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_uint32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.svtk_bam_n_ref.argtypes = [C.c_void_p]
     L.svtk_bam_ref.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint32)]
     L.svtk_process_vcf_ins.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -459,6 +461,13 @@ class Auditor:
         flags = (0 if info_lines else 1) | (2 if owns_unplaced else 0)
         _check(self.lib.svtk_process_vcf_region(self.ctx, vcf_path.encode(), out_path.encode() if out_path else None, int(tid_lo), int(tid_hi), flags, C.byref(n)))
         return n.value
+
+    def audit_shard(self, bam_path, vcf_path, out_path, shard, n_shards, info_lines=False, bai_path=None):
+        """svtk_audit_shard: region shard `shard` of n_shards of the whole job, file to file; returns (records, loader stats)."""
+        n, st = C.c_int64(0), BamStats()
+        _check(self.lib.svtk_audit_shard(self.ctx, os.fsencode(bam_path), os.fsencode(bai_path) if bai_path else None, os.fsencode(vcf_path),
+                                         os.fsencode(out_path), int(shard), int(n_shards), 0 if info_lines else 1, C.byref(n), C.byref(st)))
+        return n.value, {k: getattr(st, k) for k, _ in BamStats._fields_}
 
     def process_vcf(self, vcf_path, out_path):
         n = C.c_int64(0)

@@ -37,7 +37,7 @@ def build_cli() -> str:
     """gcc: the driver links libsvtk_b200.so next to it (rpath $ORIGIN)."""
     if os.path.exists(CLI) and os.path.getmtime(CLI) >= max(os.path.getmtime(CLI_SRC), os.path.getmtime(os.path.join(HERE, "libsvtk_b200.so"))):
         return CLI
-    cmd = ["gcc", "-O2", "-std=c99", "-D_GNU_SOURCE", "-Wall", "-o", CLI, CLI_SRC, "-L" + HERE, "-lsvtk_b200", "-Wl,-rpath,$ORIGIN"]
+    cmd = ["gcc", "-O2", "-std=c99", "-D_GNU_SOURCE", "-Wall", "-pthread", "-o", CLI, CLI_SRC, "-L" + HERE, "-lsvtk_b200", "-Wl,-rpath,$ORIGIN"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("gcc failed:\n" + r.stdout + r.stderr)

@@ -22,7 +22,9 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <memory>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -657,8 +659,8 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     if (first_use_on_device(attr_seen)) CU(cudaFuncSetAttribute(k_bgzf_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (32 * BZ_TABLE_WORDS + BZ_LUT_WORDS) * 4));
 
     // lanes per warp of an inflate launch (see k_bgzf_inflate): thin warps finish a block sooner, wide warps fit more blocks on
-    // the machine.  A launch should fit ~18 resident single-warp CTAs per SM (the kernel's register budget).
-    long long want_warps = (long long)sms * 18;
+    // the machine.  A launch should fit the 20 resident single-warp CTAs per SM the kernel's 96 registers allow.
+    long long want_warps = (long long)sms * 20;
     if (const char *e = getenv("SVTK_BZ_WARPS")) if (*e) want_warps = std::max(1ll, atoll(e));
     int forced_lanes = 0;
     if (const char *e = getenv("SVTK_BZ_LANES")) if (*e) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) forced_lanes = v; }
@@ -670,10 +672,10 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     int lanes = lanes_for(image_bytes / 40000 + 1);
     // Upload and inflate overlap in a FEW big pieces: a launch lasts as long as its slowest block (10 - 30 ms whatever its size:
     // 57 launches of 32 MB each took 450 ms against 71 ms for one launch of everything, profiles/r02a_bam_sweep.jsonl), so a
-    // piece must upload for about as long as it inflates.  Files below 256 MB: one launch after the upload.
-    size_t pipe_bytes = std::max<size_t>(128u << 20, image_bytes / 4 + 1);
+    // piece must upload for about as long as it inflates.  Files below 768 MB: one launch after the upload.
+    size_t pipe_bytes = std::max<size_t>(384u << 20, image_bytes / 3 + 1);     // B200, 1.9 GB file: 4 pieces 98 ms, 3 pieces 88 ms, 1 piece 126 ms
     if (const char *e = getenv("SVTK_BAM_PIPE_MB")) if (*e) pipe_bytes = (size_t)std::max(1ll, atoll(e)) << 20;
-    bool pipelined = image_bytes >= (256u << 20);
+    bool pipelined = image_bytes >= (768u << 20);
     if (const char *e = getenv("SVTK_BAM_PIPE")) if (*e) pipelined = (*e == '1');
     if (pipelined) {      // concurrent launches need their own token slices: room for the whole load, by the capacity guesses
         if (int rc = c->bam_tok.reserve(8 * (size_t)(bz_tok_capacity(infl_cap, blk_cap) + 4))) return rc;
@@ -725,7 +727,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
 
     // ---- the pipeline
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    int T = (int)std::min(12u, std::max(1u, hw / 2));
+    int T = (int)std::min(16u, std::max(1u, hw * 3 / 4));        // pread threads (the calling thread issues the copies and walks the block headers)
     if (const char *e = getenv("SVTK_BAM_THREADS")) if (*e) T = std::max(1, std::min(64, atoi(e)));
     bool fits = true;                                       // the capacity guesses still hold
     CU(cudaEventRecord(c->bam_ev[0], c->stream));
@@ -735,25 +737,52 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     size_t scan_span = 0, scan_off = spans.empty() ? 0 : spans[0].fb;
     size_t span_img0 = 0;                                   // image offset of the current scan span's first byte
     uint8_t carry[65536 + 64];                              // head of a block that straddles two chunks
-    for (size_t si = 0; si < spans.size(); ++si) {
-        for (size_t done = spans[si].fb; done < spans[si].fe;) {
-            const size_t n = std::min(CH, spans[si].fe - done);
+    // reader pool: T threads pread() their slice of every chunk into the pinned ring, up to NSTAGE chunks ahead of the DMA
+    struct Piece { size_t si, file_off, n; };
+    std::vector<Piece> pieces;
+    for (size_t si = 0; si < spans.size(); ++si)
+        for (size_t d = spans[si].fb; d < spans[si].fe; d += CH) pieces.push_back(Piece{si, d, std::min(CH, spans[si].fe - d)});
+    struct Pool {
+        std::vector<std::thread> th;
+        std::atomic<long> released{0};
+        std::atomic<int> failed{0};
+        std::unique_ptr<std::atomic<int>[]> arrived;
+        ~Pool() { failed.store(1); for (auto &x : th) if (x.joinable()) x.join(); }
+    } pool;
+    pool.arrived.reset(new std::atomic<int>[pieces.size() + 1]);
+    for (size_t i = 0; i <= pieces.size(); ++i) pool.arrived[i].store(0);
+    pool.released.store(std::min<long>((long)pieces.size(), NSTAGE));
+    {
+        const int fd = file.fd;
+        char *ring[NSTAGE];
+        for (int i = 0; i < NSTAGE; ++i) ring[i] = (char *)c->bam_stage[i].p;
+        const Piece *pc = pieces.data();
+        const long np = (long)pieces.size();
+        for (int t = 0; t < T; ++t)
+            pool.th.emplace_back([&pool, pc, np, fd, t, T, ring]() {
+                for (long q = 0; q < np; ++q) {
+                    while (pool.released.load(std::memory_order_acquire) <= q) { if (pool.failed.load()) return; std::this_thread::yield(); }
+                    const size_t n = pc[q].n, per = ((n + (size_t)T - 1) / (size_t)T + 4095) & ~(size_t)4095, a = per * (size_t)t;
+                    if (a < n && !pread_all(fd, ring[q % NSTAGE] + a, std::min(per, n - a), pc[q].file_off + a)) { pool.failed.store(1); return; }
+                    pool.arrived[q].fetch_add(1, std::memory_order_release);
+                }
+            });
+    }
+    for (size_t pi = 0; pi < pieces.size(); ++pi) {
+        {
+            const size_t si = pieces[pi].si, done = pieces[pi].file_off, n = pieces[pi].n;
             const int sb = k % NSTAGE;
-            CU(cudaEventSynchronize(c->bam_stage_ev[sb]));              // the DMA that last read this buffer is over
             char *st = (char *)c->bam_stage[sb].p;
-            {
-                const int fd = file.fd;
-                const size_t per = ((n + T - 1) / T + 4095) & ~(size_t)4095;
-                std::vector<int> ok((size_t)T, 1);
-                std::vector<std::thread> th;
-                auto rd = [&, fd, st, done, n, per](int t) { const size_t a = per * (size_t)t; if (a < n) ok[(size_t)t] = pread_all(fd, st + a, std::min(per, n - a), done + a) ? 1 : 0; };
-                for (int t = 1; t < T; ++t) if (per * (size_t)t < n) th.emplace_back(rd, t);
-                rd(0);
-                for (auto &x : th) x.join();
-                for (int v : ok) if (!v) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+            while (pool.arrived[pi].load(std::memory_order_acquire) < T) {
+                if (pool.failed.load()) return fail(SVTK_ERR_IO, "bam: cannot read %s", bam_path);
+                std::this_thread::yield();
             }
             CU(cudaMemcpyAsync((char *)c->bam_comp.p + img_off, st, n, cudaMemcpyHostToDevice, c->stream));
             CU(cudaEventRecord(c->bam_stage_ev[sb], c->stream));
+            if (k >= 1) {                                             // the previous chunk's DMA is over (or nearly): its buffer takes chunk k - 1 + NSTAGE
+                CU(cudaEventSynchronize(c->bam_stage_ev[(k - 1) % NSTAGE]));
+                pool.released.store(std::min<long>((long)pieces.size(), (long)k - 1 + NSTAGE + 1), std::memory_order_release);
+            }
             // ---- block table of the bytes staged so far (this chunk: file bytes [done, done + n) of span si)
             const size_t have_to = done + n;
             while (scan_span == si && scan_off < spans[si].fe) {
@@ -794,7 +823,6 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
                 scan_span = si + 1; scan_off = spans[si + 1].fb;
             }
             img_off += n;
-            done += n;
             // ---- ship the new descriptors, launch their inflate behind this chunk's bytes
             if (fits && pipelined && n_blk > launched && (img_off - last_launch_off >= pipe_bytes || img_off == image_bytes)) {
                 last_launch_off = img_off;
@@ -802,7 +830,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
                 shipped_tab = n_blk;
                 cudaEvent_t ev = c->bam_chunk_ev[k % NCHEV];
                 CU(cudaEventRecord(ev, c->stream));
-                cudaStream_t side = c->bam_side[k % NSIDE];
+                cudaStream_t side = c->bam_side[n_launch % NSIDE];
                 CU(cudaStreamWaitEvent(side, ev, 0));
                 if (first_launch) { CU(cudaEventRecord(c->bam_ev[1], side)); first_launch = false; }
                 if (int rc = launch_inflate(launched, n_blk, side, true)) return rc;
@@ -1043,6 +1071,29 @@ extern "C" int svtk_load_bam_windows(svtk_ctx *ctx, const char *bam_path, const 
     merge_ranges(r);
     return load_bam_ranges(ctx, bam_path, bai_path, &bai, &r, stats);
 }
+
+// compressed bytes of the file under each window, by the .bai's linear index (16 kb tiles): what loading + inflating the reads of
+// that window costs -- the work estimate region shards are balanced by (depth shows up as more bytes per base)
+namespace svtk {
+int bam_window_weights(const char *bam_path, const char *bai_path, int n, const int32_t *chrom, const uint32_t *start, const uint32_t *end, double *weight) {
+    Bai bai;
+    if (int rc = open_bai(bam_path, bai_path, bai)) return rc;
+    for (int i = 0; i < n; ++i) {
+        weight[i] = 1.0;
+        const long long tid = (long long)chrom[i] - 1;
+        if (tid < 0 || tid >= (long long)bai.refs.size()) continue;
+        const BaiRefIdx &R = bai.refs[(size_t)tid];
+        const long long beg = (long long)(uint32_t)(start[i] - 1u), e = (long long)(uint32_t)(end[i] - 1u);
+        if (e < beg || R.lin.empty()) continue;
+        const size_t t0 = std::min<size_t>((size_t)(beg >> 14), R.lin.size() - 1), t1 = (size_t)(e >> 14) + 1;
+        uint64_t vb = R.lin[t0], ve = t1 < R.lin.size() ? R.lin[t1] : R.end;
+        if (vb == 0) vb = R.beg;
+        if (ve < vb) ve = vb;
+        weight[i] = 65536.0 + (double)((ve >> 16) - (vb >> 16));
+    }
+    return 0;
+}
+}  // namespace svtk
 
 extern "C" int svtk_bam_n_ref(const svtk_ctx *ctx) { return ctx ? (int)reinterpret_cast<const Ctx *>(ctx)->bam_ref_names.size() : 0; }
 

@@ -116,6 +116,7 @@ struct Ctx {
 
 int upload(Ctx *c, void *dst, const void *src, size_t bytes);   // host -> device on the ctx stream (pinned staging)
 int set_device(Ctx *c);
-int adopt_device_reads(Ctx *c, const svtk_reads *d);   // what svtk_attach_reads_device does, for loaders that fill c->r_* themselves
+int adopt_device_reads(Ctx *c, const svtk_reads *d);
+int bam_window_weights(const char *bam_path, const char *bai_path, int n, const int32_t *chrom, const uint32_t *start, const uint32_t *end, double *weight);   // svtk_bam.cu   // what svtk_attach_reads_device does, for loaders that fill c->r_* themselves
 
 }  // namespace svtk

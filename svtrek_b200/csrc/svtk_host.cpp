@@ -229,6 +229,7 @@ using namespace svtk;
 // every piece parsed like thread_func parses a line (audit.c:65-173), the pieces' records and windows concatenated in file
 // order.  tid_lo >= 0: only records on references tid_lo .. tid_hi (chrom - 1) are kept -- a region shard of a multi-GPU run.
 static int vcf_front(const char *vcf_path, const svtk_params &params, int tid_lo, int tid_hi, unsigned flags, int n_ref, Batch &b, int *threads_used) {
+    const bool quiet = (flags & SVTK_VCF_QUIET) != 0;
     const bool sharded = tid_lo >= 0;
     const bool owns_unplaced = !sharded || (flags & SVTK_VCF_OWNS_UNPLACED) != 0;
     // ---- read the file (pread by several threads: a 1 M-record VCF is ~150 MB)
@@ -316,7 +317,7 @@ static int vcf_front(const char *vcf_path, const svtk_params &params, int tid_lo
     b.clear();
     b.rec.reserve(nr); b.first.reserve(nr); b.chrom.reserve(nw); b.start.reserve(nw); b.end.reserve(nw); b.pos.reserve(nw); b.kind.reserve(nw);
     for (auto &P : piece) {
-        if (!P.err.empty()) fwrite(P.err.data(), 1, P.err.size(), stderr);
+        if (!P.err.empty() && !quiet) fwrite(P.err.data(), 1, P.err.size(), stderr);
         const int shift = (int)b.chrom.size();
         b.rec.insert(b.rec.end(), P.b.rec.begin(), P.b.rec.end());
         for (int f : P.b.first) b.first.push_back(f < 0 ? -1 : f + shift);
@@ -338,16 +339,22 @@ static int vcf_back(const Batch &b, const int32_t *res, const char *out_path, un
     FILE *out = to_stdout ? stdout : fopen(out_path, "w");
     if (!out) return fail(SVTK_ERR_IO, "cannot open %s: %s", out_path, strerror(errno));
     if (!no_info) fputs("[INFO] Started processing variation file.\n", out);                 // audit.c:252
+    const bool tee = (flags & SVTK_VCF_TEE_STDOUT) != 0 && !to_stdout;
+    if (tee && !no_info) fputs("[INFO] Started processing variation file.\n", stdout);
     std::vector<std::string> parts;
     format_all(b, res, threads, parts, n_lines);
-    for (auto &s : parts) fwrite(s.data(), 1, s.size(), out);
+    for (auto &s : parts) { fwrite(s.data(), 1, s.size(), out); if (tee) fwrite(s.data(), 1, s.size(), stdout); }
     *keep_open = out;
     return 0;
 }
 
 static int vcf_back_close(FILE *out, const char *out_path, unsigned flags, bool ok) {
     const bool to_stdout = !out_path || !strcmp(out_path, "-");
-    if (ok && !(flags & SVTK_VCF_NO_INFO_LINES)) fputs("[INFO] Ended processing variation file\n", out);   // audit.c:354
+    if (ok && !(flags & SVTK_VCF_NO_INFO_LINES)) {
+        fputs("[INFO] Ended processing variation file\n", out);   // audit.c:354
+        if ((flags & SVTK_VCF_TEE_STDOUT) && !to_stdout) fputs("[INFO] Ended processing variation file\n", stdout);
+    }
+    if ((flags & SVTK_VCF_TEE_STDOUT) && !to_stdout) fflush(stdout);
     if (to_stdout) fflush(out); else fclose(out);
     return 0;
 }
@@ -422,6 +429,66 @@ extern "C" int svtk_vcf_format(const char *vcf_path, const svtk_params *params, 
 
 extern "C" int svtk_process_vcf(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int64_t *n_records) {
     return process_vcf_impl(ctx, vcf_path, out_path, nullptr, 0, n_records, nullptr);
+}
+
+extern "C" int svtk_process_vcf_flags(svtk_ctx *ctx, const char *vcf_path, const char *out_path, const char *fasta_path, int32_t tol, uint32_t flags,
+                                      int64_t *n_records, int64_t *n_consensus) {
+    if (tol < 0) tol = reinterpret_cast<Ctx *>(ctx) ? reinterpret_cast<Ctx *>(ctx)->params.consensus_interval : 0;
+    return process_vcf_impl(ctx, vcf_path, out_path, fasta_path, tol, n_records, n_consensus, -1, -1, flags);
+}
+
+// One region shard of a whole job, file to file: the VCF's records are cut into n_shards contiguous runs (VCF order == genomic
+// order) of equal estimated work -- compressed BAM bytes under each record's windows, by the .bai's linear index -- and shard
+// `shard` loads only what ITS windows can see (svtk_load_bam_windows: cuts fall inside references), refines them and writes its
+// lines.  Every shard computes the same cut points; shard outputs concatenated in order are the whole output.
+extern "C" int svtk_audit_shard(svtk_ctx *ctx, const char *bam_path, const char *bai_path, const char *vcf_path, const char *out_path, int32_t shard,
+                                int32_t n_shards, uint32_t flags, int64_t *n_records, svtk_bam_stats *stats) {
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !bam_path || !vcf_path) return fail(SVTK_ERR_ARG, "null argument");
+    if (n_shards < 1 || shard < 0 || shard >= n_shards) return fail(SVTK_ERR_ARG, "bad shard %d of %d", shard, n_shards);
+    Batch b;
+    int T = 1;
+    const unsigned fl = flags | (shard == 0 ? 0u : (unsigned)SVTK_VCF_QUIET);          // malformed lines are reported once, by shard 0
+    if (int rc = vcf_front(vcf_path, c->params, -1, -1, fl, 0, b, &T)) return rc;
+    const size_t nr = b.rec.size(), nw = b.chrom.size();
+    // work per record = compressed bytes under its windows
+    std::vector<double> ww(std::max<size_t>(nw, 1), 1.0);
+    if (nw) if (int rc = bam_window_weights(bam_path, bai_path, (int)nw, b.chrom.data(), b.start.data(), b.end.data(), ww.data())) return rc;
+    std::vector<double> cum(nr + 1, 0.0);
+    std::vector<int> w_first(nr + 1, (int)nw);                 // first window at or after record i
+    {
+        int next = (int)nw;
+        for (size_t i = nr; i-- > 0;) { if (b.first[i] >= 0) next = b.first[i]; w_first[i] = next; }
+    }
+    for (size_t i = 0; i < nr; ++i) {
+        double w = 1.0;
+        for (int k = w_first[i]; k < w_first[i + 1]; ++k) w += ww[(size_t)k];
+        cum[i + 1] = cum[i] + w;
+    }
+    auto cut = [&](int s) -> size_t {
+        if (s <= 0) return 0;
+        if (s >= n_shards) return nr;
+        const double target = cum[nr] * (double)s / (double)n_shards;
+        return (size_t)(std::lower_bound(cum.begin(), cum.end(), target) - cum.begin());
+    };
+    const size_t r0 = std::min(cut(shard), nr), r1 = std::min(std::max(cut(shard + 1), r0), nr);
+    const int w0 = w_first[r0], w1 = w_first[r1];
+    // the shard's own batch (window indices rebased)
+    Batch m;
+    for (size_t i = r0; i < r1; ++i) { m.rec.push_back(b.rec[i]); m.first.push_back(b.first[i] < 0 ? -1 : b.first[i] - w0); }
+    m.chrom.assign(b.chrom.begin() + w0, b.chrom.begin() + w1); m.start.assign(b.start.begin() + w0, b.start.begin() + w1);
+    m.end.assign(b.end.begin() + w0, b.end.begin() + w1); m.pos.assign(b.pos.begin() + w0, b.pos.begin() + w1);
+    m.kind.assign(b.kind.begin() + w0, b.kind.begin() + w1);
+    const svtk_windows w = {(int32_t)m.chrom.size(), m.chrom.data(), m.start.data(), m.end.data(), m.pos.data(), m.kind.data()};
+    if (int rc = svtk_load_bam_windows(ctx, bam_path, bai_path, &w, stats)) return rc;
+    std::vector<int32_t> res(std::max<size_t>(m.chrom.size(), 1));
+    if (w.n_win > 0) if (int rc = svtk_refine_windows(ctx, &w, res.data())) return rc;
+    int64_t n_lines = 0;
+    FILE *out = nullptr;
+    if (int rc = vcf_back(m, res.data(), out_path, flags, T, &n_lines, &out)) return rc;
+    vcf_back_close(out, out_path, flags, true);
+    if (n_records) *n_records = n_lines;
+    return 0;
 }
 
 extern "C" int svtk_process_vcf_region(svtk_ctx *ctx, const char *vcf_path, const char *out_path, int32_t tid_lo, int32_t tid_hi, uint32_t flags,

@@ -3,10 +3,11 @@
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this
  * file's library.  The product (svtrek_b200/csrc) never links, imports or calls it.
  *
- * Parity status: PINNED.  tests/test_oracle_vs_reference.py checks every function below against the
- * unmodified reference compiled from /root/reference (oracle/build_ref.sh -> oracle/_ref/libsvtrek_ref.so
- * and oracle/_ref/svtrek), and tests/golden/ holds vectors captured from that reference so the same
- * checks run where /root/reference is absent (the GPU box).
+ * Parity status: PINNED.  tests/golden/ holds vectors captured from the unmodified reference compiled from
+ * /root/reference (oracle/build_ref.sh -> oracle/_ref/libsvtrek_ref.so and oracle/_ref/svtrek; written by
+ * tools/make_golden.py, which asserts oracle == reference on every vector as it goes), and
+ * tests/test_oracle_golden.py checks every function below against them wherever the tests run.  Where the
+ * compiled reference is present, tests/test_golden_drift.py regenerates the vectors and fails on any drift.
  *
  * The algorithm is restated from the reference's behaviour, not copied: reads live in the SoA layout the
  * GPU path uses (no HTSlib), selection is a range filter instead of an index iterator, the consensus is a

@@ -116,6 +116,22 @@ def test_process_vcf_stdout_golden(auditor):
     auditor.set_params(**api.DEFAULT_PARAMS)
 
 
+def test_process_vcf_on_a_vcf_from_the_references_simvcf_py(auditor):
+    """The VCF utils/simvcf.py itself wrote (tests/golden/simvcf_cli.json) through the whole GPU path == `svtrek audt -t 1`."""
+    rs, _ = util.load_reads("c1mini_reads.npz")
+    auditor.load_reads(rs)
+    auditor.set_params(**api.DEFAULT_PARAMS)
+    gold = util.load_json("simvcf_cli.json")
+    with tempfile.TemporaryDirectory() as d:
+        for style, g in gold.items():
+            vcf, out = os.path.join(d, style + ".vcf"), os.path.join(d, "out.txt")
+            open(vcf, "w").write(g["vcf"])
+            n = auditor.process_vcf(vcf, out)
+            text = open(out).read()
+            assert text == g["stdout"], (style, _first_diff(text, g["stdout"]))
+            assert n == g["stdout"].count("\n") - 2
+
+
 def _first_diff(a, b):
     for i, (x, y) in enumerate(zip(a.splitlines(), b.splitlines())):
         if x != y:

@@ -99,3 +99,20 @@ def test_many_pieces_equal_one_piece(lib_built, tmp_path, monkeypatch):
         assert np.array_equal(res["1"][0][k], res["16"][0][k]), k
     assert res["1"][1] == res["16"][1]
     assert len(res["1"][0]["chrom"]) > 400
+
+
+def test_a_vcf_written_by_the_references_own_simvcf_py(lib_built, tmp_path, capfd):
+    """tests/golden/simvcf_cli.json: utils/simvcf.py (unmodified, tools/make_simvcf_golden.py) wrote the VCF -- header lines, CIPOS /
+    CIEND before END (END parses as CIEND's value), 'chr' stripped from CHROM, untouched short variants -- and
+    `svtrek audt -t 1` printed the stdout.  Front end + oracle + back end reproduce it byte for byte."""
+    rs, _ = util.load_reads("c1mini_reads.npz")
+    orc = B.OracleReads(rs)
+    gold = util.load_json("simvcf_cli.json")
+    for style, g in gold.items():
+        vcf, out = str(tmp_path / (style + ".vcf")), str(tmp_path / "o.txt")
+        open(vcf, "w").write(g["vcf"])
+        n, w = _audit_on_cpu(vcf, out, orc, dict(api.DEFAULT_PARAMS), rs.n_tid, capfd=capfd)
+        err = capfd.readouterr().err
+        assert open(out).read() == g["stdout"], style
+        assert err == g["stderr"], style
+        assert n == g["stdout"].count("\n") - 2 and n >= 90

@@ -17,7 +17,7 @@ sys.path.insert(0, ROOT)
 from oracle import binding as B  # noqa: E402
 from svtrek_b200 import simreads as S  # noqa: E402
 
-GOLD = os.path.join(ROOT, "tests", "golden")
+GOLD = os.environ.get("SVTK_GOLDEN_OUT") or os.path.join(ROOT, "tests", "golden")      # SVTK_GOLDEN_OUT: tests/test_golden_drift.py regenerates into a scratch directory
 os.makedirs(GOLD, exist_ok=True)
 
 
@@ -314,5 +314,6 @@ if __name__ == "__main__":
         golden_consensus()
         golden_quirks(tmp)
         golden_mix(tmp)
-        golden_cli(tmp)
+        if os.environ.get("SVTK_GOLDEN_SKIP_CLI") != "1":      # the CLI captures belong to the stored c1mini read set (c1mini_reads.npz), not to a fresh simulate()
+            golden_cli(tmp)
     print("golden vectors written to", GOLD)

@@ -269,6 +269,78 @@ __device__ inline ScanResult consensus_scan_warp(const int *a, int n, int pos, T
     return ScanResult{0, -1, best, dist};
 }
 
+// consensus_pos for n <= 32 sorted values held one per lane (lane i: a[i], i < n): both scans of refinement.c:56-98 without
+// shared memory.  The cluster behind an anchor is a contiguous run of the sorted values (the j loops stop at the first value
+// more than `interval` away), so its bounds come from a 5-step search over the lanes and its sum from one 64-bit prefix scan;
+// the reference's sequential max_count / distance bookkeeping is then replayed in scan order over the lanes that qualify.
+__device__ __forceinline__ int consensus_pos_lanes(int v, int n, int pos, Tunables t) {
+    const int lane = lane_id();
+    const bool valid = lane < n;
+    // inclusive prefix sums of the values as the reference accumulates them: uint64_t total += int (sign-extended)
+    unsigned long long P = valid ? (unsigned long long)(long long)v : 0ull;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned long long o = __shfl_up_sync(FULL, P, d); if (lane >= d) P += o; }
+    const unsigned inr = __ballot_sync(FULL, valid && iabs_wrap(pos - v) < t.range);
+    // cluster bounds: lo = first j <= lane with a[lane] <= a[j] + interval ; hi = last j >= lane with a[j] <= a[lane] + interval
+    int lo = 0, lo_hi = lane, hi = lane, hi_hi = n - 1;           // search ranges [lo, lo_hi] and [hi, hi_hi] (answers inside)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int m1 = (lo + lo_hi) >> 1, m2 = (hi + hi_hi + 1) >> 1;
+        const int a1 = __shfl_sync(FULL, v, m1 & 31), a2 = __shfl_sync(FULL, v, m2 & 31);
+        if (lo < lo_hi) { if (v <= a1 + t.interval) lo_hi = m1; else lo = m1 + 1; }
+        if (hi < hi_hi) { if (a2 <= v + t.interval) hi = m2; else hi_hi = m2 - 1; }
+    }
+    const int loc = lo_hi, hic = valid ? hi : lane;               // converged (5 steps cover 32 lanes)
+    const unsigned long long Plo = __shfl_sync(FULL, P, (loc - 1) & 31), Phi = __shfl_sync(FULL, P, hic & 31), Pm1 = __shfl_up_sync(FULL, P, 1);
+    int best_l = -1, dist_l = 0x7fffffff, best_r = -1, dist_r = 0x7fffffff;
+    {   // ---- leftward scan from lower_bound(pos + 25): index of the last value <= x, clamped to 0 (refinement.c:3-10,56)
+        const unsigned gt = __ballot_sync(FULL, valid && v > pos + SV_MIN_LENGTH / 2);
+        const int first = gt ? __ffs(gt) - 1 : n;
+        const int start = gt ? (first > 0 ? first - 1 : 0) : n - 1;
+        const unsigned upto = start >= 31 ? 0xffffffffu : ((2u << start) - 1u);
+        const unsigned stop = ~inr & upto;                        // the loop ends at the first out-of-range value going down
+        const unsigned run = upto & (stop ? ~((2u << (31 - __clz(stop))) - 1u) : 0xffffffffu);
+        const int count = lane - loc + 1;
+        const unsigned long long total = P - (loc > 0 ? Plo : 0ull);
+        const int cand = (int)((total + (unsigned long long)(long long)(count / 2)) / (unsigned long long)(long long)count);
+        const int d = iabs_wrap(pos - cand);
+        int maxc = t.min_count - 1;
+        unsigned pending = run;
+        while (true) {
+            const unsigned m = __ballot_sync(FULL, ((pending >> lane) & 1u) && count > maxc);
+            if (!m) break;
+            const int l = 31 - __clz(m);                          // scan order: highest lane first
+            const int c = __shfl_sync(FULL, count, l), cd = __shfl_sync(FULL, cand, l), dd = __shfl_sync(FULL, d, l);
+            if (dd < t.interval) return cd;                       // refinement.c:67-68
+            if (dd < dist_l) { maxc = c; best_l = cd; dist_l = dd; }
+            pending &= (1u << l) - 1u;
+        }
+    }
+    {   // ---- rightward scan from upper_bound(pos - 25): 0 or n - 1 on ascending input (refinement.c:12-19,78)
+        const int a0 = __shfl_sync(FULL, v, 0);
+        const int start = (a0 < pos - SV_MIN_LENGTH / 2) ? 0 : n - 1;
+        const unsigned from = start >= 32 ? 0u : ~((1u << start) - 1u);
+        const unsigned stop = ~inr & from;                        // first out-of-range (or invalid) lane going up
+        const unsigned run = from & (stop ? ((1u << (__ffs(stop) - 1)) - 1u) : 0xffffffffu);
+        const int count = hic - lane + 1;
+        const unsigned long long total = Phi - (lane > 0 ? Pm1 : 0ull);
+        const int cand = (int)((total + (unsigned long long)(long long)(count / 2)) / (unsigned long long)(long long)count);
+        const int d = iabs_wrap(pos - cand);
+        int maxc = t.min_count - 1;
+        unsigned pending = run;
+        while (true) {
+            const unsigned m = __ballot_sync(FULL, ((pending >> lane) & 1u) && count > maxc);
+            if (!m) break;
+            const int l = __ffs(m) - 1;                           // scan order: lowest lane first
+            const int c = __shfl_sync(FULL, count, l), cd = __shfl_sync(FULL, cand, l), dd = __shfl_sync(FULL, d, l);
+            if (dd < t.interval) return cd;                       // refinement.c:89-90
+            if (dd < dist_r) { maxc = c; best_r = cd; dist_r = dd; }
+            pending &= ~((2u << l) - 1u);
+        }
+    }
+    return dist_l < dist_r ? best_l : best_r;                     // refinement.c:100
+}
+
 // a: sorted, n >= 1, n >= min_count.  s_res: 2 ScanResult slots in shared memory.  Needs >= 2 warps.
 __device__ inline int block_consensus(const int *a, int n, int pos, Tunables t, ScanResult *s_res) {
     const int warp = threadIdx.x >> 5;

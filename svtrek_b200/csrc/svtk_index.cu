@@ -79,6 +79,33 @@ __device__ __forceinline__ uint32_t mad_hi_u32(uint32_t a, uint32_t b, uint32_t 
     return d;
 }
 
+// A segment keeps its events in two classes, one after the other: first the ones deletion windows look at (D > 50, trailing /
+// leading soft clip), then the insertions.  A window reads only its own class -- half the events at an even DEL / INS mix.
+// Descriptor .y = count of the first class | count of the second << 16 (a segment holds <= IDX_DEVCAP events).
+__device__ __forceinline__ uint32_t seg_count(uint32_t y) { return (y & 0xffffu) + (y >> 16); }
+__device__ __forceinline__ void seg_class(uint32_t base, uint32_t y, bool ins, uint32_t &cbase, uint32_t &ccount) {
+    cbase = base + (ins ? (y & 0xffffu) : 0u);
+    ccount = ins ? (y >> 16) : (y & 0xffffu);
+}
+
+// s.ev[0 .. nev) -> X.events[fb ..], stably partitioned by class; returns the packed counts (uniform).  nev <= 64.
+template <class SH>
+__device__ __forceinline__ uint32_t index_store_partitioned(SH &s, const DevIndex &X, uint32_t fb, int nev) {
+    const int lane = lane_id();
+    const unsigned below = (1u << lane) - 1u;
+    uint4 e0 = make_uint4(0u, 0u, 0u, 0u), e1 = e0;
+    const bool h0 = lane < nev, h1 = lane + 32 < nev;
+    if (h0) e0 = s.ev[lane];
+    if (h1) e1 = s.ev[lane + 32];
+    const bool b0 = h0 && (e0.y & 15u) == (uint32_t)EV_INS, b1 = h1 && (e1.y & 15u) == (uint32_t)EV_INS;
+    const unsigned mb0 = __ballot_sync(FULL, b0), mb1 = __ballot_sync(FULL, b1);
+    const unsigned ma0 = __ballot_sync(FULL, h0 && !b0), ma1 = __ballot_sync(FULL, h1 && !b1);
+    const uint32_t nA = (uint32_t)(__popc(ma0) + __popc(ma1)), nB = (uint32_t)(__popc(mb0) + __popc(mb1));
+    if (h0) X.events[(size_t)fb + (b0 ? nA + (uint32_t)__popc(mb0 & below) : (uint32_t)__popc(ma0 & below))] = e0;
+    if (h1) X.events[(size_t)fb + (b1 ? nA + (uint32_t)(__popc(mb0) + __popc(mb1 & below)) : (uint32_t)(__popc(ma0) + __popc(ma1 & below)))] = e1;
+    return nA | nB << 16;
+}
+
 // append the warp's staged events to the chunk as one more segment; `head` (uniform) is the chunk's newest segment
 template <class SH>
 __device__ __forceinline__ void index_flush_warp(SH &s, const DevIndex &X, int pool, int nev, uint4 &head) {
@@ -102,9 +129,8 @@ __device__ __forceinline__ void index_flush_warp(SH &s, const DevIndex &X, int p
     }
     fb = __shfl_sync(FULL, fb, 0);
     nh.x = __shfl_sync(FULL, nh.x, 0); nh.y = __shfl_sync(FULL, nh.y, 0); nh.z = __shfl_sync(FULL, nh.z, 0);
+    if (fb != 0xffffffffu) nh.y = index_store_partitioned(s, X, fb, nev);
     head = nh;
-    if (fb != 0xffffffffu)
-        for (int i = lane; i < nev; i += 32) X.events[(size_t)fb + i] = s.ev[i];
     __syncwarp();
 }
 
@@ -137,6 +163,7 @@ static_assert(IDX_FIXK <= 32, "one lane per fixed slot");
 #endif
 constexpr int IDX_DEVCAP = SVTK_IDX_DEVCAP;  // events a warp stages between flushes (>= 32 + 2 * IDX_READS: one resolve round, the clip events)
 static_assert(IDX_DEVCAP >= 32 + 2 * IDX_READS, "event staging too small");
+static_assert(IDX_DEVCAP <= 64, "index_store_partitioned handles two events per lane");
 
 struct __align__(16) IndexDeferShared {
     uint4 ev[IDX_DEVCAP];
@@ -428,8 +455,9 @@ __global__ void __launch_bounds__(IDX_WARPS * 32, SVTK_IDX_DMINB) k_index_reads_
     if (nev > 0 && nev <= IDX_FIXK && head.y == 0u) {
         const uint32_t fb = (uint32_t)IDX_POOLS * X.pool_cap + (uint32_t)c * (uint32_t)IDX_FIXK;
         if (lane == 0) atomicAdd(&X.ctrl[pool * CTRL_STRIDE + 1], (unsigned int)nev);
-        if (lane < nev) X.events[(size_t)fb + lane] = s.ev[lane];
-        head = make_uint4(fb, (uint32_t)nev, 0xffffffffu, head.w);
+        __syncwarp();
+        const uint32_t packed = index_store_partitioned(s, X, fb, nev);
+        head = make_uint4(fb, packed, 0xffffffffu, head.w);
     } else
 #endif
     if (nev > 0) index_flush_warp(s, X, pool, nev, head);
@@ -642,6 +670,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
         return;
     }
     const unsigned below = (1u << lane) - 1u;
+    const bool ins_class = kind == KIND_INS;
     // consensus_pos only ever looks at signatures within `range` of pos (plus `interval` for the cluster behind an anchor), at
     // the array's two ends and at its size (refinement.c:43,56-98).  With the values further away replaced by their nearest
     // representative on either side -- the largest one below pos - reach, the smallest one above pos + reach -- every loop of
@@ -670,6 +699,7 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
         // 32 chunk heads at a time, then their events as ONE flat list: lane e takes event e of the concatenation
         uint4 myh = make_uint4(0u, 0u, 0xffffffffu, 0u);
         if (cb + lane <= c1) myh = __ldg(X.chunks + cb + lane);
+        seg_class(myh.x, myh.y, ins_class, myh.x, myh.y);            // from here on: base and count of this window's class
         uint32_t incl = myh.y;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += o; }
@@ -699,7 +729,8 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
             chained &= chained - 1;
             uint32_t nxt = __shfl_sync(FULL, myh.z, j);
             while (nxt != 0xffffffffu) {
-                const uint4 seg = __ldg(X.segs + nxt);
+                uint4 seg = __ldg(X.segs + nxt);
+                seg_class(seg.x, seg.y, ins_class, seg.x, seg.y);
                 if (STATS) { n_scan += seg.y; n_seg += 1; }
                 for (uint32_t e0 = 0; e0 < seg.y; e0 += 32) {
                     int code = 0, val = 0;
@@ -758,16 +789,21 @@ __global__ void __launch_bounds__(RW_WARPS * 32, SVTK_RW_MINB) k_refine_warp(Dev
     if (any_lo) { const int v = __reduce_max_sync(FULL, far_lo); if (lane == 0) s.sig[nk] = v; }
     if (any_hi) { const int v = __reduce_min_sync(FULL, far_hi); if (lane == 0) s.sig[nk + (any_lo ? 1 : 0)] = v; }
     __syncwarp();
-    if (nf <= 32) warp_sort_segment<1>(s.sig, nf);
-    else if (nf <= 64) warp_sort_segment<2>(s.sig, nf);
-    else if (nf <= 128) warp_sort_segment<4>(s.sig, nf);
-    else warp_sort_segment<8>(s.sig, nf);
     int res;
-    const ScanResult L = consensus_scan_warp(s.sig, nf, pos, t, true);
-    if (L.early) res = L.value;
-    else {
-        const ScanResult Rr = consensus_scan_warp(s.sig, nf, pos, t, false);
-        res = Rr.early ? Rr.value : (L.dist < Rr.dist ? L.best : Rr.best);
+    if (nf <= 32) {                                              // the common case: sort and both scans in registers
+        int v[1] = {lane < nf ? s.sig[lane] : 0x7fffffff};
+        warp_bitonic_sort<1>(v);
+        res = consensus_pos_lanes(v[0], nf, pos, t);
+    } else {
+        if (nf <= 64) warp_sort_segment<2>(s.sig, nf);
+        else if (nf <= 128) warp_sort_segment<4>(s.sig, nf);
+        else warp_sort_segment<8>(s.sig, nf);
+        const ScanResult L = consensus_scan_warp(s.sig, nf, pos, t, true);
+        if (L.early) res = L.value;
+        else {
+            const ScanResult Rr = consensus_scan_warp(s.sig, nf, pos, t, false);
+            res = Rr.early ? Rr.value : (L.dist < Rr.dist ? L.best : Rr.best);
+        }
     }
     if (lane == 0) result[w] = res;
 }
@@ -817,7 +853,8 @@ __global__ void __launch_bounds__(NT) k_refine_block(DevReads R, DevWindows W, D
         for (long long c = c0 + warp; c <= c1; c += NWARP) {
             uint4 sg = __ldg(X.chunks + c);
             while (true) {
-                const uint32_t base = sg.x, cnt = sg.y;
+                uint32_t base, cnt;
+                seg_class(sg.x, sg.y, kind == KIND_INS, base, cnt);
                 for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
                     int code = 0, val = 0;
                     if (e0 + lane < cnt) code = event_for_window(__ldg(X.events + (size_t)base + e0 + lane), kind, w_start, w_end, beg, lo, hi, X.rend, val);

@@ -62,6 +62,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
     ap.add_argument("--ref-threads", type=int, default=0)
     ap.add_argument("--no-bam", action="store_true", help="skip the file-to-file leg")
+    ap.add_argument("--no-c3", action="store_true", help="N = 1: skip the extra configs[2]-sized resident pass (c3_single_gpu)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="file-to-file steps (default: min(steps, 10))")
     ap.add_argument("--poa-sets", type=int, default=4000, help="INS read sets per GPU of the POA (K3) leg: a bounded sample of configs[3]'s 20k records; 0 skips the leg")
     ap.add_argument("--poa-steps", type=int, default=2)
@@ -300,11 +301,12 @@ def pinned(arr):
 POA_DESC = "BASELINE.json configs[3] sample: INS read sets, inserted length log-uniform 50 bp - 10 kb, 60x depth x 0.8 carriers, 8 % ONT-like errors"
 
 
-def poa_leg(a, rank, n_sets, steps):
+def poa_leg(a, rank, world, n_sets, steps):
     """K3: svtk_poa_consensus (host buffers in, consensus out) on this rank's read sets.  GCUPS = band cells the kernel itself
     counted (5-state convex cell updates) / CUDA-event time of k_poa_sets; e2e = the same cells / wall time of the call."""
     from svtrek_b200 import simpoa as P
-    sets = P.ins_workload(SEED0 + 77 + 1000 * rank, n_sets, depth=60, carrier=0.8, err=0.08, len_lo=50, len_hi=10000)
+    # one job of n_sets x world read sets, dealt to the ranks by estimated work (heaviest first, snake order)
+    sets, _mine, _all = P.ins_workload_shard(SEED0 + 77, n_sets * world, world, rank, depth=60, carrier=0.8, err=0.08, len_lo=50, len_hi=10000)
     so, qo, b = P.pack(sets)
     a.poa_consensus(so, qo, b)                       # warm-up: scratch allocation, first touch
     kms, wall, st, cons = 0.0, 0.0, None, None
@@ -313,7 +315,7 @@ def poa_leg(a, rank, n_sets, steps):
         cons, st = a.poa_consensus(so, qo, b)
         wall += time.perf_counter() - t0
         kms += st["kernel_ms"]
-    return sets, cons, dict(cells=st["cells"], cells_full=st["cells_full"], n_sets=n_sets, n_reads=int(len(qo) - 1), n_bases=int(len(b)),
+    return sets, cons, dict(cells=st["cells"], cells_full=st["cells_full"], n_sets=len(sets), n_reads=int(len(qo) - 1), n_bases=int(len(b)),
                             kernel_ms=kms / steps, wall_ms=wall * 1e3 / steps, workers=st["workers"], relaunched=st["relaunched"],
                             phase_cycles=st["phase_cycles"])
 
@@ -392,8 +394,16 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     K, W = args.steps, max(args.warmup, 3)
+    if world > 1 and "SVTK_BAM_THREADS" not in os.environ:       # the ranks share the host's cores: pread threads per rank
+        os.environ["SVTK_BAM_THREADS"] = str(max(2, (os.cpu_count() or 2) // world - 1))
     if args.workload == "c3":
-        return run_c3(args, rank, world, local, dev, dist, K, W)
+        out = c3_measure(args, rank, world, local, dev, dist, K, W)
+        if rank == 0:
+            emit(out)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     def barrier():
         torch.cuda.synchronize()
@@ -487,7 +497,7 @@ def run_ours(args):
     # ---- K3: POA consensus leg (GCUPS half of the metric)
     poa = None
     if args.poa_sets > 0:
-        poa_sets_l, poa_cons, poa = poa_leg(a, rank, args.poa_sets, max(1, args.poa_steps))
+        poa_sets_l, poa_cons, poa = poa_leg(a, rank, world, args.poa_sets, max(1, args.poa_steps))
         pr = torch.tensor([poa["kernel_ms"], poa["wall_ms"]], dtype=torch.float64, device=dev)
         pt = torch.tensor([float(poa["cells"]), float(poa["cells_full"]), float(poa["n_sets"])], dtype=torch.float64, device=dev)
         if world > 1:
@@ -581,8 +591,15 @@ def run_ours(args):
                 out["poa_gcups"]["cpu_baseline"] = poa_cpu_baseline(poa_sets_l, poa_cons)
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_reference_baseline(args, paths, n_records, port_s, n_win)
-        emit(out)
     a.close()
+    if world == 1 and not args.no_c3 and args.workload == "c2" and args.scale == 1.0:
+        # the same pass at the size the north star states its HBM target on (configs[2], 3.1 Gb, one GPU): its own roofline
+        sub = argparse.Namespace(**vars(args))
+        sub.workload = "c3"
+        c3 = c3_measure(sub, 0, 1, local, dev, dist, min(K, 10), 3)
+        out["c3_single_gpu"] = {k: c3[k] for k in ("value", "unit", "ms_per_step", "steps", "config", "roofline", "roofline_other", "parity", "work", "kernel_share")}
+    if rank == 0:
+        emit(out)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -702,7 +719,8 @@ def _c3_contig(job):
     return i, rs.pos, rs.end, rs.n_cigar, rs.cigar, truth.pos0, truth.length, truth.is_del
 
 
-def run_c3(args, rank, world, local, dev, dist, K, W):
+def c3_measure(args, rank, world, local, dev, dist, K, W):
+    """The resident pass on configs[2] cut into `world` region shards; returns rank 0's JSON object (None elsewhere)."""
     import multiprocessing as mp
     import torch
     from oracle import binding as B
@@ -826,6 +844,7 @@ def run_c3(args, rank, world, local, dev, dist, K, W):
         dist.all_reduce(red, op=dist.ReduceOp.MAX); dist.all_reduce(tot, op=dist.ReduceOp.SUM); dist.all_reduce(per_rank, op=dist.ReduceOp.SUM)
     dev_ms_max, e2e_ms_max = [float(x) for x in red.cpu()]
     rec_all, launches_all, h2d_all, d2h_all, win_all, words_all, reads_all = [float(x) for x in tot.cpu()]
+    out = None
     if rank == 0:
         peak, peak_src = measured_peak()
         idx_ms = tim["index_kernel_ms"] / max(1, tim["index_kernel_launches"])
@@ -834,7 +853,7 @@ def run_c3(args, rank, world, local, dev, dist, K, W):
         dom = max(kern, key=lambda k: kern[k][0])
         oth = [k for k in kern if k != dom][0]
         achieved = kern[dom][1] / (kern[dom][0] * 1e-3) / 1e9 if kern[dom][0] > 0 else 0.0
-        emit({"metric": METRIC, "value": rec_all * K / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        out = {"metric": METRIC, "value": rec_all * K / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
               "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic", "impl": "ours",
               "config": job_config(args, world), "clocks": clocks,
               "e2e": {"value": rec_all * Ke / (e2e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all), "ms_per_step": e2e_ms_max / Ke,
@@ -849,11 +868,9 @@ def run_c3(args, rank, world, local, dev, dist, K, W):
                            "algorithmic_bytes_per_launch": kern[dom][1], "kernel_ms": kern[dom][0], "work": stats},
               "roofline_other": {"kernel": oth, "achieved": kern[oth][1] / (kern[oth][0] * 1e-3) / 1e9 if kern[oth][0] > 0 else 0.0, "unit": "GB/s", "peak": peak,
                                  "frac": (kern[oth][1] / (kern[oth][0] * 1e-3) / 1e9 / peak) if kern[oth][0] > 0 else None,
-                                 "algorithmic_bytes_per_launch": kern[oth][1], "kernel_ms": kern[oth][0]}})
+                                 "algorithmic_bytes_per_launch": kern[oth][1], "kernel_ms": kern[oth][0]}}
     a.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    return out if rank == 0 else None
 
 
 # ------------------------------------------------------------------------------------------------------------

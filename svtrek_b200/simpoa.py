@@ -97,3 +97,25 @@ def ins_workload(seed, n_sets, depth=60, carrier=0.8, err=0.08, len_lo=50, len_h
         n = max(2, int(rng.binomial(depth, carrier)))
         sets.append([mutate(rng, tpl, err) for _ in range(n)])
     return sets
+
+
+def ins_workload_shard(seed, n_total, world, rank, depth=60, carrier=0.8, err=0.08, len_lo=50, len_hi=10000):
+    """Rank `rank`'s share of ONE job of n_total INS read sets (same distribution as ins_workload): every set's inserted length,
+    read count and seed are drawn up front, the sets are dealt to the ranks heaviest first in snake order so that every rank gets
+    the same estimated work (rows x band: reads x L x (20 + 0.02 L)), and only the rank's own sets are generated."""
+    rng = np.random.default_rng(seed)
+    L = np.rint(np.exp(rng.uniform(np.log(len_lo), np.log(len_hi), n_total))).astype(np.int64)
+    n = np.maximum(2, rng.binomial(depth, carrier, n_total))
+    seeds = rng.integers(0, 2**62, n_total)
+    work = n * L * (20.0 + 0.02 * L)
+    order = np.argsort(-work, kind="stable")
+    k = np.arange(n_total)
+    rnd, posn = k // world, k % world
+    owner = np.where(rnd % 2 == 0, posn, world - 1 - posn)
+    mine = order[owner == rank]
+    sets = []
+    for i in mine.tolist():
+        r = np.random.default_rng(int(seeds[i]))
+        tpl = r.integers(0, 4, int(L[i])).astype(np.uint8)
+        sets.append([mutate(r, tpl, err) for _ in range(int(n[i]))])
+    return sets, float(work[mine].sum()), float(work.sum())

@@ -308,15 +308,23 @@ static int resolve_overflow(Ctx *c) {
             const LaunchWindows w = c->pend_win;
             int32_t *res = c->pend_result;
             const int mode = c->pend_mode;
-            // every flush bumped its counter even when it found no room: the tops are the exact need
-            if (int rc = ensure_index_buffers(c, (uint64_t)max_pool + 64, c->idx_n_segs + c->idx_n_events / 32 + 1024)) return rc;
-            c->index_valid = false;
-            if (int rc = launch_batch(c, w, res, mode)) return rc;
-            CU(cudaStreamSynchronize(c->stream));
-            unsigned int err2 = 0; uint64_t e2 = 0, s2 = 0;
-            index_totals(c, &e2, &s2, &max_pool, &err2);
-            if (err2) return fail(SVTK_ERR_STATE, "signature index still out of room after re-dimensioning (events %llu, segments %llu)",
-                                  (unsigned long long)e2, (unsigned long long)s2);
+            // every flush bumped its counter even when it found no room, so the tops are what THIS layout needed; a rebuild can
+            // need a little more (a chunk whose earlier flushes failed kept its last events in its own slots and never counted
+            // them): grow with slack and try again until the build goes through
+            uint64_t pool_need = (uint64_t)max_pool + 64, seg_need = c->idx_n_segs + c->idx_n_events / 32 + 1024;
+            for (int attempt = 0;; ++attempt) {
+                if (int rc = ensure_index_buffers(c, pool_need, seg_need)) return rc;
+                c->index_valid = false;
+                if (int rc = launch_batch(c, w, res, mode)) return rc;
+                CU(cudaStreamSynchronize(c->stream));
+                unsigned int err2 = 0; uint64_t e2 = 0, s2 = 0;
+                index_totals(c, &e2, &s2, &max_pool, &err2);
+                if (!err2) break;
+                if (attempt >= 6) return fail(SVTK_ERR_STATE, "signature index still out of room after re-dimensioning (events %llu, segments %llu)",
+                                              (unsigned long long)e2, (unsigned long long)s2);
+                pool_need = std::max<uint64_t>(pool_need * 3 / 2, (uint64_t)max_pool + 4096);
+                seg_need = std::max<uint64_t>(seg_need * 3 / 2, s2 + 4096);
+            }
             return resolve_overflow(c);
         }
     }

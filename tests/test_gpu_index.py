@@ -61,6 +61,33 @@ def test_indexed_equals_walker_equals_oracle_c1(auditor):
     assert st["index_bytes"] >= 4 * st["n_words"]
 
 
+def test_index_regrow_when_late_chunks_find_their_pools_already_empty(auditor):
+    """many more signature-dense chunks than fit the GPU at once (16 sub-pools x a few resident chunks), so chunks START
+    after their pool ran dry: all their flushes fail, their last events sit in their own slots uncounted, and the exact-size rebuild
+    of the first retry can fall short.  The re-dimensioning now retries with slack until the build goes through; results == oracle."""
+    rng = np.random.default_rng(8)
+    reads = []
+    for i in range(24_000):                                   # 3 000 chunks of 8 reads, ~40 events each: 3x the first-guess pool
+        pos = int(100_000 + i * 40)
+        words = []
+        for _k in range(40):
+            words.append(int(rng.integers(5, 30)) << 4)
+            words.append(int(rng.integers(51, 60)) << 4 | (2 if rng.random() < 0.6 else 1))
+        words.append(50 << 4)
+        reads.append((pos, words))
+    rs = _readset(reads)
+    auditor.load_reads(rs)
+    auditor.set_params(wider_interval=3000, median_interval=1500, narrow_interval=400)
+    centers = np.array([150_000, 400_000, 700_000, 1_000_000, 300_000, 900_000, 500_000])
+    kinds = np.array([0, 0, 0, 1, 1, 2, 2])
+    w = _win(np.ones(7), centers - 3000, centers + 500, centers - 7, kinds)
+    indexed, walker, st, _ = _both_paths(auditor, w)
+    want = B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+    assert list(indexed) == list(want) and list(walker) == list(want)
+    assert st["n_events"] == 24_000 * 40
+    auditor.set_params(**api.DEFAULT_PARAMS)
+
+
 def test_index_pool_regrow_and_multi_segment_chunks(auditor):
     """Reads that are almost all D > 50 ops: far more events than the first-guess pool, chunks that flush many
     512-event segments, tiles in which every second word is a candidate."""

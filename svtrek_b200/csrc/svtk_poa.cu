@@ -74,6 +74,7 @@ struct PoaLaunch {
     unsigned char *scratch;
     PoaTrace trace;
     int have_trace;
+    unsigned long long *times;         // SVTK_POA_DEBUG: per read set {start, end} of %globaltimer (ns), else null
 };
 
 // NW = 1: one warp per read set (the throughput shape).  NW = 8: the whole 256-thread CTA shares each DP row and the
@@ -123,9 +124,11 @@ __global__ void __launch_bounds__(32 * NW, NW == 1 ? SVTK_POA_MINB : 1) k_poa_se
             const int sv = L.items[i0 + it];
             const long long co = L.cons_off[sv];
             const int cap = (int)(L.cons_off[sv + 1] - co);
+            if (L.times && lane == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); L.times[2 * sv] = t; }
             const int len = poa_run_set<NW>(s, xch, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
                                         L.have_trace ? &L.trace : nullptr);
             if (lane == 0) {
+                if (L.times) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); L.times[2 * sv + 1] = t; }
                 L.status[sv] = s.status;
                 L.cons_len[sv] = len;
                 if (!s.status) {
@@ -397,6 +400,12 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         L.set_off = d_set_off; L.seq_off = d_seq_off; L.bases = d_bases; L.cons = d_cons; L.cov = d_cov; L.cons_off = d_cons_off;
         L.cons_len = d_len; L.status = d_status; L.cells = d_cells; L.scratch = (unsigned char *)c->poa_scratch.p;
         L.trace = tr; L.have_trace = trace ? 1 : 0;
+        const bool dbg = getenv("SVTK_POA_DEBUG") != nullptr;
+        if (dbg) {
+            if (int rc = c->tmp_c.reserve(16 * (size_t)ns + 16)) return rc;
+            CU(cudaMemsetAsync(c->tmp_c.p, 0, 16 * (size_t)ns, c->stream));
+            L.times = (unsigned long long *)c->tmp_c.p;
+        }
         CU(cudaEventRecord(c->poa_ev[0], c->stream));
         if (wA > 0) {                                          // side stream: both launches are resident together
             CU(cudaStreamWaitEvent(c->poa_side, c->poa_ev[0], 0));
@@ -424,6 +433,28 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         if (getenv("SVTK_POA_DEBUG")) {
             float msA = 0.f;
             if (wA > 0) cudaEventElapsedTime(&msA, c->poa_ev[0], c->poa_ev[2]);
+            std::vector<unsigned long long> tm(2 * (size_t)ns);
+            cudaMemcpy(tm.data(), c->tmp_c.p, 16 * (size_t)ns, cudaMemcpyDeviceToHost);
+            unsigned long long t0 = ~0ull;
+            for (int x : todo) if (tm[2 * x]) t0 = std::min(t0, tm[2 * x]);
+            for (size_t k = 0; k < cls.size(); ++k) {
+                double first = 1e30, last = 0, sum = 0, lstart = 0;
+                for (int i = cls[k].item_begin; i < cls[k].item_end; ++i) {
+                    const int x = todo[i];
+                    const double a = (tm[2 * x] - t0) * 1e-6, b = (tm[2 * x + 1] - t0) * 1e-6;
+                    first = std::min(first, a); last = std::max(last, b); lstart = std::max(lstart, a); sum += b - a;
+                }
+                fprintf(stderr, "[poa]   class %zu %s cls %d: %d sets, %d workers, %.1f MB/worker; first start %.0f ms, last start %.0f ms, last end %.0f ms, busy %.1f worker-s\n",
+                        k, k < clsA.size() ? "wide" : "warp", info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
+                        cls[k].worker_end - cls[k].worker_begin, poa_layout(cls[k].caps).total / 1e6, first, lstart, last, sum * 1e-3);
+            }
+            std::vector<int> by_end(todo);
+            std::sort(by_end.begin(), by_end.end(), [&](int x, int y) { return tm[2 * x + 1] > tm[2 * y + 1]; });
+            for (size_t i = 0; i < std::min<size_t>(12, by_end.size()); ++i) {
+                const int x = by_end[i];
+                fprintf(stderr, "[poa]   late set %d: cls %d maxlen %d reads %d work %.3g: %.0f -> %.0f ms\n", x, info[x].cls, info[x].maxlen, info[x].n, info[x].work,
+                        (tm[2 * x] - t0) * 1e-6, (tm[2 * x + 1] - t0) * 1e-6);
+            }
             fprintf(stderr, "[poa] attempt %d: wide %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
                     attempt, (long long)nA, wA, memA / 1e6, msA, todo.size() - nA, wB, memB / 1e6, ms);
         }

@@ -245,6 +245,21 @@ int svtk_inversion(svtk_ctx *ctx, int chrom, svtk_interval begin, svtk_interval 
  * imprecise position pos[s]; min_count / interval / range come from the ctx params.  Runs on the device. */
 int svtk_consensus_pos_batch(svtk_ctx *ctx, const int32_t *values, const int64_t *offsets, int32_t n_seg,
                              const int32_t *pos, int32_t *result);
+/* svtk_consensus_pos_batch on DEVICE arrays, allocating nothing.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  dev_values [n_values] / dev_offsets [n_seg + 1] / dev_pos [n_seg] / dev_result [n_seg] are device pointers the caller
+ * owns; the kernel is enqueued on the ctx stream and the call returns without waiting (svtk_sync, or synchronise the stream
+ * given to svtk_create, before reading dev_result).  The global sort scratch of segments longer than 8 192 values is a
+ * file-scope device array of 2 * SVTK_STATIC_MAX_VALUES ints (8 MiB, held by every GPU that loads the library until exit):
+ * n_values > SVTK_STATIC_MAX_VALUES fails with SVTK_ERR_ARG and launches nothing.  No cudaMalloc / cudaFree / allocating
+ * library call is made; the first call on a device looks the array's address up (cudaGetSymbolAddress) -- make that call
+ * outside a capture.  All calls on one GPU share the array: nothing in it has to start at zero (a segment reads back only what
+ * it wrote in the same launch), but calls that overlap on the GPU (other streams, other ctx) race.  A segment that does not
+ * lie inside [0, n_values] gets SVTK_STATIC_BAD_SEGMENT and touches no memory. */
+#define SVTK_STATIC_MAX_VALUES (1 << 20)
+#define SVTK_STATIC_BAD_SEGMENT (-2147483647 - 1)
+int svtk_consensus_pos_batch_static(svtk_ctx *ctx, const int32_t *dev_values, const int64_t *dev_offsets, int32_t n_seg, int64_t n_values,
+                                    const int32_t *dev_pos, int32_t *dev_result);
 /* the raw signature multiset of one window (what the reference collects before quicksort, refinement.c:54),
  * ascending.  *n_sig receives the full count even when it exceeds cap. */
 int svtk_window_signatures(svtk_ctx *ctx, int kind, int chrom, svtk_interval inter, int32_t *sig_out, int64_t cap, int64_t *n_sig);

@@ -82,7 +82,10 @@ EXPORTS = ["svtk_version", "svtk_last_error", "svtk_device_count", "svtk_create"
            "svtk_load_reads", "svtk_attach_reads_device", "svtk_refine_windows", "svtk_refine_windows_device", "svtk_measure_windows",
            "svtk_sync", "svtk_launch_count", "svtk_set_profiling", "svtk_get_timing", "svtk_index_reads", "svtk_measure_index", "svtk_deletion", "svtk_insertion", "svtk_inversion", "svtk_consensus_pos_batch",
            "svtk_window_signatures", "svtk_sliding_window_ins", "svtk_process_vcf", "svtk_poa_consensus",
-           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format", "svtk_load_bam_windows", "svtk_process_vcf_flags", "svtk_audit_shard"]
+           "svtk_load_bam", "svtk_bam_n_ref", "svtk_bam_ref", "svtk_copy_reads", "svtk_ins_sequences", "svtk_process_vcf_ins", "svtk_load_bam_refs", "svtk_audit_device", "svtk_process_vcf_region", "svtk_vcf_windows", "svtk_vcf_format", "svtk_load_bam_windows", "svtk_process_vcf_flags", "svtk_audit_shard", "svtk_consensus_pos_batch_static"]
+
+STATIC_MAX_VALUES = 1 << 20            # SVTK_STATIC_MAX_VALUES (include/svtk.h)
+STATIC_BAD_SEGMENT = -(1 << 31)        # SVTK_STATIC_BAD_SEGMENT
 
 _lib = None
 
@@ -117,6 +120,7 @@ def load_library():
     L.svtk_insertion.argtypes = [C.c_void_p, C.c_int, Interval, C.c_uint32, C.POINTER(C.c_uint32)]
     L.svtk_inversion.argtypes = [C.c_void_p, C.c_int, Interval, Interval, Interval, C.POINTER(Interval)]
     L.svtk_consensus_pos_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.svtk_consensus_pos_batch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]
     L.svtk_window_signatures.argtypes = [C.c_void_p, C.c_int, C.c_int, Interval, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
     L.svtk_sliding_window_ins.argtypes = [C.c_void_p, C.c_int, Interval, C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_char_p, C.c_size_t]
     L.svtk_process_vcf.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
@@ -387,6 +391,11 @@ class Auditor:
         out = np.empty(n, dtype=np.int32)
         _check(self.lib.svtk_consensus_pos_batch(self.ctx, values.ctypes.data, offsets.ctypes.data, n, pos.ctypes.data, out.ctypes.data))
         return out
+
+    def consensus_pos_batch_static(self, dev_values, dev_offsets, n_seg, n_values, dev_pos, dev_result):
+        """svtk_consensus_pos_batch_static: raw DEVICE pointers in and out, no allocation, asynchronous on the ctx stream
+        (call sync() before reading dev_result).  No counterpart in the reference (include/svtk.h)."""
+        _check(self.lib.svtk_consensus_pos_batch_static(self.ctx, dev_values, dev_offsets, int(n_seg), int(n_values), dev_pos, dev_result))
 
     def consensus_pos(self, locations, pos):
         """consensus_pos(locations, size, pos, ...) of refinement.c:41 with the ctx's min-count/interval/range."""

@@ -9,7 +9,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("SVTK_LIB_OUT") or os.path.join(HERE, "libsvtk_b200.so")
-SOURCES = ["svtk_kernels.cu", "svtk_index.cu", "svtk_poa.cu", "svtk_bam.cu", "svtk_ins.cu", "svtk_capi.cpp", "svtk_host.cpp"]
+SOURCES = ["svtk_kernels.cu", "svtk_index.cu", "svtk_poa.cu", "svtk_bam.cu", "svtk_ins.cu", "svtk_static.cu", "svtk_capi.cpp", "svtk_host.cpp"]
 HEADERS = ["svtk_device.cuh", "svtk_poa_core.cuh", "svtk_bgzf_core.cuh", "svtk_launch.h", "svtk_ctx.h", os.path.join("..", "..", "include", "svtk.h")]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-Wall", "-shared", "-cudart", "shared"]

@@ -44,7 +44,7 @@ __host__ __device__ inline PoaLayout poa_layout(const PoaCaps &c) {
     L.edge_id = o; o = a16(o + 4ll * c.edge_cap);
     L.edge_w = o; o = a16(o + 4ll * c.edge_cap);
     L.edge_idx = o; o = a16(o + 4ll * c.edge_cap);
-    L.rowmeta = o; o = a16(o + 16ll * c.node_cap);
+    L.rowmeta = o; o = a16(o + 48ll * c.node_cap);           // rowmeta, rowout, rowinfo
     L.cigar = o; o = a16(o + 8ll * c.cigar_cap);
     L.cells = o; o = a16(o + c.cell_bytes);
     L.total = (o + 255) & ~255ll;
@@ -108,6 +108,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 1 ? SVTK_POA_MINB : 1) k_poa_se
         s.edge_w = reinterpret_cast<int *>(blk + lay.edge_w);
         s.edge_idx = reinterpret_cast<int *>(blk + lay.edge_idx);
         s.rowmeta = reinterpret_cast<int4 *>(blk + lay.rowmeta);
+        s.rowout = s.rowmeta + N;
+        s.rowinfo = s.rowmeta + 2 * (long long)N;
         s.cigar = reinterpret_cast<int2 *>(blk + lay.cigar);
         s.cells = blk + lay.cells;
     }
@@ -203,26 +205,38 @@ static int plan_group(const std::vector<SetInfo> &info, const int *items, size_t
     W = std::min<long long>(W, (long long)n);
     double tot_work = 0;
     for (double x : cwork) tot_work += x;
-    std::vector<long long> nw(K), bytes(K);
-    long long mem = 0, used = 0;
-    for (int k = 0; k < K; ++k) {                              // share of the CTAs proportional to the class's work
+    // Workers per class.  A set's time is ~ proportional to its work and nothing shortens the heaviest set, so the batch cannot
+    // end before T = (heaviest set's work) x (sets the busiest worker runs one after the other).  A class therefore NEEDS
+    // ceil(its work / T) workers -- with fewer, its sets queue up behind each other and become the batch's tail (measured: a class
+    // of 479 sets of 2-6 s each on 209 workers ended at 10.9 s when the heaviest set of the batch took 5.1 s) -- and gains
+    // nothing from more than one worker per set.  Start from T = the heaviest set (x 0.75: estimates are rough, spare
+    // workers steal from the smaller classes anyway) and stretch T until the scratch fits the budget; what is left of the
+    // budget and of the W CTAs goes to the classes with the largest reads first.
+    std::vector<long long> nw(K), bytes(K), nk(K);
+    double wmax = 1.0;
+    for (size_t i = 0; i < n; ++i) wmax = std::max(wmax, info[items[i]].work);
+    long long min_mem = 0;
+    for (int k = 0; k < K; ++k) {
         bytes[k] = poa_layout(cls[k].caps).total;
         if (bytes[k] > budget) return fail(SVTK_ERR_ALLOC, "poa: one worker needs %lld bytes of scratch, budget %lld", bytes[k], budget);
-        const long long nk = cls[k].item_end - cls[k].item_begin;
-        nw[k] = std::max<long long>(1, std::min<long long>(nk, (long long)std::llround((double)W * cwork[k] / std::max(tot_work, 1.0))));
-        mem += nw[k] * bytes[k]; used += nw[k];
+        nk[k] = cls[k].item_end - cls[k].item_begin;
+        min_mem += bytes[k];
     }
-    for (int k = 0; k < K && used < W; ++k) {                  // slots the split left unused: largest reads first
-        const long long nk = cls[k].item_end - cls[k].item_begin;
-        const long long add = std::min<long long>(nk - nw[k], W - used);
+    if (min_mem > budget) return fail(SVTK_ERR_ALLOC, "poa: scratch for one worker per size class (%lld bytes) exceeds the budget %lld", min_mem, budget);
+    long long mem = 0, used = 0;
+    for (double T = 0.75 * wmax;; T *= 1.15) {
+        mem = 0; used = 0;
+        for (int k = 0; k < K; ++k) {
+            nw[k] = std::max<long long>(1, std::min<long long>(nk[k], (long long)std::ceil(cwork[k] / T)));
+            mem += nw[k] * bytes[k]; used += nw[k];
+        }
+        if (mem <= budget && used <= std::max<long long>(W, K)) break;
+        if (T > 4.0 * tot_work + 4.0 * wmax) break;            // every class is down to one worker: min_mem fits (checked above)
+    }
+    for (int k = 0; k < K && used < W; ++k) {                  // what is left: largest reads first
+        const long long room = bytes[k] > 0 ? (budget - mem) / bytes[k] : (nk[k] - nw[k]);
+        const long long add = std::max<long long>(0, std::min<long long>(std::min<long long>(nk[k] - nw[k], W - used), room));
         nw[k] += add; used += add; mem += add * bytes[k];
-    }
-    while (mem > budget) {                                     // trim the class holding the most scratch
-        int big = -1;
-        for (int k = 0; k < K; ++k) if (nw[k] > 1 && (big < 0 || nw[k] * bytes[k] > nw[big] * bytes[big])) big = k;
-        if (big < 0) return fail(SVTK_ERR_ALLOC, "poa: scratch for one worker per size class (%lld bytes) exceeds the budget %lld", mem, budget);
-        const long long cut = std::max<long long>(1, nw[big] / 10);
-        nw[big] -= cut; mem -= cut * bytes[big];
     }
     long long off = 0;
     for (int k = 0; k < K; ++k) {
@@ -270,7 +284,24 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         si.work = work * std::max(si.maxlen, 1);
         int cls = 0;
         while ((1 << cls) < std::max(si.maxlen, 1)) ++cls;
-        si.cls = cls;
+        si.cls = cls;                                         // octave of the longest read; refined below
+    }
+    // Size classes: a worker's scratch block is sized for the largest set of its class, and a block for 8 192-base reads is 4x
+    // what a set of 4 100-base reads needs, so octaves waste most of the memory of the heavy classes (and memory is what limits
+    // how many heavy sets run side by side).  Quarter octaves (block within ~1.4x of the need) unless the batch spans so many
+    // octaves that the class table would overflow.
+    {
+        int lo = 64, hi = 0;
+        for (int s = 0; s < ns; ++s) if (info[s].n > 0) { lo = std::min(lo, info[s].cls); hi = std::max(hi, info[s].cls); }
+        int sub = 4;
+        while (sub > 1 && (hi - lo + 1) * sub > 56) sub >>= 1;
+        if (const char *e = getenv("SVTK_POA_SUBCLASS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) sub = std::min(sub, v); }
+        if (sub > 1)
+            for (int s = 0; s < ns; ++s) {
+                SetInfo &si = info[s];
+                const double l2 = std::log2((double)std::max(si.maxlen, 1));
+                si.cls = (int)std::ceil(l2 * sub - 1e-9);
+            }
     }
     const long long cons_total = cons_off[ns] - cons_off[0];
     if (cons_off[0] != 0) return fail(SVTK_ERR_ARG, "cons_off must start at 0");
@@ -318,17 +349,30 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     int *d_cursors = (int *)((unsigned char *)c->poa_ctl.p + 64);
     PoaClass *d_classes = (PoaClass *)((unsigned char *)c->poa_ctl.p + 64 + 4 * MAXC);
     int *d_items = (int *)((unsigned char *)d_classes + a16(sizeof(PoaClass) * MAXC));
-    for (int i = 0; i < 3; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
+    for (int i = 0; i < 4; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
     if (!c->poa_side) {
         CU(cudaStreamCreateWithFlags(&c->poa_side, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&c->poa_side2, cudaStreamNonBlocking));
         // First use: run both instantiations once with no work.  k_poa_sets<1> needs a larger local-memory pool than
         // k_poa_sets<8>; growing that pool is a device-wide synchronisation, which would otherwise serialise the first
         // pair of launches (measured: 12.1 s instead of 6.7 s for the first batch).
+        // The three instantiations must be able to share an SM: a CTA is only placed on an SM whose shared-memory carve-out
+        // suits its kernel, and left to itself the driver sizes the carve-out for each kernel's own CTAs -- the warp-per-set
+        // CTAs then stay off every SM that holds a wide CTA (measured: they started only when wide CTAs retired).  Same
+        // carve-out for all three: 64 KB covers 16 warp-per-set CTAs.
+        int carve = -1;
+        if (const char *e = getenv("SVTK_POA_CARVEOUT")) carve = atoi(e);
+        if (carve >= 0) {
+            CU(cudaFuncSetAttribute(k_poa_sets<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+            CU(cudaFuncSetAttribute(k_poa_sets<4>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+            CU(cudaFuncSetAttribute(k_poa_sets<8>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        }
         CU(cudaMemsetAsync(d_classes, 0, sizeof(PoaClass) * MAXC, c->stream));
         PoaLaunch L0{};
         L0.classes = d_classes; L0.cursors = d_cursors; L0.scratch = (unsigned char *)c->poa_ctl.p;
         k_poa_sets<1><<<1, 32, 0, c->stream>>>(L0);
         k_poa_sets<8><<<1, 256, 0, c->stream>>>(L0);
+        k_poa_sets<4><<<1, 128, 0, c->stream>>>(L0);
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(c->stream));
     }
@@ -343,7 +387,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     double scale = 1.0, kernel_ms = 0.0;
     if (const char *e = getenv("SVTK_POA_SCALE")) { const double v = atof(e); if (v > 0.0) scale = v; }   // tests: start from a too-small block
     int wide_on = 1;
-    if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere
+    if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere, 1 = tiers <8> and <1> only
     uint64_t relaunched = 0, max_workers = 0;
     CU(cudaMemsetAsync(d_cells, 0, 64, c->stream));
     int sms = 148;
@@ -358,40 +402,53 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             if (info[x].work != info[y].work) return info[x].work > info[y].work;
             return x < y;
         });
-        // A set alone on a warp can outlast the rest of the batch.  The sets within 1/WIDE_GAIN of the heaviest one's work (reads
-        // beyond 2 kb, at most one per SM: a 256-thread CTA holds half an SM's registers) get a whole CTA each (k_poa_sets<8>),
-        // which finishes them ~WIDE_GAIN x sooner; everything else runs one warp per set, the shape that fills the SMs.
-        constexpr double WIDE_GAIN = 1.5;
-        std::vector<int> wide, rest;
+        // A set alone on a warp can outlast the rest of the batch: its reads are aligned one after the other, and only the row DP
+        // (about half of its time) gets faster with more threads.  Three tiers by estimated work, heaviest first:
+        //   k_poa_sets<8>  the sets within 1/1.5 of the heaviest one (reads beyond 2 kb, at most one per SM: a 256-thread CTA
+        //                  holds more than half an SM's registers) -- done in ~0.45 of their single-warp time;
+        //   k_poa_sets<4>  the sets that would still outlast those on a single warp (work above 0.44 of the heaviest; at most two
+        //                  per SM) -- done in ~0.56 of their single-warp time at half the registers;
+        //   k_poa_sets<1>  everything else, one warp per set: the shape that fills the SMs.
+        // Measured on 4 000 C4-like sets: tiers 8 / 1 only ended at 7.1 s with the <8> launch done at 5.1 s (profiles/r02n..r02q).
+        constexpr double WIDE_GAIN = 1.5, MID_FRAC = 0.44;
+        std::vector<int> wide, mid, rest;
         {
             double wmax = 0;
             for (int x : todo) wmax = std::max(wmax, info[x].work);
             std::vector<int> by_work(todo);
             std::sort(by_work.begin(), by_work.end(), [&](int x, int y) { return info[x].work != info[y].work ? info[x].work > info[y].work : x < y; });
-            std::vector<char> is_wide(ns, 0);
+            std::vector<char> tier(ns, 0);
             for (int x : by_work) {
-                if (!wide_on || (int)wide.size() >= sms || info[x].maxlen <= 2048 || info[x].work * WIDE_GAIN < wmax) break;
-                wide.push_back(x); is_wide[x] = 1;
+                if (wide_on < 1 || info[x].maxlen <= 2048) break;
+                if ((int)wide.size() < sms && info[x].work * WIDE_GAIN >= wmax) { wide.push_back(x); tier[x] = 2; }
+                else if (wide_on >= 2 && (int)mid.size() < 2 * sms && info[x].work >= MID_FRAC * wmax) { mid.push_back(x); tier[x] = 1; }
+                else break;
             }
-            for (int x : todo) if (!is_wide[x]) rest.push_back(x);
-            std::sort(wide.begin(), wide.end(), [&](int x, int y) {
+            for (int x : todo) if (!tier[x]) rest.push_back(x);
+            auto by_class = [&](int x, int y) {
                 if (info[x].cls != info[y].cls) return info[x].cls > info[y].cls;
                 if (info[x].work != info[y].work) return info[x].work > info[y].work;
                 return x < y;
-            });
+            };
+            std::sort(wide.begin(), wide.end(), by_class);
+            std::sort(mid.begin(), mid.end(), by_class);
             todo = wide;
+            todo.insert(todo.end(), mid.begin(), mid.end());
             todo.insert(todo.end(), rest.begin(), rest.end());
         }
-        const size_t nA = wide.size();
-        std::vector<PoaClass> clsA, clsB;
-        long long wA = 0, wB = 0, memA = 0, memB = 0;
-        if (int rc = plan_group(info, todo.data(), nA, 0, scale, (long long)nA, (long long)(0.6 * (double)budget), clsA, wA, memA)) return rc;
-        if (int rc = plan_group(info, todo.data() + nA, todo.size() - nA, (int)nA, scale, (long long)sms * 32, budget - memA, clsB, wB, memB)) return rc;
-        if (clsA.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
-        for (PoaClass &pc : clsB) pc.scratch_off += memA;
+        const size_t nA = wide.size(), nM = mid.size();
+        std::vector<PoaClass> clsA, clsM, clsB;
+        long long wA = 0, wM = 0, wB = 0, memA = 0, memM = 0, memB = 0;
+        if (int rc = plan_group(info, todo.data(), nA, 0, scale, (long long)nA, (long long)(0.45 * (double)budget), clsA, wA, memA)) return rc;
+        if (int rc = plan_group(info, todo.data() + nA, nM, (int)nA, scale, (long long)nM, (long long)(0.7 * (double)budget) - memA, clsM, wM, memM)) return rc;
+        if (int rc = plan_group(info, todo.data() + nA + nM, todo.size() - nA - nM, (int)(nA + nM), scale, (long long)sms * 32, budget - memA - memM, clsB, wB, memB)) return rc;
+        if (clsA.size() + clsM.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
+        for (PoaClass &pc : clsM) pc.scratch_off += memA;
+        for (PoaClass &pc : clsB) pc.scratch_off += memA + memM;
         std::vector<PoaClass> cls(clsA);
+        cls.insert(cls.end(), clsM.begin(), clsM.end());
         cls.insert(cls.end(), clsB.begin(), clsB.end());
-        if (int rc = c->poa_scratch.reserve((size_t)(memA + memB))) return rc;
+        if (int rc = c->poa_scratch.reserve((size_t)(memA + memM + memB))) return rc;
         CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(d_classes, cls.data(), sizeof(PoaClass) * cls.size(), cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemsetAsync(d_cursors, 0, 4 * MAXC, c->stream));
@@ -407,7 +464,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             L.times = (unsigned long long *)c->tmp_c.p;
         }
         CU(cudaEventRecord(c->poa_ev[0], c->stream));
-        if (wA > 0) {                                          // side stream: both launches are resident together
+        if (wA > 0) {                                          // side streams: the three launches are resident together
             CU(cudaStreamWaitEvent(c->poa_side, c->poa_ev[0], 0));
             PoaLaunch LA = L;
             LA.n_classes = (int)clsA.size(); LA.classes = d_classes; LA.cursors = d_cursors;
@@ -416,14 +473,24 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             CU(cudaEventRecord(c->poa_ev[2], c->poa_side));
             c->launches += 1;
         }
+        if (wM > 0) {
+            CU(cudaStreamWaitEvent(c->poa_side2, c->poa_ev[0], 0));
+            PoaLaunch LM = L;
+            LM.n_classes = (int)clsM.size(); LM.classes = d_classes + clsA.size(); LM.cursors = d_cursors + clsA.size();
+            k_poa_sets<4><<<(unsigned)wM, 128, 0, c->poa_side2>>>(LM);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(c->poa_ev[3], c->poa_side2));
+            c->launches += 1;
+        }
         if (wB > 0) {
             PoaLaunch LB = L;
-            LB.n_classes = (int)clsB.size(); LB.classes = d_classes + clsA.size(); LB.cursors = d_cursors + clsA.size();
+            LB.n_classes = (int)clsB.size(); LB.classes = d_classes + clsA.size() + clsM.size(); LB.cursors = d_cursors + clsA.size() + clsM.size();
             k_poa_sets<1><<<(unsigned)wB, 32, 0, c->stream>>>(LB);
             CU(cudaGetLastError());
             c->launches += 1;
         }
         if (wA > 0) CU(cudaStreamWaitEvent(c->stream, c->poa_ev[2], 0));
+        if (wM > 0) CU(cudaStreamWaitEvent(c->stream, c->poa_ev[3], 0));
         CU(cudaEventRecord(c->poa_ev[1], c->stream));
         CU(cudaMemcpyAsync(h_status.data(), d_status, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));                  // also: todo / cls were read by the copies above
@@ -431,8 +498,9 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
         kernel_ms += ms;
         if (getenv("SVTK_POA_DEBUG")) {
-            float msA = 0.f;
+            float msA = 0.f, msM = 0.f;
             if (wA > 0) cudaEventElapsedTime(&msA, c->poa_ev[0], c->poa_ev[2]);
+            if (wM > 0) cudaEventElapsedTime(&msM, c->poa_ev[0], c->poa_ev[3]);
             std::vector<unsigned long long> tm(2 * (size_t)ns);
             cudaMemcpy(tm.data(), c->tmp_c.p, 16 * (size_t)ns, cudaMemcpyDeviceToHost);
             unsigned long long t0 = ~0ull;
@@ -445,7 +513,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                     first = std::min(first, a); last = std::max(last, b); lstart = std::max(lstart, a); sum += b - a;
                 }
                 fprintf(stderr, "[poa]   class %zu %s cls %d: %d sets, %d workers, %.1f MB/worker; first start %.0f ms, last start %.0f ms, last end %.0f ms, busy %.1f worker-s\n",
-                        k, k < clsA.size() ? "wide" : "warp", info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
+                        k, k < clsA.size() ? "wide8" : (k < clsA.size() + clsM.size() ? "wide4" : "warp"), info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
                         cls[k].worker_end - cls[k].worker_begin, poa_layout(cls[k].caps).total / 1e6, first, lstart, last, sum * 1e-3);
             }
             std::vector<int> by_end(todo);
@@ -455,10 +523,10 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                 fprintf(stderr, "[poa]   late set %d: cls %d maxlen %d reads %d work %.3g: %.0f -> %.0f ms\n", x, info[x].cls, info[x].maxlen, info[x].n, info[x].work,
                         (tm[2 * x] - t0) * 1e-6, (tm[2 * x + 1] - t0) * 1e-6);
             }
-            fprintf(stderr, "[poa] attempt %d: wide %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
-                    attempt, (long long)nA, wA, memA / 1e6, msA, todo.size() - nA, wB, memB / 1e6, ms);
+            fprintf(stderr, "[poa] attempt %d: <8> %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; <4> %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
+                    attempt, (long long)nA, wA, memA / 1e6, msA, (long long)nM, wM, memM / 1e6, msM, todo.size() - nA - nM, wB, memB / 1e6, ms);
         }
-        max_workers = std::max<uint64_t>(max_workers, (uint64_t)(wA + wB));
+        max_workers = std::max<uint64_t>(max_workers, (uint64_t)(wA + wM + wB));
         std::vector<int> again;
         for (int s : todo) {
             const int st = h_status[s];

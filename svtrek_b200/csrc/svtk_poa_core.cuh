@@ -36,6 +36,8 @@ static inline long long poa_shfl_ll(long long v, int) { return v; }
 static inline int poa_shfl_up(int v, int) { return v; }
 static inline int poa_max_all(int v) { return v; }
 static inline int poa_min_all(int v) { return v; }
+static inline bool poa_any(bool v) { return v; }
+static inline void poa_touch(const void *) {}
 #else
 #define PD __device__ __forceinline__
 #define POA_NL 32
@@ -46,6 +48,9 @@ PD long long poa_shfl_ll(long long v, int src) { return __shfl_sync(0xffffffffu,
 PD int poa_shfl_up(int v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
 PD int poa_max_all(int v) { return __reduce_max_sync(0xffffffffu, v); }
 PD int poa_min_all(int v) { return __reduce_min_sync(0xffffffffu, v); }
+PD bool poa_any(bool v) { return __any_sync(0xffffffffu, v) != 0; }
+// request a line into L1 without consuming it (the value is never read, so nothing waits for it)
+PD void poa_touch(const void *p) { unsigned v; asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(v) : "l"(p)); (void)v; }
 #endif
 #if defined(POA_HOSTSIM)
 static inline long long poa_clock() { return 0; }
@@ -98,6 +103,8 @@ struct PoaState {
     // what the row DP streams, rebuilt by every topological sort: per INDEX {node id, base | in-degree << 8, first
     // in-edge slot, max_remain}, and per in-edge slot the predecessor's index
     int4 *rowmeta;
+    int4 *rowinfo;                                             // per INDEX {dp_beg, dp_end, row_off low, row_off high}: one load for the backtrack
+    int4 *rowout;                                              // per INDEX {out-degree, first out-edge slot, target of out-edge 0, of out-edge 1}
     int *edge_idx;
     // one alignment
     int *dp_beg, *dp_end;
@@ -262,6 +269,8 @@ PD void poa_topological_sort(PoaState &sh) {
         m.x = id; m.y = (int)s.base[id] | (pn << 8); m.z = po; m.w = s.remain[id];
         s.rowmeta[i] = m;
         for (int k = 0; k < pn; ++k) s.edge_idx[po + k] = s.id2idx[s.edge_id[po + k]];
+        const int on = s.out_n[id], oo = s.out_off[id];
+        s.rowout[i] = make_int4(on, oo, on > 0 ? s.edge_id[oo] : -1, on > 1 ? s.edge_id[oo + 1] : -1);
     }
     poa_bar<NW>();
 }
@@ -280,50 +289,58 @@ PD void poa_add_first(PoaState &s, const uint8_t *q, int qlen) {
 }
 
 // abpoa_add_subgraph_alignment (abpoa_graph.c:688) with beg = SRC, end = SINK, inc_both_ends = 1, all weights 1.
-// The cigar is in backtrack order (last op first); ops are consumed from the back.  lane 0
-PD void poa_add_alignment(PoaState &s, const uint8_t *q, int qlen) {
+// The cigar is in backtrack order (last op first); ops are consumed from the back.
+// All lanes of the first warp enter, lane 0 does the work (one thread chasing pointers: every op reads what the previous one
+// wrote).  Measured, not kept: the other lanes requesting the node and edge-list lines of the next 32 ops into L1 ahead of lane 0
+// (the cigar says which) -- fusion time unchanged (+5 %): the chain is not waiting on those lines.
+PD void poa_add_alignment(PoaState &s, const uint8_t *q, int qlen, int lane) {
     if (s.n_cigar == 0) return;                                // abpoa_graph.c:706-709
     int query_id = -1, last_new = 0, last_id = SRC;
-    for (int c = s.n_cigar - 1; c >= 0; --c) {
-        const int op = s.cigar[c].x, arg = s.cigar[c].y;
-        if (op == CG_MATCH) {
-            const int node_id = arg;
-            ++query_id;
-            const uint8_t b = q[query_id];
-            if (s.base[node_id] != b) {                        // mismatch: reuse an aligned node with this base, else a new one
-                int aligned = -1;
-                for (int i = 0; i < s.aln_n[node_id]; ++i) {
-                    const int a = s.aln_id[node_id * ALN_MAX + i];
-                    if (s.base[a] == b) { aligned = a; break; }
-                }
-                if (aligned != -1) {
-                    poa_add_edge(s, last_id, aligned, 1 - last_new, 1);
-                    last_id = aligned; last_new = 0;
+    for (int c0 = s.n_cigar - 1; c0 >= 0; c0 -= POA_NL) {
+        bool stop = false;
+        if (lane == 0)
+        for (int c = c0; c > c0 - POA_NL && c >= 0; --c) {
+            const int op = s.cigar[c].x, arg = s.cigar[c].y;
+            if (op == CG_MATCH) {
+                const int node_id = arg;
+                ++query_id;
+                const uint8_t b = q[query_id];
+                if (s.base[node_id] != b) {                    // mismatch: reuse an aligned node with this base, else a new one
+                    int aligned = -1;
+                    for (int i = 0; i < s.aln_n[node_id]; ++i) {
+                        const int a = s.aln_id[node_id * ALN_MAX + i];
+                        if (s.base[a] == b) { aligned = a; break; }
+                    }
+                    if (aligned != -1) {
+                        poa_add_edge(s, last_id, aligned, 1 - last_new, 1);
+                        last_id = aligned; last_new = 0;
+                    } else {
+                        const int nid = poa_add_node(s, b);
+                        if (nid < 0) { stop = true; break; }
+                        poa_add_edge(s, last_id, nid, 0, 1);
+                        last_id = nid; last_new = 1;
+                        poa_add_aligned(s, node_id, nid);
+                    }
                 } else {
-                    const int nid = poa_add_node(s, b);
-                    if (nid < 0) return;
+                    poa_add_edge(s, last_id, node_id, 1 - last_new, 1);
+                    last_id = node_id; last_new = 0;
+                }
+            } else if (op == CG_INS) {
+                for (int l = 0; l < arg; ++l) {
+                    ++query_id;
+                    const int nid = poa_add_node(s, q[query_id]);
+                    if (nid < 0) { stop = true; break; }
                     poa_add_edge(s, last_id, nid, 0, 1);
                     last_id = nid; last_new = 1;
-                    poa_add_aligned(s, node_id, nid);
+                    if (s.status) { stop = true; break; }
                 }
-            } else {
-                poa_add_edge(s, last_id, node_id, 1 - last_new, 1);
-                last_id = node_id; last_new = 0;
-            }
-        } else if (op == CG_INS) {
-            for (int l = 0; l < arg; ++l) {
-                ++query_id;
-                const int nid = poa_add_node(s, q[query_id]);
-                if (nid < 0) return;
-                poa_add_edge(s, last_id, nid, 0, 1);
-                last_id = nid; last_new = 1;
-                if (s.status) return;
-            }
-        }                                                      // CG_DEL: nothing
-        if (s.status) return;
+            }                                                  // CG_DEL: nothing
+            if (stop || s.status) { stop = true; break; }
+        }
+        if (poa_any(stop)) return;                             // out of nodes / edges: the caller sees s.status (lane 0's copy)
     }
     (void)qlen;
-    poa_add_edge(s, last_id, SINK, 1 - last_new, 1);
+    if (lane == 0) poa_add_edge(s, last_id, SINK, 1 - last_new, 1);
 }
 
 // ----------------------------------------------------------------------------------------------- alignment
@@ -340,81 +357,112 @@ PD void poa_push_cigar(PoaState &s, int op, int arg) {
     s.cigar[s.n_cigar].x = op; s.cigar[s.n_cigar].y = arg; ++s.n_cigar;
 }
 
-// simd_abpoa_cg_backtrack (abpoa_align_simd.c:309-458) with put_gap_on_right = put_gap_at_end = 0.  lane 0
+// One DP row as the backtrack sees it: band and cells from ONE 16-byte load (rowinfo).
+template <typename SC>
+struct PoaRow {
+    int b, e, w;
+    const SC *c;
+};
+template <typename SC>
+PD PoaRow<SC> poa_row(const PoaState &s, int i) {
+    const int4 r = s.rowinfo[i];
+    PoaRow<SC> v;
+    v.b = r.x; v.e = r.y; v.w = r.y - r.x + 1;
+    v.c = reinterpret_cast<const SC *>(s.cells) + (((long long)r.w << 32) | (long long)(unsigned)r.z) * 5;
+    return v;
+}
+template <typename SC>
+PD int poa_rcell(const PoaRow<SC> &v, int plane, int j, int inf_min) {
+    if (j < v.b || j > v.e) return inf_min;
+    return (int)v.c[(long long)plane * v.w + (j - v.b)];
+}
+
+// simd_abpoa_cg_backtrack (abpoa_align_simd.c:309-458) with put_gap_on_right = put_gap_at_end = 0.  lane 0.
+// One step is a chain of dependent loads; it is kept short by reading what the topological sort and the DP left per INDEX
+// (rowmeta: node id, base, in-edges; edge_idx: the predecessors' indices; rowinfo: band and cells) instead of going through
+// the node arrays (idx2id -> in_off -> edge_id -> id2idx -> dp_beg / dp_end / row_off -> cell).
 template <typename SC>
 PD void poa_backtrack(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
     int i = s.best_i, j = s.best_j, cur_op = OP_ALL;
     s.n_cigar = 0;
     if (j < qlen) poa_push_cigar(s, CG_INS, qlen - j);
     int guard = s.node_n + qlen + 8;
+    int4 meta = s.rowmeta[i];
+    PoaRow<SC> cur = poa_row<SC>(s, i);
     while (i > 0 && j > 0) {
         if (--guard < 0 || s.status) { if (!s.status) s.status = POA_ERR_BACKTRACK; return; }
-        const int id = s.idx2id[i];
-        const int sc = poa_score(s.base[id], q[j - 1]);
-        const int pn = s.in_n[id], po = s.in_off[id];
-        const int Hij = poa_cell<SC>(s, i, 0, j, inf_min);
+        const int id = meta.x;
+        const int sc = poa_score(meta.y & 0xff, q[j - 1]);
+        const int pn = meta.y >> 8, po = meta.z;
+        const int Hij = poa_rcell<SC>(cur, 0, j, inf_min);
         bool hit = false;
         if (cur_op & OP_M) {
             for (int k = 0; k < pn; ++k) {
-                const int p = s.id2idx[s.edge_id[po + k]];
-                if (j - 1 < s.dp_beg[p] || j - 1 > s.dp_end[p]) continue;
-                if (poa_cell<SC>(s, p, 0, j - 1, inf_min) + sc == Hij) {
+                const int p = s.edge_idx[po + k];
+                const PoaRow<SC> pv = poa_row<SC>(s, p);
+                const int4 pm = s.rowmeta[p];
+                if (j - 1 < pv.b || j - 1 > pv.e) continue;
+                if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
                     poa_push_cigar(s, CG_MATCH, id);
-                    i = p; --j; hit = true; cur_op = OP_ALL;
+                    i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
                     break;
                 }
             }
         }
         if (!hit && (cur_op & OP_E)) {
             for (int k = 0; k < pn && !hit; ++k) {
-                const int p = s.id2idx[s.edge_id[po + k]];
-                if (j < s.dp_beg[p] || j > s.dp_end[p]) continue;
-                const int pH = poa_cell<SC>(s, p, 0, j, inf_min);
+                const int p = s.edge_idx[po + k];
+                const PoaRow<SC> pv = poa_row<SC>(s, p);
+                const int4 pm = s.rowmeta[p];
+                if (j < pv.b || j > pv.e) continue;
+                const int pH = poa_rcell<SC>(pv, 0, j, inf_min);
                 if (cur_op & OP_E1) {
-                    const int pe1 = poa_cell<SC>(s, p, 1, j, inf_min);
-                    const bool ok = (cur_op & OP_M) ? (Hij == pe1) : (poa_cell<SC>(s, i, 1, j, inf_min) == pe1 - GAP_E1);
+                    const int pe1 = poa_rcell<SC>(pv, 1, j, inf_min);
+                    const bool ok = (cur_op & OP_M) ? (Hij == pe1) : (poa_rcell<SC>(cur, 1, j, inf_min) == pe1 - GAP_E1);
                     if (ok) {
                         cur_op = (pH - GAP_OE1 == pe1) ? (OP_M | OP_F) : OP_E1;
-                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p;
+                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
                         break;
                     }
                 }
                 if (cur_op & OP_E2) {
-                    const int pe2 = poa_cell<SC>(s, p, 2, j, inf_min);
-                    const bool ok = (cur_op & OP_M) ? (Hij == pe2) : (poa_cell<SC>(s, i, 2, j, inf_min) == pe2 - GAP_E2);
+                    const int pe2 = poa_rcell<SC>(pv, 2, j, inf_min);
+                    const bool ok = (cur_op & OP_M) ? (Hij == pe2) : (poa_rcell<SC>(cur, 2, j, inf_min) == pe2 - GAP_E2);
                     if (ok) {
                         cur_op = (pH - GAP_OE2 == pe2) ? (OP_M | OP_F) : OP_E2;
-                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p;
+                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
                         break;
                     }
                 }
             }
         }
         if (!hit && (cur_op & OP_F)) {
-            const int Hl = poa_cell<SC>(s, i, 0, j - 1, inf_min);
+            const int Hl = poa_rcell<SC>(cur, 0, j - 1, inf_min);
             if (cur_op & OP_F1) {
-                const int f1 = poa_cell<SC>(s, i, 3, j, inf_min);
+                const int f1 = poa_rcell<SC>(cur, 3, j, inf_min);
                 if (!(cur_op & OP_M) || Hij == f1) {
                     if (Hl - GAP_OE1 == f1) { cur_op = OP_M | OP_E; hit = true; }
-                    else if (poa_cell<SC>(s, i, 3, j - 1, inf_min) - GAP_E1 == f1) { cur_op = OP_F1; hit = true; }
+                    else if (poa_rcell<SC>(cur, 3, j - 1, inf_min) - GAP_E1 == f1) { cur_op = OP_F1; hit = true; }
                 }
             }
             if (!hit && (cur_op & OP_F2)) {
-                const int f2 = poa_cell<SC>(s, i, 4, j, inf_min);
+                const int f2 = poa_rcell<SC>(cur, 4, j, inf_min);
                 if (!(cur_op & OP_M) || Hij == f2) {
                     if (Hl - GAP_OE2 == f2) { cur_op = OP_M | OP_E; hit = true; }
-                    else if (poa_cell<SC>(s, i, 4, j - 1, inf_min) - GAP_E2 == f2) { cur_op = OP_F2; hit = true; }
+                    else if (poa_rcell<SC>(cur, 4, j - 1, inf_min) - GAP_E2 == f2) { cur_op = OP_F2; hit = true; }
                 }
             }
             if (hit) { poa_push_cigar(s, CG_INS, 1); --j; }
         }
         if (!hit && (cur_op & OP_M)) {
             for (int k = 0; k < pn; ++k) {
-                const int p = s.id2idx[s.edge_id[po + k]];
-                if (j - 1 < s.dp_beg[p] || j - 1 > s.dp_end[p]) continue;
-                if (poa_cell<SC>(s, p, 0, j - 1, inf_min) + sc == Hij) {
+                const int p = s.edge_idx[po + k];
+                const PoaRow<SC> pv = poa_row<SC>(s, p);
+                const int4 pm = s.rowmeta[p];
+                if (j - 1 < pv.b || j - 1 > pv.e) continue;
+                if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
                     poa_push_cigar(s, CG_MATCH, id);
-                    i = p; --j; hit = true; cur_op = OP_ALL;
+                    i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
                     break;
                 }
             }
@@ -446,7 +494,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     {
         const int w0 = end0 + 1;
         if (w0 > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return 0; }
-        if (lane == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; }
+        if (lane == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; g.rowinfo[0] = make_int4(0, end0, 0, 0); }
         for (int j = lane; j <= end0; j += POA_NL) {
             int h, e1 = inf_min, e2 = inf_min, f1, f2;
             if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
@@ -464,7 +512,14 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     // memory round trip, not one per 32 columns.
     int lb = 0, le = end0;                                     // band of row i-1
     long long lo = 0;                                          // its first cell
+    // The band hints (max_pos_left / max_pos_right of a node) are written by a row's predecessors and read when the row
+    // starts; through memory that is a store -> load round trip at the head of every row and a chain of three dependent loads
+    // (out-degree -> edge -> the target's hint) at its tail.  Instead: the next row's hints are requested one row ahead, as every
+    // predecessor but the current row has left them, and the current row's own share is added in registers; the current
+    // row's out-edge targets (rowout, lane k = edge k) and their hints are requested when the row starts.
     int4 meta = g.rowmeta[1], meta_n = g.rowmeta[imin(2, n - 1)];
+    int4 om = g.rowout[1];
+    int ml = g.max_left[meta.x], mr = g.max_right[meta.x];
     int pi[PRED_REG];
 #pragma unroll
     for (int k = 0; k < PRED_REG; ++k) pi[k] = k < (meta.y >> 8) ? g.edge_idx[meta.z + k] : -1;
@@ -472,10 +527,16 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
         const int id = meta.x, nb = meta.y & 0xff, pn = meta.y >> 8, po = meta.z;
         const int rt = qlen - meta.w;                          // remain[SINK] == -1 (abpoa_align.h:34-35)
         const int4 meta_nn = g.rowmeta[imin(i + 2, n - 1)];    // in flight during this row
+        const int4 om_n = g.rowout[imin(i + 1, n - 1)];
+        int ml_n = g.max_left[meta_n.x], mr_n = g.max_right[meta_n.x];
         int pi_n[PRED_REG];
 #pragma unroll
         for (int k = 0; k < PRED_REG; ++k) pi_n[k] = k < (meta_n.y >> 8) ? g.edge_idx[meta_n.z + k] : -1;
-        const int ml = g.max_left[id], mr = g.max_right[id];
+        int to = -1, tml = 0, tmr = 0;                         // this lane's out-edge target and its hints so far
+        if (lane < om.x) {
+            to = lane == 0 ? om.z : (lane == 1 ? om.w : g.edge_id[om.y + lane]);
+            tml = g.max_left[to]; tmr = g.max_right[to];
+        }
         // the first PRED_REG predecessors' bands and row pointers stay in registers for the whole row (an empty slot
         // has an empty band, so it never contributes); nodes with more in-edges take the generic loop for the rest
         int pbv[PRED_REG], pev[PRED_REG];
@@ -498,7 +559,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
         if (wd <= 0 || pn <= 0) { if (lane == 0) s.status = POA_ERR_BAND; poa_sync(); return top; }
         if (top + wd > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return top; }
         SC *row = cells + top * 5;
-        if (lane == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; }
+        if (lane == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; g.rowinfo[i] = make_int4(beg, end, (int)(unsigned)(top & 0xffffffffll), (int)(top >> 32)); }
 
         int carry_h = inf_min;                                 // Hme of the column left of the chunk
         int carry_f1 = inf_min - GAP_OE1, carry_f2 = inf_min - GAP_OE2;
@@ -513,8 +574,8 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                 int m = inf_min, e1in = inf_min, e2in = inf_min, sc = 0;
                 if (valid) {
 #pragma unroll
-                    for (int k = 0; k < PRED_REG; ++k) {       // max over predecessors is order independent
-                        const int pb = pbv[k], pe = pev[k], pw = pe - pb + 1;
+                    for (int k = 0; k < PRED_REG; ++k) {       // max over predecessors is order independent; empty slots stay predicated
+                        const int pb = pbv[k], pe = pev[k], pw = pe - pb + 1;   // (a uniform branch around them: +8 % DP time, the loads stop overlapping)
                         const SC *pr = prv[k];
                         if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
                         if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
@@ -531,16 +592,15 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                 hmev[u] = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
                 e1v[u] = e1in; e2v[u] = e2in;
             }
-            // pass 2: F[j] = max(Hme[j-1] - oe, F[j-1] - e) as a prefix max of (Hme[k-1] - oe + k*e) across the lanes (:1052-1059)
+            // pass 2: F[j] = max(Hme[j-1] - oe, F[j-1] - e) as a prefix max of (Hme[k-1] - oe + k*e) across the lanes (:1052-1059).
+            // 2a: the prefix maxima inside each 32-column chunk -- they need only Hme, so the chunks' shuffle chains are
+            // independent and overlap; 2b: the running F of the columns to the left joins chunk by chunk (one shuffle each).
+            int g1v[ROW_CB], g2v[ROW_CB];
 #pragma unroll
             for (int u = 0; u < ROW_CB; ++u) {
-                const int c0 = cb + u * POA_NL;
-                if (c0 > end) break;
-                const int j = c0 + lane;
-                const bool valid = j <= end;
-                const int hme = hmev[u];
-                int left = poa_shfl_up(hme, 1);
-                if (lane == 0) left = carry_h;
+                const int prev_last = u == 0 ? carry_h : poa_shfl(hmev[u > 0 ? u - 1 : 0], POA_NL - 1);   // all lanes shuffle
+                int left = poa_shfl_up(hmev[u], 1);
+                if (lane == 0) left = prev_last;
                 int g1 = left - GAP_OE1 + lane * GAP_E1, g2 = left - GAP_OE2 + lane * GAP_E2;
 #if POA_NL > 1
 #pragma unroll
@@ -549,8 +609,17 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                     if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
                 }
 #endif
-                const int f1 = imax(g1 - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
-                const int f2 = imax(g2 - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
+                g1v[u] = g1; g2v[u] = g2;
+            }
+#pragma unroll
+            for (int u = 0; u < ROW_CB; ++u) {
+                const int c0 = cb + u * POA_NL;
+                if (c0 > end) break;
+                const int j = c0 + lane;
+                const bool valid = j <= end;
+                const int hme = hmev[u];
+                const int f1 = imax(g1v[u] - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
+                const int f2 = imax(g2v[u] - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
                 const int h = imax(hme, imax(f1, f2));
                 if (valid) {
                     const int x = j - beg;
@@ -573,11 +642,19 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             right_i = poa_max_all(bv == vmax ? br : -1);
             if (vmax > inf_min) left_i = poa_min_all(bv == vmax ? bl : 0x7fffffff);
         }
-        for (int k = lane; k < g.out_n[id]; k += POA_NL) {
-            const int o = g.edge_id[g.out_off[id] + k];
+        bool feeds_next = to == meta_n.x;                      // (to == -1 never matches a node id)
+        if (to >= 0) {
+            if (right_i + 1 > tmr) g.max_right[to] = right_i + 1;
+            if (left_i + 1 < tml) g.max_left[to] = left_i + 1;
+        }
+        for (int k = lane + POA_NL; k < om.x; k += POA_NL) {   // more out-edges than lanes
+            const int o = g.edge_id[om.y + k];
             if (right_i + 1 > g.max_right[o]) g.max_right[o] = right_i + 1;
             if (left_i + 1 < g.max_left[o]) g.max_left[o] = left_i + 1;
+            feeds_next |= o == meta_n.x;
         }
+        if (poa_any(feeds_next)) { mr_n = imax(mr_n, right_i + 1); ml_n = imin(ml_n, left_i + 1); }
+        ml = ml_n; mr = mr_n; om = om_n;
         lb = beg; le = end; lo = top;
         top += wd;
         meta = meta_n; meta_n = meta_nn;
@@ -632,7 +709,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
     {
         const int w0 = end0 + 1;
         if (w0 > cell_cap) { if (t == 0) s.status = POA_ERR_CELLS; __syncthreads(); return 0; }
-        if (t == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; }
+        if (t == 0) { g.dp_beg[0] = 0; g.dp_end[0] = end0; g.row_off[0] = 0; g.rowinfo[0] = make_int4(0, end0, 0, 0); }
         for (int j = t; j <= end0; j += NT) {
             int h, e1 = inf_min, e2 = inf_min, f1, f2;
             if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
@@ -677,7 +754,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
         if (wd <= 0 || pn <= 0) { if (t == 0) s.status = POA_ERR_BAND; __syncthreads(); return top; }
         if (top + wd > cell_cap) { if (t == 0) s.status = POA_ERR_CELLS; __syncthreads(); return top; }
         SC *row = cells + top * 5;
-        if (t == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; }
+        if (t == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; g.rowinfo[i] = make_int4(beg, end, (int)(unsigned)(top & 0xffffffffll), (int)(top >> 32)); }
 
         int carry_h = inf_min;                                 // Hme of the column left of the block
         int run1 = IMIN, run2 = IMIN;                          // max of g1 / g2 over all columns left of the block
@@ -911,14 +988,13 @@ PD int poa_run_set(PoaState &s, XCH &xch, long long r0, long long r1, const long
                 }
                 tr->ops_hash[r] = h; tr->n_ops[r] = nops;
             }
-            const long long t2 = poa_clock();
-            if (rows > 2) {
-                PoaState g = s;
-                poa_add_alignment(g, q, qlen);
-                s.node_n = g.node_n; s.edge_top = g.edge_top; s.status = g.status;
-            }
-            s.t_phase[2] += poa_clock() - t2;
             if (tr && tr->best_score) { tr->best_score[r] = rows > 2 ? s.best_score : 0; tr->cells[r] = cells; }
+        }
+        if (lane < POA_NL && rows > 2 && !s.status) {          // the first warp: lane 0 fuses, the others prefetch for it
+            const long long t2 = poa_clock();
+            PoaState g = s;
+            poa_add_alignment(g, q, qlen, lane);
+            if (lane == 0) { s.node_n = g.node_n; s.edge_top = g.edge_top; s.status = g.status; s.t_phase[2] += poa_clock() - t2; }
         }
         poa_bar<NW>();
         if (s.status) break;

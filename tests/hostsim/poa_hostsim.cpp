@@ -7,6 +7,7 @@
 #include <vector>
 struct int2 { int x, y; };
 struct int4 { int x, y, z, w; };
+static inline int4 make_int4(int x, int y, int z, int w) { int4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
 #include "../../svtrek_b200/csrc/svtk_poa_core.cuh"
 
 using namespace svtk_poa;
@@ -30,7 +31,7 @@ extern "C" int hostsim_poa(int n, const long long *off, const uint8_t *bases, ui
     std::vector<long long> roff(s.node_cap);
     std::vector<unsigned char> cellbuf((size_t)s.cell_bytes);
     std::vector<int2> cig(s.cigar_cap);
-    std::vector<int4> rmeta(s.node_cap);
+    std::vector<int4> rmeta(s.node_cap), rout(s.node_cap), rinfo(s.node_cap);
     std::vector<int> eidx(s.edge_cap);
     int *p = ints.data();
     auto take = [&](int k) { int *r = p; p += (size_t)k * s.node_cap; return r; };
@@ -40,7 +41,7 @@ extern "C" int hostsim_poa(int n, const long long *off, const uint8_t *bases, ui
     s.idx2id = take(1); s.id2idx = take(1); s.max_left = take(1); s.max_right = take(1); s.remain = take(1);
     s.deg = take(1); s.queue = take(1); s.dp_beg = take(1); s.dp_end = take(1);
     s.edge_id = eid.data(); s.edge_w = ew.data(); s.row_off = roff.data(); s.cells = cellbuf.data(); s.cigar = cig.data();
-    s.rowmeta = rmeta.data(); s.edge_idx = eidx.data();
+    s.rowmeta = rmeta.data(); s.rowout = rout.data(); s.rowinfo = rinfo.data(); s.edge_idx = eidx.data();
     PoaTrace tr;
     tr.best_score = best_score; tr.node_n = node_n; tr.n_ops = n_ops; tr.ops_hash = ops_hash; tr.cells = cells;
     tr.dump_read = dump_read; tr.dump = dump; tr.dump_cap = dump_cap;

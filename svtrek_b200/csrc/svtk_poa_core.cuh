@@ -178,6 +178,9 @@ PD void poa_add_aligned(PoaState &s, int node_id, int new_id) {            // ab
 
 // BFS index (abpoa_BFS_set_node_index, abpoa_graph.c:221): FIFO Kahn order, a node enters the queue together with its
 // aligned group once every member has in-degree 0.  Uses the out-edge order BEFORE this round's edge sort.
+// One thread, one chain of dependent loads per node; the caller has laid out what a step needs so that the chain is three loads
+// deep instead of five: rowout[id] (free until the end of the sort) = {out-degree, first out-edge slot, targets of edges 0 and 1},
+// deg[id] = remaining in-degree | aligned-group size << 24.
 PD void poa_bfs_index(PoaState &s) {
     int head = 0, tail = 0, index = 0;
     s.queue[tail++] = SRC;
@@ -185,13 +188,16 @@ PD void poa_bfs_index(PoaState &s) {
         const int cur = s.queue[head++];
         s.idx2id[index] = cur; s.id2idx[cur] = index++;
         if (cur == SINK) { if (index != s.node_n) s.status = POA_ERR_BFS; return; }
-        const int no = s.out_n[cur], oo = s.out_off[cur];
+        const int4 out = s.rowout[cur];
+        const int no = out.x, oo = out.y;
         for (int i = 0; i < no; ++i) {
-            const int o = s.edge_id[oo + i];
-            if (--s.deg[o] == 0) {
+            const int o = i == 0 ? out.z : (i == 1 ? out.w : s.edge_id[oo + i]);
+            const int d = s.deg[o] - 1;
+            s.deg[o] = d;
+            if ((d & 0xffffff) == 0) {
                 bool ok = true;
-                const int na = s.aln_n[o];
-                for (int j = 0; j < na; ++j) if (s.deg[s.aln_id[o * ALN_MAX + j]] != 0) { ok = false; break; }
+                const int na = (int)((unsigned)d >> 24);
+                for (int j = 0; j < na; ++j) if ((s.deg[s.aln_id[o * ALN_MAX + j]] & 0xffffff) != 0) { ok = false; break; }
                 if (!ok) continue;
                 if (tail + 1 + na > s.node_cap) { s.status = POA_ERR_BFS; return; }
                 s.queue[tail++] = o;
@@ -217,7 +223,11 @@ PD void poa_topological_sort(PoaState &sh) {
     poa_bar<NW>();
     PoaState s = sh;                                           // register copy: the shared struct would be re-read after every store
     const int n = s.node_n;
-    for (int i = lane; i < n; i += (NW * POA_NL)) s.deg[i] = s.in_n[i];
+    for (int i = lane; i < n; i += (NW * POA_NL)) {
+        const int on = s.out_n[i], oo = s.out_off[i];
+        s.deg[i] = s.in_n[i] | (s.aln_n[i] << 24);             // in-degree < 2^24 (node_cap), group size <= ALN_MAX
+        s.rowout[i] = make_int4(on, oo, on > 0 ? s.edge_id[oo] : -1, on > 1 ? s.edge_id[oo + 1] : -1);
+    }
     poa_bar<NW>();
     if (lane == 0) { poa_bfs_index(s); sh.status = s.status; }
     poa_bar<NW>();
@@ -546,7 +556,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
             const int p = pi[k];
             if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
-            else if (p >= 0) { pbv[k] = g.dp_beg[p]; pev[k] = g.dp_end[p]; prv[k] = cells + g.row_off[p] * 5; }
+            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * 5; }
         }
         int beg = imax(0, imin(ml, rt) - w);
         const int end = imin(qlen, imax(mr, rt) + w);
@@ -741,7 +751,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
             pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
             const int p = pi[k];
             if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
-            else if (p >= 0) { pbv[k] = g.dp_beg[p]; pev[k] = g.dp_end[p]; prv[k] = cells + g.row_off[p] * 5; }
+            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * 5; }
         }
         int beg = imax(0, imin(ml, rt) - w);
         const int end = imin(qlen, imax(mr, rt) + w);

@@ -675,6 +675,8 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
     // piece must upload for about as long as it inflates.  Files below 768 MB: one launch after the upload.
     size_t pipe_bytes = std::max<size_t>(384u << 20, image_bytes / 3 + 1);     // B200, 1.9 GB file: 4 pieces 98 ms, 3 pieces 88 ms, 1 piece 126 ms
     if (const char *e = getenv("SVTK_BAM_PIPE_MB")) if (*e) pipe_bytes = (size_t)std::max(1ll, atoll(e)) << 20;
+    size_t first_bytes = pipe_bytes;                                            // the first piece may be smaller: the GPU starts earlier
+    if (const char *e = getenv("SVTK_BAM_PIPE_FIRST_MB")) if (*e) first_bytes = (size_t)std::max(1ll, atoll(e)) << 20;
     bool pipelined = image_bytes >= (768u << 20);
     if (const char *e = getenv("SVTK_BAM_PIPE")) if (*e) pipelined = (*e == '1');
     if (pipelined) {      // concurrent launches need their own token slices: room for the whole load, by the capacity guesses
@@ -824,7 +826,7 @@ static int load_bam_ranges(svtk_ctx *ctx, const char *bam_path, const char *bai_
             }
             img_off += n;
             // ---- ship the new descriptors, launch their inflate behind this chunk's bytes
-            if (fits && pipelined && n_blk > launched && (img_off - last_launch_off >= pipe_bytes || img_off == image_bytes)) {
+            if (fits && pipelined && n_blk > launched && (img_off - last_launch_off >= (first_launch ? first_bytes : pipe_bytes) || img_off == image_bytes)) {
                 last_launch_off = img_off;
                 CU(cudaMemcpyAsync((BgzfBlock *)c->bam_blocks.p + shipped_tab, tab + shipped_tab, sizeof(BgzfBlock) * (n_blk - shipped_tab), cudaMemcpyHostToDevice, c->stream));
                 shipped_tab = n_blk;

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--dir", default=None, help="keep / reuse the generated BAMs in this directory")
     ap.add_argument("--lanes", default="0,1,2,4,8,16,32", help="SVTK_BZ_LANES values (0: the loader's own choice)")
     ap.add_argument("--no-unpiped", action="store_true")
+    ap.add_argument("--settings-json", default=None, help='instead of the built-in sweep: a JSON list of {"ENV": "value"} dicts')
     args = ap.parse_args()
     from svtrek_b200 import api, simreads as S
     d = args.dir or tempfile.mkdtemp(prefix="svtk_bam_")
@@ -41,8 +42,10 @@ def main():
             settings += [dict(SVTK_BAM_PIPE="0"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="128"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256"),
                          dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="640"), dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256", SVTK_BZ_LANES="8"),
                          dict(SVTK_BAM_PIPE="1", SVTK_BAM_PIPE_MB="256", SVTK_BAM_THREADS="16")]
+        if args.settings_json:
+            settings = json.loads(args.settings_json)
         for env in settings:
-            for k in ("SVTK_BZ_LANES", "SVTK_BAM_PIPE", "SVTK_BAM_THREADS", "SVTK_BAM_PIPE_MB"):
+            for k in ("SVTK_BZ_LANES", "SVTK_BAM_PIPE", "SVTK_BAM_THREADS", "SVTK_BAM_PIPE_MB", "SVTK_BAM_PIPE_FIRST_MB", "SVTK_BZ_WARPS"):
                 os.environ.pop(k, None)
             for k, v in env.items():
                 if v != "0" or k != "SVTK_BZ_LANES":

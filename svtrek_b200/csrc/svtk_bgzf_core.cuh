@@ -75,8 +75,8 @@ BZ_HD void bz_prime(BzBits &b, unsigned long long pos) {      // start reading b
     b.nxt = b.w[b.wi];
 }
 BZ_HD unsigned long long bz_ip(const BzBits &b) { return (unsigned long long)b.wi * 4ull; }   // byte offset of the first byte not yet in buf
-BZ_HD void bz_refill(BzBits &b) {         // afterwards cnt >= 32; the load issued here is consumed by the NEXT refill
-    if (b.cnt < 32) { b.buf |= (unsigned long long)b.nxt << b.cnt; b.cnt += 32; b.nxt = b.w[++b.wi]; }
+BZ_HD void bz_refill(BzBits &b) {         // afterwards 33 <= cnt <= 64; the load issued here is consumed by the NEXT refill
+    if (b.cnt <= 32) { b.buf |= (unsigned long long)b.nxt << b.cnt; b.cnt += 32; b.nxt = b.w[++b.wi]; }
 }
 BZ_HD uint32_t bz_take(BzBits &b, int n) {   // n <= 16, cnt >= n
     const uint32_t v = (uint32_t)b.buf & ((1u << n) - 1u);
@@ -340,8 +340,7 @@ BZ_HD void bz_step(BzLane &z, const BzTables &T, const BzLut &L) {
     const uint32_t len = (le & 0xffffu) + bz_take(b, (int)(le >> 16));
     const int d = bz_symbol(b, T.dist, BZ_DBITS, T.dcnt, T.dsym, T.dresume);
     if (d < 0 || d > 29) return bz_fail(z, BZ_ERR_CODE);
-    bz_refill(b);
-    const uint32_t de = bz_dist_lookup(L, d);
+    const uint32_t de = bz_dist_lookup(L, d);             // no refill: 33 bits cover length extra (5) + distance code (15) + distance extra (13)
     const uint32_t dist = (de & 0xffffu) + bz_take(b, (int)(de >> 16));
     if (dist > z.op) return bz_fail(z, BZ_ERR_DIST);
     if (z.op + len > z.out_len) return bz_fail(z, BZ_ERR_OUT);

@@ -150,7 +150,7 @@ struct BzLane {
     BzBits b;
     uint8_t *out;
     uint32_t op, out_len;                 // bytes produced so far / expected (ISIZE)
-    unsigned long long *tok;              // match tokens of this block (bz_step queues, bz_resolve_* copies): pos | len << 16 | (dist - 1) << 25
+    unsigned long long *tok;              // match tokens of this block (bz_step queues, bz_resolve_* copies): pos | len << 16 | (dist - 1) << 32
     uint32_t n_tok;
     int state, last, err;
 };
@@ -256,11 +256,11 @@ BZ_HD uint32_t bz_dist_lookup(const BzLut &L, int d) { return L.w ? L.w[32 + d] 
 // (k_bgzf_resolve: one WARP per block, 32 matches in flight at a time, full occupancy) fills the holes in stream order.
 // A block of n inflated bytes holds at most n / 3 matches.
 BZ_HD unsigned long long bz_token(uint32_t pos, uint32_t len, uint32_t dist) {
-    return (unsigned long long)pos | (unsigned long long)len << 16 | (unsigned long long)(dist - 1u) << 25;
+    return (unsigned long long)(pos | len << 16) | (unsigned long long)(dist - 1u) << 32;   // two 32-bit halves: no shift across the words
 }
-BZ_HD uint32_t bz_tok_pos(unsigned long long t) { return (uint32_t)(t & 0xffffull); }
-BZ_HD uint32_t bz_tok_len(unsigned long long t) { return (uint32_t)(t >> 16) & 511u; }
-BZ_HD uint32_t bz_tok_dist(unsigned long long t) { return ((uint32_t)(t >> 25) & 0xffffu) + 1u; }
+BZ_HD uint32_t bz_tok_pos(unsigned long long t) { return (uint32_t)t & 0xffffu; }
+BZ_HD uint32_t bz_tok_len(unsigned long long t) { return ((uint32_t)t >> 16) & 511u; }
+BZ_HD uint32_t bz_tok_dist(unsigned long long t) { return (uint32_t)(t >> 32) + 1u; }
 BZ_HD unsigned long long bz_tok_capacity(unsigned long long inflated_bytes, unsigned long long n_blocks) { return inflated_bytes / 3ull + n_blocks; }
 BZ_HD unsigned long long bz_tok_offset(unsigned long long out_off, unsigned long long block_index) { return out_off / 3ull + block_index; }
 

@@ -421,3 +421,59 @@ def test_load_bam_refs_shards_equal_the_whole(tmp_path):
         assert np.array_equal(part["pos"], z["pos"][r0:r1]) and np.array_equal(part["end"], z["end"][r0:r1])
     with pytest.raises(api.SvtkError):
         a.load_bam(GOLD_BAM, refs=(2, 5))
+
+
+@pytest.mark.gpu
+def test_ranged_load_near_the_end_of_a_file_beyond_16_gib(tmp_path):
+    """The decoder's 32-bit word index is relative to the bytes a load ships, so the 16 GiB limit applies to those, not to the file
+    (ADVICE r1): a sparse 17 GiB BAM whose second reference sits at the very end loads by reference like a small file; only the
+    whole-file load is refused.  (The hole is never read: a ranged load touches the header blocks and its own byte range.)"""
+    import struct
+    from oracle import binding as B
+    from svtrek_b200 import api, simreads as S
+    if S._packer() is None:
+        pytest.skip("tools/libbgzfpack.so not built")
+    L = 300_000
+    parts, metas, sets = [], [], []
+    for t in range(2):
+        rs, truth = S.simulate(90 + t, contig_lens=[L], coverage=6, read_len=8000, small_rate=0.01, n_sv=30, min_gap=1500)
+        p = str(tmp_path / f"part{t}.bam")
+        m = S.write_bam_fast(p, rs, truth=truth, header_contigs=[L, L], tid_shift=t, want_meta=True)
+        parts.append(p); metas.append(m); sets.append((rs, truth))
+    hdr = int(metas[0]["hdr_bytes"])
+    gap_at = 17 << 30                                          # where reference 1's blocks start
+    big = str(tmp_path / "big.bam")
+    try:
+        with open(big, "wb") as f:
+            with open(parts[0], "rb") as p0:
+                f.write(p0.read(int(metas[0]["size"]) - 28))   # header blocks + reference 0's blocks
+            f.seek(gap_at)                                     # a hole: no disk blocks behind it
+            with open(parts[1], "rb") as p1:
+                p1.seek(hdr)
+                f.write(p1.read())                             # reference 1's blocks + the EOF block
+        if os.stat(big).st_blocks * 512 > (1 << 30):
+            pytest.skip("the file system does not keep the file sparse")
+    except OSError as e:
+        pytest.skip(f"cannot create a sparse 17 GiB file here: {e}")
+    with open(big + ".bai", "wb") as f:
+        f.write(b"BAI\1" + struct.pack("<i", 2))
+        for t, shift in ((0, 0), (1, gap_at - hdr)):
+            rs = sets[t][0]
+            f.write(S.bai_section(metas[t]["bins"], metas[t]["v0"], metas[t]["v1"], rs.pos, rs.end, shift=shift))
+    with api.Auditor(0) as a:
+        with pytest.raises(api.SvtkError, match="16 GiB"):
+            a.load_bam(big)
+        for t in range(2):
+            rs, truth = sets[t]
+            st = a.load_bam(big, refs=(t, t))
+            got = a.copy_reads()
+            assert st["n_reads"] == rs.n_reads and st["image_bytes"] < 2 * os.path.getsize(parts[t])
+            lo, hi = int(got["tid_off"][t]), int(got["tid_off"][t + 1])
+            assert (lo, hi) == (0, rs.n_reads)
+            for k, want in (("pos", rs.pos), ("end", rs.end), ("n_cigar", rs.n_cigar), ("cigar", rs.cigar)):
+                assert np.array_equal(got[k].astype(np.int64), np.asarray(want).astype(np.int64)), (t, k)
+            # the part's windows, asked for on reference t + 1 of the big file == the oracle on the part alone (its reference 1)
+            w = S.windows_from_truth(truth)
+            res = a.refine_windows(np.full_like(w["chrom"], t + 1), w["start"], w["end"], w["pos"], w["kind"])
+            want = B.refine_batch(B.OracleReads(rs), w["chrom"], w["start"], w["end"], w["pos"], w["kind"])
+            assert np.array_equal(res, want) and int((want >= 0).sum()) > 5, t

@@ -64,8 +64,8 @@ def parse_args():
     ap.add_argument("--no-bam", action="store_true", help="skip the file-to-file leg")
     ap.add_argument("--no-c3", action="store_true", help="N = 1: skip the extra configs[2]-sized resident pass (c3_single_gpu)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="file-to-file steps (default: min(steps, 10))")
-    ap.add_argument("--poa-sets", type=int, default=4000, help="INS read sets per GPU of the POA (K3) leg: a bounded sample of configs[3]'s 20k records; 0 skips the leg")
-    ap.add_argument("--poa-steps", type=int, default=2)
+    ap.add_argument("--poa-sets", type=int, default=10000, help="INS read sets per GPU of the POA (K3) leg: a bounded sample (half) of configs[3]'s 20k records; 0 skips the leg")
+    ap.add_argument("--poa-steps", type=int, default=1)
     return ap.parse_args()
 
 

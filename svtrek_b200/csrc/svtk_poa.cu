@@ -74,7 +74,8 @@ struct PoaLaunch {
     unsigned char *scratch;
     PoaTrace trace;
     int have_trace;
-    unsigned long long *times;         // SVTK_POA_DEBUG: per read set {start, end} of %globaltimer (ns), else null
+    unsigned long long *times;         // SVTK_POA_DEBUG: per read set {start, end} of %globaltimer (ns), then {peak cells, nodes | edges << 32}; else null
+    int n_sets_dbg;
 };
 
 // NW = 1: one warp per read set (the throughput shape).  NW = 8: the whole 256-thread CTA shares each DP row and the
@@ -130,7 +131,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 1 ? SVTK_POA_MINB : 1) k_poa_se
             const int len = poa_run_set<NW>(s, xch, L.set_off[sv], L.set_off[sv + 1], L.seq_off, L.bases, L.cons + co, L.cov ? L.cov + co : nullptr, cap,
                                         L.have_trace ? &L.trace : nullptr);
             if (lane == 0) {
-                if (L.times) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); L.times[2 * sv + 1] = t; }
+                if (L.times) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); L.times[2 * sv + 1] = t;
+                               L.times[2 * L.n_sets_dbg + 2 * sv] = (unsigned long long)s.cells_peak; L.times[2 * L.n_sets_dbg + 2 * sv + 1] = (unsigned long long)s.node_n | (unsigned long long)s.edge_top << 32; }
                 L.status[sv] = s.status;
                 L.cons_len[sv] = len;
                 if (!s.status) {
@@ -172,7 +174,10 @@ static PoaCaps caps_for(const SetInfo &si, double scale) {
     const long long dp_rows = std::min<long long>(nodes, (long long)(scale * 4.0 * si.maxlen) + 256);
     const long long len = std::max<long long>(si.maxlen, nodes);
     const int sc_bytes = (std::max<long long>(si.maxlen * MATCH, len * GAP_E1 + GAP_O1) <= 32767 - MISMATCH - GAP_OE1 - GAP_OE2) ? 2 : 4;
-    c.cell_bytes = a16(dp_rows * width * 5 * sc_bytes);
+    // rows x width is what a set can reach; the C4-like sets (8 % errors, 48 reads) peak at 0.54 of it (profiles/r03m: the most any
+    // set of a class used).  3/4 of the product leaves 40 % on top of that; a set that still outgrows its block is rerun with a
+    // 4x block (never truncated), and the scratch budget is what limits how many heavy sets run side by side.
+    c.cell_bytes = a16((long long)(0.75 * (double)(dp_rows * width)) * 5 * sc_bytes);
     return c;
 }
 
@@ -418,9 +423,29 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             std::vector<int> by_work(todo);
             std::sort(by_work.begin(), by_work.end(), [&](int x, int y) { return info[x].work != info[y].work ? info[x].work > info[y].work : x < y; });
             std::vector<char> tier(ns, 0);
+            // The wide tiers buy latency with registers and scratch; they pay only while the batch waits for its heaviest sets.
+            // A batch with enough work to keep every warp-per-set worker busy for longer than its heaviest set takes on one warp
+            // (r >= 1: total work / (workers x heaviest set)) gains nothing from them -- and a wide CTA keeps the warp-per-set
+            // CTAs off its SM (different shared-memory carve-out), so with one on every SM nothing else starts for seconds
+            // (10 000 sets: 22.7 s with 148 wide CTAs, the warp-per-set launch idle until 3.4 s; 11.1 s with none).  Measured
+            // crossover on C4-like sets (batch time with / without the wide tier): 4 000 sets, r = 0.14: 6.7 / 7.5 s; 5 000,
+            // r = 0.21: 7.5 / 7.9 s; 6 000, r = 0.46: 8.5 / 7.8 s.  No wide tier from r = 0.3 on, and never more wide CTAs than
+            // 5/6 of the SMs.
+            int wide_cap = std::max(1, sms * 5 / 6);
+            {
+                std::vector<PoaClass> cls0;
+                long long w0 = 0, m0 = 0;
+                double tot = 0;
+                for (int x : todo) tot += info[x].work;
+                if (plan_group(info, todo.data(), todo.size(), 0, scale, (long long)sms * 32, budget, cls0, w0, m0) == 0 && w0 > 0) {
+                    const double r = tot / ((double)std::min<long long>(w0, (long long)sms * 16) * std::max(wmax, 1.0));
+                    if (r >= 0.3) wide_cap = 0;
+                    if (getenv("SVTK_POA_DEBUG")) fprintf(stderr, "[poa] warp-per-set plan alone: %lld workers, r = %.2f -> at most %d wide CTAs\n", w0, r, wide_cap);
+                }
+            }
             for (int x : by_work) {
                 if (wide_on < 1 || info[x].maxlen <= 2048) break;
-                if ((int)wide.size() < sms && info[x].work * WIDE_GAIN >= wmax) { wide.push_back(x); tier[x] = 2; }
+                if ((int)wide.size() < wide_cap && info[x].work * WIDE_GAIN >= wmax) { wide.push_back(x); tier[x] = 2; }
                 else if (wide_on >= 2 && (int)mid.size() < 2 * sms && info[x].work >= MID_FRAC * wmax) { mid.push_back(x); tier[x] = 1; }
                 else break;
             }
@@ -459,9 +484,9 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         L.trace = tr; L.have_trace = trace ? 1 : 0;
         const bool dbg = getenv("SVTK_POA_DEBUG") != nullptr;
         if (dbg) {
-            if (int rc = c->tmp_c.reserve(16 * (size_t)ns + 16)) return rc;
-            CU(cudaMemsetAsync(c->tmp_c.p, 0, 16 * (size_t)ns, c->stream));
-            L.times = (unsigned long long *)c->tmp_c.p;
+            if (int rc = c->tmp_c.reserve(32 * (size_t)ns + 16)) return rc;
+            CU(cudaMemsetAsync(c->tmp_c.p, 0, 32 * (size_t)ns, c->stream));
+            L.times = (unsigned long long *)c->tmp_c.p; L.n_sets_dbg = ns;
         }
         CU(cudaEventRecord(c->poa_ev[0], c->stream));
         if (wA > 0) {                                          // side streams: the three launches are resident together
@@ -501,20 +526,26 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             float msA = 0.f, msM = 0.f;
             if (wA > 0) cudaEventElapsedTime(&msA, c->poa_ev[0], c->poa_ev[2]);
             if (wM > 0) cudaEventElapsedTime(&msM, c->poa_ev[0], c->poa_ev[3]);
-            std::vector<unsigned long long> tm(2 * (size_t)ns);
-            cudaMemcpy(tm.data(), c->tmp_c.p, 16 * (size_t)ns, cudaMemcpyDeviceToHost);
+            std::vector<unsigned long long> tm(4 * (size_t)ns);
+            cudaMemcpy(tm.data(), c->tmp_c.p, 32 * (size_t)ns, cudaMemcpyDeviceToHost);
             unsigned long long t0 = ~0ull;
             for (int x : todo) if (tm[2 * x]) t0 = std::min(t0, tm[2 * x]);
             for (size_t k = 0; k < cls.size(); ++k) {
-                double first = 1e30, last = 0, sum = 0, lstart = 0;
+                double first = 1e30, last = 0, sum = 0, lstart = 0, use_cells = 0, use_nodes = 0, use_edges = 0;
                 for (int i = cls[k].item_begin; i < cls[k].item_end; ++i) {
                     const int x = todo[i];
+                    {   // how much of the class's block its sets needed (cells: 5 planes x 2 or 4 bytes -- 4 assumed, the upper bound)
+                        const PoaCaps own = caps_for(info[x], scale);
+                        use_cells = std::max(use_cells, (double)tm[2 * ns + 2 * x] * 20.0 / (double)std::max<long long>(own.cell_bytes, 1));
+                        use_nodes = std::max(use_nodes, (double)(tm[2 * ns + 2 * x + 1] & 0xffffffffull) / (double)own.node_cap);
+                        use_edges = std::max(use_edges, (double)(tm[2 * ns + 2 * x + 1] >> 32) / (double)own.edge_cap);
+                    }
                     const double a = (tm[2 * x] - t0) * 1e-6, b = (tm[2 * x + 1] - t0) * 1e-6;
                     first = std::min(first, a); last = std::max(last, b); lstart = std::max(lstart, a); sum += b - a;
                 }
-                fprintf(stderr, "[poa]   class %zu %s cls %d: %d sets, %d workers, %.1f MB/worker; first start %.0f ms, last start %.0f ms, last end %.0f ms, busy %.1f worker-s\n",
+                fprintf(stderr, "[poa]   class %zu %s cls %d: %d sets, %d workers, %.1f MB/worker; first start %.0f ms, last start %.0f ms, last end %.0f ms, busy %.1f worker-s; most of a set's own estimate used: cells %.2f nodes %.2f edges %.2f\n",
                         k, k < clsA.size() ? "wide8" : (k < clsA.size() + clsM.size() ? "wide4" : "warp"), info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
-                        cls[k].worker_end - cls[k].worker_begin, poa_layout(cls[k].caps).total / 1e6, first, lstart, last, sum * 1e-3);
+                        cls[k].worker_end - cls[k].worker_begin, poa_layout(cls[k].caps).total / 1e6, first, lstart, last, sum * 1e-3, use_cells, use_nodes, use_edges);
             }
             std::vector<int> by_end(todo);
             std::sort(by_end.begin(), by_end.end(), [&](int x, int y) { return tm[2 * x + 1] > tm[2 * y + 1]; });

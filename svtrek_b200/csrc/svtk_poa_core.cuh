@@ -113,6 +113,7 @@ struct PoaState {
     int2 *cigar;
     int n_cigar;
     int best_score, best_i, best_j, ret_len;
+    long long cells_peak;                                      // most band cells any one alignment of this set used (sizing statistics)
     long long cells_done, cells_full;                          // band cells / full-matrix-equivalent cells of this read set
     long long t_phase[4];                                      // SM cycles of this read set in: row DP, backtrack, graph fusion, topological sort
     int status;
@@ -945,7 +946,7 @@ PD int poa_run_set(PoaState &s, XCH &xch, long long r0, long long r1, const long
                    int32_t *cov, int cons_cap, const PoaTrace *tr) {
     const int lane = poa_tid<NW>();
     if (lane == 0) {                                           // abpoa_reset (abpoa_graph.c:782): graph = {SRC, SINK}
-        s.node_n = 0; s.edge_top = 0; s.status = POA_OK; s.n_cigar = 0; s.cells_done = 0; s.cells_full = 0;
+        s.node_n = 0; s.edge_top = 0; s.status = POA_OK; s.n_cigar = 0; s.cells_done = 0; s.cells_full = 0; s.cells_peak = 0;
         s.t_phase[0] = s.t_phase[1] = s.t_phase[2] = s.t_phase[3] = 0;
         poa_add_node(s, 0); poa_add_node(s, 0);
     }
@@ -978,6 +979,7 @@ PD int poa_run_set(PoaState &s, XCH &xch, long long r0, long long r1, const long
                 s.n_cigar = g.n_cigar; s.status = g.status;
                 s.t_phase[0] += t1 - t0; s.t_phase[1] += poa_clock() - t1;
                 s.cells_done += cells;
+                if (cells > s.cells_peak) s.cells_peak = cells;
                 s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
             }
         }

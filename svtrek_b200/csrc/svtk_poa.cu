@@ -293,14 +293,14 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     }
     // Size classes: a worker's scratch block is sized for the largest set of its class, and a block for 8 192-base reads is 4x
     // what a set of 4 100-base reads needs, so octaves waste most of the memory of the heavy classes (and memory is what limits
-    // how many heavy sets run side by side).  Quarter octaves (block within ~1.4x of the need) unless the batch spans so many
+    // how many heavy sets run side by side).  Eighths of an octave (block within ~1.2x of the need) unless the batch spans so many
     // octaves that the class table would overflow.
     {
         int lo = 64, hi = 0;
         for (int s = 0; s < ns; ++s) if (info[s].n > 0) { lo = std::min(lo, info[s].cls); hi = std::max(hi, info[s].cls); }
-        int sub = 4;
-        while (sub > 1 && (hi - lo + 1) * sub > 56) sub >>= 1;
-        if (const char *e = getenv("SVTK_POA_SUBCLASS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) sub = std::min(sub, v); }
+        int sub = 8;
+        while (sub > 1 && (hi - lo + 1) * sub > 80) sub >>= 1;                   // three tiers x their classes must fit the class table
+        if (const char *e = getenv("SVTK_POA_SUBCLASS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8) sub = std::min(sub, v); }
         if (sub > 1)
             for (int s = 0; s < ns; ++s) {
                 SetInfo &si = info[s];
@@ -347,7 +347,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     CU(cudaMemsetAsync(d_len, 0, a16(4 * ns) * 2, c->stream));
 
     // control block: cells[6] | 128 class cursors | 128 class descriptors | item list
-    constexpr int MAXC = 128;
+    constexpr int MAXC = 256;
     const size_t ctl_bytes = 64 + 4 * MAXC + a16(sizeof(PoaClass) * MAXC) + 4 * (size_t)ns;
     if (int rc = c->poa_ctl.reserve(ctl_bytes)) return rc;
     unsigned long long *d_cells = (unsigned long long *)c->poa_ctl.p;

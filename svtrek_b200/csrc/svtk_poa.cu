@@ -177,7 +177,7 @@ static PoaCaps caps_for(const SetInfo &si, double scale) {
     // rows x width is what a set can reach; the C4-like sets (8 % errors, 48 reads) peak at 0.54 of it (profiles/r03m: the most any
     // set of a class used).  3/4 of the product leaves 40 % on top of that; a set that still outgrows its block is rerun with a
     // 4x block (never truncated), and the scratch budget is what limits how many heavy sets run side by side.
-    c.cell_bytes = a16((long long)(0.75 * (double)(dp_rows * width)) * 5 * sc_bytes);
+    c.cell_bytes = a16((long long)(0.75 * (double)(dp_rows * width)) * NPL * sc_bytes);
     return c;
 }
 
@@ -439,9 +439,9 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             // (r >= 1: total work / (workers x heaviest set)) gains nothing from them -- and a wide CTA keeps the warp-per-set
             // CTAs off its SM (different shared-memory carve-out), so with one on every SM nothing else starts for seconds
             // (10 000 sets: 22.7 s with 148 wide CTAs, the warp-per-set launch idle until 3.4 s; 11.1 s with none).  Measured
-            // crossover on C4-like sets (batch time with / without the wide tier): 4 000 sets, r = 0.14: 6.7 / 7.5 s; 5 000,
-            // r = 0.21: 7.5 / 7.9 s; 6 000, r = 0.46: 8.5 / 7.8 s.  No wide tier from r = 0.3 on, and never more wide CTAs than
-            // 5/6 of the SMs.
+            // crossover on C4-like sets (batch time with / without the wide tier): 4 000 sets, r = 0.28: 6.7 / 7.5 s; 5 000,
+            // r = 0.35: 7.5 / 7.9 s; 6 000, r = 0.42: 8.5 / 7.8 s.  No wide tier from r = 0.39 on, and never more wide CTAs
+            // than 5/6 of the SMs.
             int wide_cap = std::max(1, sms * 5 / 6);
             {
                 std::vector<PoaClass> cls0;
@@ -449,8 +449,10 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                 double tot = 0;
                 for (int x : todo) tot += info[x].work;
                 if (plan_group(info, todo.data(), todo.size(), 0, scale, (long long)sms * 32, budget, cls0, w0, m0) == 0 && w0 > 0) {
-                    const double r = tot / ((double)std::min<long long>(w0, (long long)sms * 16) * std::max(wmax, 1.0));
-                    if (r >= 0.3) wide_cap = 0;
+                    // workers that count: the machine's set rate stops growing at about 8 warp-per-set workers per SM (10 000 sets:
+                    // 990 sets/s with 1 150 workers, 970 with 2 246 -- a third of the warp cycles then wait for instruction fetch)
+                    const double r = tot / ((double)std::min<long long>(w0, (long long)sms * 8) * std::max(wmax, 1.0));
+                    if (r >= 0.39) wide_cap = 0;
                     if (getenv("SVTK_POA_DEBUG")) fprintf(stderr, "[poa] warp-per-set plan alone: %lld workers, r = %.2f -> at most %d wide CTAs\n", w0, r, wide_cap);
                 }
             }
@@ -547,7 +549,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                     const int x = todo[i];
                     {   // how much of the class's block its sets needed (cells: 5 planes x 2 or 4 bytes -- 4 assumed, the upper bound)
                         const PoaCaps own = caps_for(info[x], scale);
-                        use_cells = std::max(use_cells, (double)tm[2 * ns + 2 * x] * 20.0 / (double)std::max<long long>(own.cell_bytes, 1));
+                        use_cells = std::max(use_cells, (double)tm[2 * ns + 2 * x] * (4.0 * NPL) / (double)std::max<long long>(own.cell_bytes, 1));
                         use_nodes = std::max(use_nodes, (double)(tm[2 * ns + 2 * x + 1] & 0xffffffffull) / (double)own.node_cap);
                         use_edges = std::max(use_edges, (double)(tm[2 * ns + 2 * x + 1] >> 32) / (double)own.edge_cap);
                     }

@@ -78,6 +78,7 @@ constexpr int CG_MATCH = 0, CG_INS = 1, CG_DEL = 2;           // abpoa.h:20-22
 #endif
 constexpr int ROW_CB = POA_ROW_CB;                                     // 32-column chunks of a row whose loads are issued together
 constexpr int PRED_REG = 3;                                   // predecessors of a row held in registers (most nodes have 1-2 in-edges)
+constexpr int NPL = 3;                                        // score planes kept per DP cell: H, E1, E2 (F1 / F2 are recomputed by the backtrack)
 constexpr int ALN_MAX = 4;                                    // an aligned group holds distinct bases: <= 5 nodes (m = 5)
 
 enum { POA_OK = 0, POA_ERR_NODES = 1, POA_ERR_EDGES = 2, POA_ERR_CELLS = 3, POA_ERR_CIGAR = 4, POA_ERR_BACKTRACK = 5,
@@ -360,7 +361,7 @@ PD int poa_cell(const PoaState &s, int i, int plane, int j, int inf_min) {
     const int b = s.dp_beg[i], e = s.dp_end[i];
     if (j < b || j > e) return inf_min;
     const int w = e - b + 1;
-    return (int)reinterpret_cast<const SC *>(s.cells)[s.row_off[i] * 5 + (long long)plane * w + (j - b)];
+    return (int)reinterpret_cast<const SC *>(s.cells)[s.row_off[i] * NPL + (long long)plane * w + (j - b)];
 }
 
 PD void poa_push_cigar(PoaState &s, int op, int arg) {
@@ -379,7 +380,7 @@ PD PoaRow<SC> poa_row(const PoaState &s, int i) {
     const int4 r = s.rowinfo[i];
     PoaRow<SC> v;
     v.b = r.x; v.e = r.y; v.w = r.y - r.x + 1;
-    v.c = reinterpret_cast<const SC *>(s.cells) + (((long long)r.w << 32) | (long long)(unsigned)r.z) * 5;
+    v.c = reinterpret_cast<const SC *>(s.cells) + (((long long)r.w << 32) | (long long)(unsigned)r.z) * NPL;
     return v;
 }
 template <typename SC>
@@ -388,99 +389,167 @@ PD int poa_rcell(const PoaRow<SC> &v, int plane, int j, int inf_min) {
     return (int)v.c[(long long)plane * v.w + (j - v.b)];
 }
 
-// simd_abpoa_cg_backtrack (abpoa_align_simd.c:309-458) with put_gap_on_right = put_gap_at_end = 0.  lane 0.
+// F1 / F2 of row i for the columns beg .. jmax, recomputed from the H / E1 / E2 planes of its predecessors exactly as the row DP
+// computed them (pass 1: Hme = max(M, E1, E2) per column; pass 2: the prefix maxima, chunk by chunk with the same carries), as
+// the DP would have STORED them ((SC) truncation included), into fc1 / fc2 (column - beg).  All lanes of the first warp.
+// Why: the backtrack reads F only where it steps through an insertion (a few per cent of its steps), but keeping F1 / F2 of
+// every cell is 2 of 5 planes of the scratch that limits how many heavy read sets run side by side.
+template <typename SC>
+PD void poa_fill_f(const PoaState &s, int i, int jmax, const uint8_t *q, int inf_min, int lane, int *fc1, int *fc2) {
+    const int4 meta = s.rowmeta[i];
+    const int nb = meta.y & 0xff, pn = meta.y >> 8, po = meta.z;
+    const int4 ri = s.rowinfo[i];
+    const int beg = ri.x, end = imin(ri.y, jmax);
+    int carry_h = inf_min, carry_f1 = inf_min - GAP_OE1, carry_f2 = inf_min - GAP_OE2;
+    for (int cb = beg; cb <= end; cb += POA_NL) {
+        const int j = cb + lane;
+        const bool valid = j <= end;
+        int m = inf_min, e1in = inf_min, e2in = inf_min, sc = 0;
+        if (valid) {
+            for (int k = 0; k < pn; ++k) {
+                const PoaRow<SC> pv = poa_row<SC>(s, s.edge_idx[po + k]);
+                if (j - 1 >= pv.b && j - 1 <= pv.e) m = imax(m, (int)pv.c[j - 1 - pv.b]);
+                if (j >= pv.b && j <= pv.e) { e1in = imax(e1in, (int)pv.c[pv.w + j - pv.b]); e2in = imax(e2in, (int)pv.c[2 * pv.w + j - pv.b]); }
+            }
+            if (j > 0) sc = poa_score(nb, q[j - 1]);
+        }
+        const int hme = valid ? imax(imax(m + sc, e1in), e2in) : inf_min;
+        int left = poa_shfl_up(hme, 1);
+        if (lane == 0) left = carry_h;
+        int g1 = left - GAP_OE1 + lane * GAP_E1, g2 = left - GAP_OE2 + lane * GAP_E2;
+#if POA_NL > 1
+#pragma unroll
+        for (int d = 1; d < POA_NL; d <<= 1) {
+            const int t1 = poa_shfl_up(g1, d), t2 = poa_shfl_up(g2, d);
+            if (lane >= d) { g1 = imax(g1, t1); g2 = imax(g2, t2); }
+        }
+#endif
+        const int f1 = imax(g1 - lane * GAP_E1, carry_f1 - (lane + 1) * GAP_E1);
+        const int f2 = imax(g2 - lane * GAP_E2, carry_f2 - (lane + 1) * GAP_E2);
+        if (valid) { fc1[j - beg] = (int)(SC)f1; fc2[j - beg] = (int)(SC)f2; }
+        carry_h = poa_shfl(hme, POA_NL - 1);
+        carry_f1 = poa_shfl(f1, POA_NL - 1);
+        carry_f2 = poa_shfl(f2, POA_NL - 1);
+    }
+}
+
+// simd_abpoa_cg_backtrack (abpoa_align_simd.c:309-458) with put_gap_on_right = put_gap_at_end = 0.
 // One step is a chain of dependent loads; it is kept short by reading what the topological sort and the DP left per INDEX
 // (rowmeta: node id, base, in-edges; edge_idx: the predecessors' indices; rowinfo: band and cells) instead of going through
 // the node arrays (idx2id -> in_off -> edge_id -> id2idx -> dp_beg / dp_end / row_off -> cell).
+// All lanes of the first warp enter; lane 0 walks.  When a step reaches its F tests in a row whose F values are not at hand it
+// stops, the warp recomputes them (poa_fill_f into the BFS scratch arrays deg / queue, free during an alignment) and lane 0
+// takes the step again from its start -- the M and E tests it repeats have no side effects when they fail.
 template <typename SC>
-PD void poa_backtrack(PoaState &s, const uint8_t *q, int qlen, int inf_min) {
+PD void poa_backtrack(PoaState &s, const uint8_t *q, int qlen, int inf_min, int lane) {
     int i = s.best_i, j = s.best_j, cur_op = OP_ALL;
-    s.n_cigar = 0;
-    if (j < qlen) poa_push_cigar(s, CG_INS, qlen - j);
-    int guard = s.node_n + qlen + 8;
+    int guard = 2 * s.node_n + qlen + 8;
     int4 meta = s.rowmeta[i];
     PoaRow<SC> cur = poa_row<SC>(s, i);
-    while (i > 0 && j > 0) {
-        if (--guard < 0 || s.status) { if (!s.status) s.status = POA_ERR_BACKTRACK; return; }
-        const int id = meta.x;
-        const int sc = poa_score(meta.y & 0xff, q[j - 1]);
-        const int pn = meta.y >> 8, po = meta.z;
-        const int Hij = poa_rcell<SC>(cur, 0, j, inf_min);
-        bool hit = false;
-        if (cur_op & OP_M) {
-            for (int k = 0; k < pn; ++k) {
-                const int p = s.edge_idx[po + k];
-                const PoaRow<SC> pv = poa_row<SC>(s, p);
-                const int4 pm = s.rowmeta[p];
-                if (j - 1 < pv.b || j - 1 > pv.e) continue;
-                if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
-                    poa_push_cigar(s, CG_MATCH, id);
-                    i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
-                    break;
-                }
-            }
-        }
-        if (!hit && (cur_op & OP_E)) {
-            for (int k = 0; k < pn && !hit; ++k) {
-                const int p = s.edge_idx[po + k];
-                const PoaRow<SC> pv = poa_row<SC>(s, p);
-                const int4 pm = s.rowmeta[p];
-                if (j < pv.b || j > pv.e) continue;
-                const int pH = poa_rcell<SC>(pv, 0, j, inf_min);
-                if (cur_op & OP_E1) {
-                    const int pe1 = poa_rcell<SC>(pv, 1, j, inf_min);
-                    const bool ok = (cur_op & OP_M) ? (Hij == pe1) : (poa_rcell<SC>(cur, 1, j, inf_min) == pe1 - GAP_E1);
-                    if (ok) {
-                        cur_op = (pH - GAP_OE1 == pe1) ? (OP_M | OP_F) : OP_E1;
-                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
-                        break;
-                    }
-                }
-                if (cur_op & OP_E2) {
-                    const int pe2 = poa_rcell<SC>(pv, 2, j, inf_min);
-                    const bool ok = (cur_op & OP_M) ? (Hij == pe2) : (poa_rcell<SC>(cur, 2, j, inf_min) == pe2 - GAP_E2);
-                    if (ok) {
-                        cur_op = (pH - GAP_OE2 == pe2) ? (OP_M | OP_F) : OP_E2;
-                        hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
-                        break;
-                    }
-                }
-            }
-        }
-        if (!hit && (cur_op & OP_F)) {
-            const int Hl = poa_rcell<SC>(cur, 0, j - 1, inf_min);
-            if (cur_op & OP_F1) {
-                const int f1 = poa_rcell<SC>(cur, 3, j, inf_min);
-                if (!(cur_op & OP_M) || Hij == f1) {
-                    if (Hl - GAP_OE1 == f1) { cur_op = OP_M | OP_E; hit = true; }
-                    else if (poa_rcell<SC>(cur, 3, j - 1, inf_min) - GAP_E1 == f1) { cur_op = OP_F1; hit = true; }
-                }
-            }
-            if (!hit && (cur_op & OP_F2)) {
-                const int f2 = poa_rcell<SC>(cur, 4, j, inf_min);
-                if (!(cur_op & OP_M) || Hij == f2) {
-                    if (Hl - GAP_OE2 == f2) { cur_op = OP_M | OP_E; hit = true; }
-                    else if (poa_rcell<SC>(cur, 4, j - 1, inf_min) - GAP_E2 == f2) { cur_op = OP_F2; hit = true; }
-                }
-            }
-            if (hit) { poa_push_cigar(s, CG_INS, 1); --j; }
-        }
-        if (!hit && (cur_op & OP_M)) {
-            for (int k = 0; k < pn; ++k) {
-                const int p = s.edge_idx[po + k];
-                const PoaRow<SC> pv = poa_row<SC>(s, p);
-                const int4 pm = s.rowmeta[p];
-                if (j - 1 < pv.b || j - 1 > pv.e) continue;
-                if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
-                    poa_push_cigar(s, CG_MATCH, id);
-                    i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
-                    break;
-                }
-            }
-        }
-        if (!hit) { s.status = POA_ERR_BACKTRACK; return; }
+    int *fc1 = s.deg, *fc2 = s.queue;
+    int fc_row = -1;                                           // row whose F1 / F2 are in fc1 / fc2 (uniform)
+    if (lane == 0) {
+        s.n_cigar = 0;
+        if (j < qlen) poa_push_cigar(s, CG_INS, qlen - j);
     }
-    if (j > 0) poa_push_cigar(s, CG_INS, j);
+    for (;;) {
+        int need = 2;                                          // lane 0 decides: 1 = F values of row i up to column j wanted, 2 = done
+        if (lane == 0)
+        while (i > 0 && j > 0) {
+            if (--guard < 0 || s.status) { if (!s.status) s.status = POA_ERR_BACKTRACK; break; }
+            const int id = meta.x;
+            const int sc = poa_score(meta.y & 0xff, q[j - 1]);
+            const int pn = meta.y >> 8, po = meta.z;
+            const int Hij = poa_rcell<SC>(cur, 0, j, inf_min);
+            bool hit = false;
+            if (cur_op & OP_M) {
+                for (int k = 0; k < pn; ++k) {
+                    const int p = s.edge_idx[po + k];
+                    const PoaRow<SC> pv = poa_row<SC>(s, p);
+                    const int4 pm = s.rowmeta[p];
+                    if (j - 1 < pv.b || j - 1 > pv.e) continue;
+                    if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
+                        poa_push_cigar(s, CG_MATCH, id);
+                        i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
+                        break;
+                    }
+                }
+            }
+            if (!hit && (cur_op & OP_E)) {
+                for (int k = 0; k < pn && !hit; ++k) {
+                    const int p = s.edge_idx[po + k];
+                    const PoaRow<SC> pv = poa_row<SC>(s, p);
+                    const int4 pm = s.rowmeta[p];
+                    if (j < pv.b || j > pv.e) continue;
+                    const int pH = poa_rcell<SC>(pv, 0, j, inf_min);
+                    if (cur_op & OP_E1) {
+                        const int pe1 = poa_rcell<SC>(pv, 1, j, inf_min);
+                        const bool ok = (cur_op & OP_M) ? (Hij == pe1) : (poa_rcell<SC>(cur, 1, j, inf_min) == pe1 - GAP_E1);
+                        if (ok) {
+                            cur_op = (pH - GAP_OE1 == pe1) ? (OP_M | OP_F) : OP_E1;
+                            hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
+                            break;
+                        }
+                    }
+                    if (cur_op & OP_E2) {
+                        const int pe2 = poa_rcell<SC>(pv, 2, j, inf_min);
+                        const bool ok = (cur_op & OP_M) ? (Hij == pe2) : (poa_rcell<SC>(cur, 2, j, inf_min) == pe2 - GAP_E2);
+                        if (ok) {
+                            cur_op = (pH - GAP_OE2 == pe2) ? (OP_M | OP_F) : OP_E2;
+                            hit = true; poa_push_cigar(s, CG_DEL, id); i = p; cur = pv; meta = pm;
+                            break;
+                        }
+                    }
+                }
+            }
+            if (!hit && (cur_op & OP_F)) {
+                if (fc_row != i) { ++guard; need = 1; break; }  // recompute this row's F1 / F2 up to column j, then take the step again
+                // F1 / F2 of (i, j) and (i, j - 1): outside the row's band they read as inf_min, like every cell
+                const bool in_j = j >= cur.b && j <= cur.e, in_l = j - 1 >= cur.b && j - 1 <= cur.e;
+                const int Hl = poa_rcell<SC>(cur, 0, j - 1, inf_min);
+                if (cur_op & OP_F1) {
+                    const int f1 = in_j ? fc1[j - cur.b] : inf_min;
+                    if (!(cur_op & OP_M) || Hij == f1) {
+                        if (Hl - GAP_OE1 == f1) { cur_op = OP_M | OP_E; hit = true; }
+                        else if ((in_l ? fc1[j - 1 - cur.b] : inf_min) - GAP_E1 == f1) { cur_op = OP_F1; hit = true; }
+                    }
+                }
+                if (!hit && (cur_op & OP_F2)) {
+                    const int f2 = in_j ? fc2[j - cur.b] : inf_min;
+                    if (!(cur_op & OP_M) || Hij == f2) {
+                        if (Hl - GAP_OE2 == f2) { cur_op = OP_M | OP_E; hit = true; }
+                        else if ((in_l ? fc2[j - 1 - cur.b] : inf_min) - GAP_E2 == f2) { cur_op = OP_F2; hit = true; }
+                    }
+                }
+                if (hit) { poa_push_cigar(s, CG_INS, 1); --j; }
+            }
+            if (!hit && (cur_op & OP_M)) {
+                for (int k = 0; k < pn; ++k) {
+                    const int p = s.edge_idx[po + k];
+                    const PoaRow<SC> pv = poa_row<SC>(s, p);
+                    const int4 pm = s.rowmeta[p];
+                    if (j - 1 < pv.b || j - 1 > pv.e) continue;
+                    if (poa_rcell<SC>(pv, 0, j - 1, inf_min) + sc == Hij) {
+                        poa_push_cigar(s, CG_MATCH, id);
+                        i = p; cur = pv; meta = pm; --j; hit = true; cur_op = OP_ALL;
+                        break;
+                    }
+                }
+            }
+            if (!hit) { s.status = POA_ERR_BACKTRACK; break; }
+        }
+        need = poa_shfl(need, 0);
+        if (need != 1) break;
+        const int ri = poa_shfl(i, 0), rj = poa_shfl(j, 0);
+        {   // fc1 / fc2 are node arrays: a band wider than the node capacity (only with a block forced too small) asks for a larger block
+            const int4 rr = s.rowinfo[ri];
+            if (imin(rr.y, rj) - rr.x + 1 > s.node_cap) { if (lane == 0) s.status = POA_ERR_NODES; break; }
+        }
+        poa_fill_f<SC>(s, ri, rj, q, inf_min, lane, fc1, fc2);
+        fc_row = ri;
+        poa_sync();
+    }
+    if (lane == 0 && !s.status && j > 0) poa_push_cigar(s, CG_INS, j);
 }
 
 // One alignment of q against the sorted graph: first row, row DP in index order, best end cell.  All lanes.
@@ -492,7 +561,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
     const int n = g.node_n;
     const int w = EXTRA_B + (int)(EXTRA_F * (float)qlen);      // abpoa_align_simd.c:474
     SC *cells = reinterpret_cast<SC *>(g.cells);
-    const long long cell_cap = g.cell_bytes / (long long)(5 * sizeof(SC));
+    const long long cell_cap = g.cell_bytes / (long long)(NPL * sizeof(SC));
     long long top = 0;
 
     // ---- first row (simd_abpoa_cg_first_row / _first_dp, :669-688, :617-633)
@@ -510,7 +579,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
             int h, e1 = inf_min, e2 = inf_min, f1, f2;
             if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
             else { f1 = -GAP_O1 - GAP_E1 * j; f2 = -GAP_O2 - GAP_E2 * j; h = imax(f1, f2); }
-            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; cells[3 * w0 + j] = (SC)f1; cells[4 * w0 + j] = (SC)f2;
+            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; (void)f1; (void)f2;
         }
         top = w0;
     }
@@ -556,8 +625,8 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
         for (int k = 0; k < PRED_REG; ++k) {
             pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
             const int p = pi[k];
-            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
-            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * 5; }
+            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * NPL; }
+            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * NPL; }
         }
         int beg = imax(0, imin(ml, rt) - w);
         const int end = imin(qlen, imax(mr, rt) + w);
@@ -569,7 +638,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
         const int wd = end - beg + 1;
         if (wd <= 0 || pn <= 0) { if (lane == 0) s.status = POA_ERR_BAND; poa_sync(); return top; }
         if (top + wd > cell_cap) { if (lane == 0) s.status = POA_ERR_CELLS; poa_sync(); return top; }
-        SC *row = cells + top * 5;
+        SC *row = cells + top * NPL;
         if (lane == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; g.rowinfo[i] = make_int4(beg, end, (int)(unsigned)(top & 0xffffffffll), (int)(top >> 32)); }
 
         int carry_h = inf_min;                                 // Hme of the column left of the chunk
@@ -594,7 +663,7 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                     for (int k = PRED_REG; k < pn; ++k) {
                         const int p = g.edge_idx[po + k];
                         const int pb = g.dp_beg[p], pe = g.dp_end[p], pw = pe - pb + 1;
-                        const SC *pr = cells + g.row_off[p] * 5;
+                        const SC *pr = cells + g.row_off[p] * NPL;
                         if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
                         if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
                     }
@@ -637,8 +706,6 @@ PD long long poa_align_dp(PoaState &s, const uint8_t *q, int qlen, int inf_min) 
                     row[x] = (SC)h;
                     row[wd + x] = (SC)imax(e1v[u] - GAP_E1, h - GAP_OE1);      // E for the next row (:1067-1071)
                     row[2 * wd + x] = (SC)imax(e2v[u] - GAP_E2, h - GAP_OE2);
-                    row[3 * wd + x] = (SC)f1;
-                    row[4 * wd + x] = (SC)f2;
                     if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
                 }
                 carry_h = poa_shfl(hme, POA_NL - 1);
@@ -708,7 +775,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
     const int n = g.node_n;
     const int w = EXTRA_B + (int)(EXTRA_F * (float)qlen);
     SC *cells = reinterpret_cast<SC *>(g.cells);
-    const long long cell_cap = g.cell_bytes / (long long)(5 * sizeof(SC));
+    const long long cell_cap = g.cell_bytes / (long long)(NPL * sizeof(SC));
     long long top = 0;
 
     if (t == 0) {
@@ -725,7 +792,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
             int h, e1 = inf_min, e2 = inf_min, f1, f2;
             if (j == 0) { h = 0; e1 = -GAP_OE1; e2 = -GAP_OE2; f1 = f2 = inf_min; }
             else { f1 = -GAP_O1 - GAP_E1 * j; f2 = -GAP_O2 - GAP_E2 * j; h = imax(f1, f2); }
-            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; cells[3 * w0 + j] = (SC)f1; cells[4 * w0 + j] = (SC)f2;
+            cells[j] = (SC)h; cells[w0 + j] = (SC)e1; cells[2 * w0 + j] = (SC)e2; (void)f1; (void)f2;
         }
         top = w0;
     }
@@ -751,8 +818,8 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
         for (int k = 0; k < PRED_REG; ++k) {
             pbv[k] = 0x7fffffff; pev[k] = -2; prv[k] = cells;
             const int p = pi[k];
-            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * 5; }
-            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * 5; }
+            if (p == i - 1) { pbv[k] = lb; pev[k] = le; prv[k] = cells + lo * NPL; }
+            else if (p >= 0) { const int4 ri = g.rowinfo[p]; pbv[k] = ri.x; pev[k] = ri.y; prv[k] = cells + (((long long)ri.w << 32) | (long long)(unsigned)ri.z) * NPL; }
         }
         int beg = imax(0, imin(ml, rt) - w);
         const int end = imin(qlen, imax(mr, rt) + w);
@@ -764,7 +831,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
         const int wd = end - beg + 1;
         if (wd <= 0 || pn <= 0) { if (t == 0) s.status = POA_ERR_BAND; __syncthreads(); return top; }
         if (top + wd > cell_cap) { if (t == 0) s.status = POA_ERR_CELLS; __syncthreads(); return top; }
-        SC *row = cells + top * 5;
+        SC *row = cells + top * NPL;
         if (t == 0) { g.dp_beg[i] = beg; g.dp_end[i] = end; g.row_off[i] = top; g.rowinfo[i] = make_int4(beg, end, (int)(unsigned)(top & 0xffffffffll), (int)(top >> 32)); }
 
         int carry_h = inf_min;                                 // Hme of the column left of the block
@@ -785,7 +852,7 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
                 for (int k = PRED_REG; k < pn; ++k) {
                     const int p = g.edge_idx[po + k];
                     const int pb = g.dp_beg[p], pe = g.dp_end[p], pw = pe - pb + 1;
-                    const SC *pr = cells + g.row_off[p] * 5;
+                    const SC *pr = cells + g.row_off[p] * NPL;
                     if (j - 1 >= pb && j - 1 <= pe) m = imax(m, (int)pr[j - 1 - pb]);
                     if (j >= pb && j <= pe) { e1in = imax(e1in, (int)pr[pw + j - pb]); e2in = imax(e2in, (int)pr[2 * pw + j - pb]); }
                 }
@@ -820,8 +887,6 @@ __device__ __noinline__ long long poa_align_dp_cta(PoaState &s, PoaXchg &x, cons
                 row[xo] = (SC)h;
                 row[wd + xo] = (SC)imax(e1in - GAP_E1, h - GAP_OE1);
                 row[2 * wd + xo] = (SC)imax(e2in - GAP_E2, h - GAP_OE2);
-                row[3 * wd + xo] = (SC)f1;
-                row[4 * wd + xo] = (SC)f2;
                 if (h > bv) { bv = h; bl = br = j; } else if (h == bv) br = j;
             }
         }
@@ -972,15 +1037,17 @@ PD int poa_run_set(PoaState &s, XCH &xch, long long r0, long long r1, const long
             const long long t0 = poa_clock();
             if (use16) cells = poa_align_any<int16_t, NW>(s, xch, q, qlen, INF_MIN16);
             else cells = poa_align_any<int32_t, NW>(s, xch, q, qlen, INF_MIN32);
-            if (lane == 0 && !s.status) {
-                const long long t1 = poa_clock();
+            const long long t1 = poa_clock();
+            if (lane < POA_NL && !s.status) {                  // the first warp: lane 0 walks back, the others help with F1 / F2
                 PoaState g = s;
-                if (use16) poa_backtrack<int16_t>(g, q, qlen, INF_MIN16); else poa_backtrack<int32_t>(g, q, qlen, INF_MIN32);
-                s.n_cigar = g.n_cigar; s.status = g.status;
-                s.t_phase[0] += t1 - t0; s.t_phase[1] += poa_clock() - t1;
-                s.cells_done += cells;
-                if (cells > s.cells_peak) s.cells_peak = cells;
-                s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
+                if (use16) poa_backtrack<int16_t>(g, q, qlen, INF_MIN16, lane); else poa_backtrack<int32_t>(g, q, qlen, INF_MIN32, lane);
+                if (lane == 0) {
+                    s.n_cigar = g.n_cigar; s.status = g.status;
+                    s.t_phase[0] += t1 - t0; s.t_phase[1] += poa_clock() - t1;
+                    s.cells_done += cells;
+                    if (cells > s.cells_peak) s.cells_peak = cells;
+                    s.cells_full += (long long)(rows - 1) * (long long)(qlen + 1);
+                }
             }
         }
         poa_bar<NW>();

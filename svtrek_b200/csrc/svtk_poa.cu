@@ -402,6 +402,8 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     std::vector<int32_t> h_status(ns, 0);
     double scale = 1.0, kernel_ms = 0.0;
     if (const char *e = getenv("SVTK_POA_SCALE")) { const double v = atof(e); if (v > 0.0) scale = v; }   // tests: start from a too-small block
+    int slots_per_sm = 32, slots_full = 8;            // warp-per-set CTAs asked for, per SM: with a wide tier / in a batch without one
+    if (const char *e = getenv("SVTK_POA_SLOTS")) { const int v = atoi(e); if (v >= 1 && v <= 64) slots_per_sm = slots_full = v; }
     int wide_on = 1;
     if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere, 1 = tiers <8> and <1> only
     uint64_t relaunched = 0, max_workers = 0;
@@ -448,7 +450,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                 long long w0 = 0, m0 = 0;
                 double tot = 0;
                 for (int x : todo) tot += info[x].work;
-                if (plan_group(info, todo.data(), todo.size(), 0, scale, (long long)sms * 32, budget, cls0, w0, m0) == 0 && w0 > 0) {
+                if (plan_group(info, todo.data(), todo.size(), 0, scale, (long long)sms * slots_per_sm, budget, cls0, w0, m0) == 0 && w0 > 0) {
                     // workers that count: the machine's set rate stops growing at about 8 warp-per-set workers per SM (10 000 sets:
                     // 990 sets/s with 1 150 workers, 970 with 2 246 -- a third of the warp cycles then wait for instruction fetch)
                     const double r = tot / ((double)std::min<long long>(w0, (long long)sms * 8) * std::max(wmax, 1.0));
@@ -479,7 +481,13 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         long long wA = 0, wM = 0, wB = 0, memA = 0, memM = 0, memB = 0;
         if (int rc = plan_group(info, todo.data(), nA, 0, scale, (long long)nA, (long long)(0.45 * (double)budget), clsA, wA, memA)) return rc;
         if (int rc = plan_group(info, todo.data() + nA, nM, (int)nA, scale, (long long)nM, (long long)(0.7 * (double)budget) - memA, clsM, wM, memM)) return rc;
-        if (int rc = plan_group(info, todo.data() + nA + nM, todo.size() - nA - nM, (int)(nA + nM), scale, (long long)sms * 32, budget - memA - memM, clsB, wB, memB)) return rc;
+        // A batch without a wide tier has work for every worker: what counts is the set rate of the machine, and that peaks at 8
+        // warp-per-set CTAs per SM (10 000 C4-like sets, sets/s at 6 / 7 / 8 / 10 / 12 / 15 per SM: 854 / 970 / 1 061 / 989 / 944 /
+        // 955 -- the kernel is ~150 KB of SASS and every warp is in another phase: beyond two warps per scheduler a third of the
+        // warp cycles wait for instruction fetch, profiles/r03y).  With a wide tier the batch is waiting for its heaviest sets and
+        // the small ones are better out of the way early (4 000 sets: 6.4 s uncapped, 6.8 s capped).
+        const long long narrow_W = (long long)sms * ((nA + nM) == 0 ? slots_full : slots_per_sm);
+        if (int rc = plan_group(info, todo.data() + nA + nM, todo.size() - nA - nM, (int)(nA + nM), scale, narrow_W, budget - memA - memM, clsB, wB, memB)) return rc;
         if (clsA.size() + clsM.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
         for (PoaClass &pc : clsM) pc.scratch_off += memA;
         for (PoaClass &pc : clsB) pc.scratch_off += memA + memM;

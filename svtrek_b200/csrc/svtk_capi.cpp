@@ -436,14 +436,13 @@ void svtk_destroy(svtk_ctx *ctx) {
                       &c->bam_splits, &c->bam_seg, &c->bam_rec, &c->bam_ctl, &c->bam_tok, &c->bam_ntok})
         b->release();
     for (PinBuf *b : {&c->stage[0], &c->stage[1], &c->h_idx, &c->h_win, &c->h_result, &c->poa_h, &c->h_audit}) b->release();
-    for (int i = 0; i < 4; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
+    for (int i = 0; i < 3; ++i) if (c->poa_ev[i]) cudaEventDestroy(c->poa_ev[i]);
     for (int i = 0; i < 5; ++i) if (c->bam_ev[i]) cudaEventDestroy(c->bam_ev[i]);
     c->bam_h.release(); c->bam_tab.release();
     for (int i = 0; i < 3; ++i) { c->bam_stage[i].release(); if (c->bam_stage_ev[i]) cudaEventDestroy(c->bam_stage_ev[i]); }
     for (int i = 0; i < 4; ++i) { if (c->bam_side_ev[i]) cudaEventDestroy(c->bam_side_ev[i]); if (c->bam_side[i]) cudaStreamDestroy(c->bam_side[i]); }
     for (int i = 0; i < 8; ++i) if (c->bam_chunk_ev[i]) cudaEventDestroy(c->bam_chunk_ev[i]);
     if (c->poa_side) cudaStreamDestroy(c->poa_side);
-    if (c->poa_side2) cudaStreamDestroy(c->poa_side2);
     for (int i = 0; i < 2; ++i) if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     for (int i = 0; i < 4; ++i) if (c->prof_ev[i]) cudaEventDestroy(c->prof_ev[i]);
     if (c->own_stream) cudaStreamDestroy(c->stream);

@@ -77,8 +77,7 @@ struct Ctx {
     // K3 (svtk_poa.cu): device copies of one batch of read sets, per-worker scratch, events
     DevBuf poa_in, poa_out, poa_scratch, poa_ctl;
     PinBuf poa_h;
-    cudaEvent_t poa_ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    cudaStream_t poa_side2 = nullptr;     // ... and the half-wide launch (4 warps per set) of the next tier
+    cudaEvent_t poa_ev[3] = {nullptr, nullptr, nullptr};
     cudaStream_t poa_side = nullptr;      // the CTA-wide launch of the heaviest read sets runs beside the warp-per-set launch
 
     // svtk_load_bam (svtk_bam.cu): the raw file, its inflated image and the record table stay resident (INS-sequence extraction

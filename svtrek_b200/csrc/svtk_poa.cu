@@ -354,30 +354,17 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     int *d_cursors = (int *)((unsigned char *)c->poa_ctl.p + 64);
     PoaClass *d_classes = (PoaClass *)((unsigned char *)c->poa_ctl.p + 64 + 4 * MAXC);
     int *d_items = (int *)((unsigned char *)d_classes + a16(sizeof(PoaClass) * MAXC));
-    for (int i = 0; i < 4; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
+    for (int i = 0; i < 3; ++i) if (!c->poa_ev[i]) CU(cudaEventCreate(&c->poa_ev[i]));
     if (!c->poa_side) {
         CU(cudaStreamCreateWithFlags(&c->poa_side, cudaStreamNonBlocking));
-        CU(cudaStreamCreateWithFlags(&c->poa_side2, cudaStreamNonBlocking));
         // First use: run both instantiations once with no work.  k_poa_sets<1> needs a larger local-memory pool than
         // k_poa_sets<8>; growing that pool is a device-wide synchronisation, which would otherwise serialise the first
         // pair of launches (measured: 12.1 s instead of 6.7 s for the first batch).
-        // The three instantiations must be able to share an SM: a CTA is only placed on an SM whose shared-memory carve-out
-        // suits its kernel, and left to itself the driver sizes the carve-out for each kernel's own CTAs -- the warp-per-set
-        // CTAs then stay off every SM that holds a wide CTA (measured: they started only when wide CTAs retired).  Same
-        // carve-out for all three: 64 KB covers 16 warp-per-set CTAs.
-        int carve = -1;
-        if (const char *e = getenv("SVTK_POA_CARVEOUT")) carve = atoi(e);
-        if (carve >= 0) {
-            CU(cudaFuncSetAttribute(k_poa_sets<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-            CU(cudaFuncSetAttribute(k_poa_sets<4>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-            CU(cudaFuncSetAttribute(k_poa_sets<8>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-        }
         CU(cudaMemsetAsync(d_classes, 0, sizeof(PoaClass) * MAXC, c->stream));
         PoaLaunch L0{};
         L0.classes = d_classes; L0.cursors = d_cursors; L0.scratch = (unsigned char *)c->poa_ctl.p;
         k_poa_sets<1><<<1, 32, 0, c->stream>>>(L0);
         k_poa_sets<8><<<1, 256, 0, c->stream>>>(L0);
-        k_poa_sets<4><<<1, 128, 0, c->stream>>>(L0);
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(c->stream));
     }
@@ -405,7 +392,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
     int slots_per_sm = 32, slots_full = 8;            // warp-per-set CTAs asked for, per SM: with a wide tier / in a batch without one
     if (const char *e = getenv("SVTK_POA_SLOTS")) { const int v = atoi(e); if (v >= 1 && v <= 64) slots_per_sm = slots_full = v; }
     int wide_on = 1;
-    if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere, 1 = tiers <8> and <1> only
+    if (const char *e = getenv("SVTK_POA_WIDE")) wide_on = atoi(e);                                        // experiments: 0 = one warp per set everywhere
     uint64_t relaunched = 0, max_workers = 0;
     CU(cudaMemsetAsync(d_cells, 0, 64, c->stream));
     int sms = 148;
@@ -421,15 +408,14 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             return x < y;
         });
         // A set alone on a warp can outlast the rest of the batch: its reads are aligned one after the other, and only the row DP
-        // (about half of its time) gets faster with more threads.  Three tiers by estimated work, heaviest first:
-        //   k_poa_sets<8>  the sets within 1/1.5 of the heaviest one (reads beyond 2 kb, at most one per SM: a 256-thread CTA
-        //                  holds more than half an SM's registers) -- done in ~0.45 of their single-warp time;
-        //   k_poa_sets<4>  the sets that would still outlast those on a single warp (work above 0.44 of the heaviest; at most two
-        //                  per SM) -- done in ~0.56 of their single-warp time at half the registers;
+        // (about half of its time) gets faster with more threads.  Two tiers by estimated work:
+        //   k_poa_sets<8>  the sets within 1/1.5 of the heaviest one (reads beyond 2 kb; a 256-thread CTA holds more than half an
+        //                  SM's registers) -- done in ~0.45 of their single-warp time;
         //   k_poa_sets<1>  everything else, one warp per set: the shape that fills the SMs.
-        // Measured on 4 000 C4-like sets: tiers 8 / 1 only ended at 7.1 s with the <8> launch done at 5.1 s (profiles/r02n..r02q).
-        constexpr double WIDE_GAIN = 1.5, MID_FRAC = 0.44;
-        std::vector<int> wide, mid, rest;
+        // (A third tier of 4-warp CTAs for the sets in between, and a common shared-memory carve-out so that all kernels share
+        // SMs, were measured and dropped: DESIGN.md 6.)
+        constexpr double WIDE_GAIN = 1.5;
+        std::vector<int> wide, rest;
         {
             double wmax = 0;
             for (int x : todo) wmax = std::max(wmax, info[x].work);
@@ -461,7 +447,6 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             for (int x : by_work) {
                 if (wide_on < 1 || info[x].maxlen <= 2048) break;
                 if ((int)wide.size() < wide_cap && info[x].work * WIDE_GAIN >= wmax) { wide.push_back(x); tier[x] = 2; }
-                else if (wide_on >= 2 && (int)mid.size() < 2 * sms && info[x].work >= MID_FRAC * wmax) { mid.push_back(x); tier[x] = 1; }
                 else break;
             }
             for (int x : todo) if (!tier[x]) rest.push_back(x);
@@ -471,30 +456,25 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                 return x < y;
             };
             std::sort(wide.begin(), wide.end(), by_class);
-            std::sort(mid.begin(), mid.end(), by_class);
             todo = wide;
-            todo.insert(todo.end(), mid.begin(), mid.end());
             todo.insert(todo.end(), rest.begin(), rest.end());
         }
-        const size_t nA = wide.size(), nM = mid.size();
-        std::vector<PoaClass> clsA, clsM, clsB;
-        long long wA = 0, wM = 0, wB = 0, memA = 0, memM = 0, memB = 0;
+        const size_t nA = wide.size();
+        std::vector<PoaClass> clsA, clsB;
+        long long wA = 0, wB = 0, memA = 0, memB = 0;
         if (int rc = plan_group(info, todo.data(), nA, 0, scale, (long long)nA, (long long)(0.45 * (double)budget), clsA, wA, memA)) return rc;
-        if (int rc = plan_group(info, todo.data() + nA, nM, (int)nA, scale, (long long)nM, (long long)(0.7 * (double)budget) - memA, clsM, wM, memM)) return rc;
         // A batch without a wide tier has work for every worker: what counts is the set rate of the machine, and that peaks at 8
         // warp-per-set CTAs per SM (10 000 C4-like sets, sets/s at 6 / 7 / 8 / 10 / 12 / 15 per SM: 854 / 970 / 1 061 / 989 / 944 /
         // 955 -- the kernel is ~150 KB of SASS and every warp is in another phase: beyond two warps per scheduler a third of the
         // warp cycles wait for instruction fetch, profiles/r03y).  With a wide tier the batch is waiting for its heaviest sets and
         // the small ones are better out of the way early (4 000 sets: 6.4 s uncapped, 6.8 s capped).
-        const long long narrow_W = (long long)sms * ((nA + nM) == 0 ? slots_full : slots_per_sm);
-        if (int rc = plan_group(info, todo.data() + nA + nM, todo.size() - nA - nM, (int)(nA + nM), scale, narrow_W, budget - memA - memM, clsB, wB, memB)) return rc;
-        if (clsA.size() + clsM.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
-        for (PoaClass &pc : clsM) pc.scratch_off += memA;
-        for (PoaClass &pc : clsB) pc.scratch_off += memA + memM;
+        const long long narrow_W = (long long)sms * (nA == 0 ? slots_full : slots_per_sm);
+        if (int rc = plan_group(info, todo.data() + nA, todo.size() - nA, (int)nA, scale, narrow_W, budget - memA, clsB, wB, memB)) return rc;
+        if (clsA.size() + clsB.size() > (size_t)MAXC) return fail(SVTK_ERR_ARG, "poa: more than %d size classes", MAXC);
+        for (PoaClass &pc : clsB) pc.scratch_off += memA;
         std::vector<PoaClass> cls(clsA);
-        cls.insert(cls.end(), clsM.begin(), clsM.end());
         cls.insert(cls.end(), clsB.begin(), clsB.end());
-        if (int rc = c->poa_scratch.reserve((size_t)(memA + memM + memB))) return rc;
+        if (int rc = c->poa_scratch.reserve((size_t)(memA + memB))) return rc;
         CU(cudaMemcpyAsync(d_items, todo.data(), 4 * todo.size(), cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(d_classes, cls.data(), sizeof(PoaClass) * cls.size(), cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemsetAsync(d_cursors, 0, 4 * MAXC, c->stream));
@@ -519,24 +499,14 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
             CU(cudaEventRecord(c->poa_ev[2], c->poa_side));
             c->launches += 1;
         }
-        if (wM > 0) {
-            CU(cudaStreamWaitEvent(c->poa_side2, c->poa_ev[0], 0));
-            PoaLaunch LM = L;
-            LM.n_classes = (int)clsM.size(); LM.classes = d_classes + clsA.size(); LM.cursors = d_cursors + clsA.size();
-            k_poa_sets<4><<<(unsigned)wM, 128, 0, c->poa_side2>>>(LM);
-            CU(cudaGetLastError());
-            CU(cudaEventRecord(c->poa_ev[3], c->poa_side2));
-            c->launches += 1;
-        }
         if (wB > 0) {
             PoaLaunch LB = L;
-            LB.n_classes = (int)clsB.size(); LB.classes = d_classes + clsA.size() + clsM.size(); LB.cursors = d_cursors + clsA.size() + clsM.size();
+            LB.n_classes = (int)clsB.size(); LB.classes = d_classes + clsA.size(); LB.cursors = d_cursors + clsA.size();
             k_poa_sets<1><<<(unsigned)wB, 32, 0, c->stream>>>(LB);
             CU(cudaGetLastError());
             c->launches += 1;
         }
         if (wA > 0) CU(cudaStreamWaitEvent(c->stream, c->poa_ev[2], 0));
-        if (wM > 0) CU(cudaStreamWaitEvent(c->stream, c->poa_ev[3], 0));
         CU(cudaEventRecord(c->poa_ev[1], c->stream));
         CU(cudaMemcpyAsync(h_status.data(), d_status, 4 * (size_t)ns, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));                  // also: todo / cls were read by the copies above
@@ -544,9 +514,8 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
         CU(cudaEventElapsedTime(&ms, c->poa_ev[0], c->poa_ev[1]));
         kernel_ms += ms;
         if (getenv("SVTK_POA_DEBUG")) {
-            float msA = 0.f, msM = 0.f;
+            float msA = 0.f;
             if (wA > 0) cudaEventElapsedTime(&msA, c->poa_ev[0], c->poa_ev[2]);
-            if (wM > 0) cudaEventElapsedTime(&msM, c->poa_ev[0], c->poa_ev[3]);
             std::vector<unsigned long long> tm(4 * (size_t)ns);
             cudaMemcpy(tm.data(), c->tmp_c.p, 32 * (size_t)ns, cudaMemcpyDeviceToHost);
             unsigned long long t0 = ~0ull;
@@ -565,7 +534,7 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                     first = std::min(first, a); last = std::max(last, b); lstart = std::max(lstart, a); sum += b - a;
                 }
                 fprintf(stderr, "[poa]   class %zu %s cls %d: %d sets, %d workers, %.1f MB/worker; first start %.0f ms, last start %.0f ms, last end %.0f ms, busy %.1f worker-s; most of a set's own estimate used: cells %.2f nodes %.2f edges %.2f\n",
-                        k, k < clsA.size() ? "wide8" : (k < clsA.size() + clsM.size() ? "wide4" : "warp"), info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
+                        k, k < clsA.size() ? "wide" : "warp", info[todo[cls[k].item_begin]].cls, cls[k].item_end - cls[k].item_begin,
                         cls[k].worker_end - cls[k].worker_begin, poa_layout(cls[k].caps).total / 1e6, first, lstart, last, sum * 1e-3, use_cells, use_nodes, use_edges);
             }
             std::vector<int> by_end(todo);
@@ -575,10 +544,10 @@ extern "C" int svtk_poa_consensus(svtk_ctx *ctx, const svtk_poa_batch *b, uint8_
                 fprintf(stderr, "[poa]   late set %d: cls %d maxlen %d reads %d work %.3g: %.0f -> %.0f ms\n", x, info[x].cls, info[x].maxlen, info[x].n, info[x].work,
                         (tm[2 * x] - t0) * 1e-6, (tm[2 * x + 1] - t0) * 1e-6);
             }
-            fprintf(stderr, "[poa] attempt %d: <8> %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; <4> %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
-                    attempt, (long long)nA, wA, memA / 1e6, msA, (long long)nM, wM, memM / 1e6, msM, todo.size() - nA - nM, wB, memB / 1e6, ms);
+            fprintf(stderr, "[poa] attempt %d: <8> %lld sets / %lld CTAs (%.1f MB) done at %.1f ms; warp-per-set %zu sets / %lld CTAs (%.1f MB); all done at %.1f ms\n",
+                    attempt, (long long)nA, wA, memA / 1e6, msA, todo.size() - nA, wB, memB / 1e6, ms);
         }
-        max_workers = std::max<uint64_t>(max_workers, (uint64_t)(wA + wM + wB));
+        max_workers = std::max<uint64_t>(max_workers, (uint64_t)(wA + wB));
         std::vector<int> again;
         for (int s : todo) {
             const int st = h_status[s];

@@ -77,7 +77,10 @@ constexpr int CG_MATCH = 0, CG_INS = 1, CG_DEL = 2;           // abpoa.h:20-22
 #define POA_ROW_CB 2
 #endif
 constexpr int ROW_CB = POA_ROW_CB;                                     // 32-column chunks of a row whose loads are issued together
-constexpr int PRED_REG = 3;                                   // predecessors of a row held in registers (most nodes have 1-2 in-edges)
+#ifndef POA_PRED_REG
+#define POA_PRED_REG 3
+#endif
+constexpr int PRED_REG = POA_PRED_REG;                                   // predecessors of a row held in registers (most nodes have 1-2 in-edges)
 constexpr int NPL = 3;                                        // score planes kept per DP cell: H, E1, E2 (F1 / F2 are recomputed by the backtrack)
 constexpr int ALN_MAX = 4;                                    // an aligned group holds distinct bases: <= 5 nodes (m = 5)
 
